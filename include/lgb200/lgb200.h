@@ -1,0 +1,191 @@
+/*
+ * lgb200.h -- the C ABI of libgran-b200 (libgran_b200/liblgb200.so).
+ *
+ * This is the drop-in boundary: plain pointers and sizes, `extern "C"`, int return codes, no C++ or
+ * torch types.  The reference has no FFI -- its hot path sits behind a C++ template API -- so each
+ * entry point below names the reference interface it stands in for (paths relative to the reference
+ * repository root; LT = deps/libtimestep/include/libtimestep, LG = include/libgran).  The header
+ * templates under include/libgran/ and include/libtimestep/ of THIS repository (same class names and
+ * constructor signatures as the reference) call nothing but these functions; so do the Python
+ * bindings in libgran_b200/system.py used by tests/ and bench.py.
+ *
+ * Conventions
+ *   - every function returns LG_OK (0) or a negative LG_E* code; lg_last_error() returns a
+ *     thread-local human-readable message for the last failure.  No exception crosses the ABI.
+ *   - all particle fields are FP64, array-of-xyz, length 3*n doubles, in the caller's particle
+ *     order (the order of the vectors handed to the reference's granular_system constructor).
+ *   - host pointers unless a parameter is named `d_*` (device pointer on the system's device).
+ *   - a system handle is not thread-safe; it owns one CUDA stream on one device.
+ *   - there is NO CPU fallback: lg_create fails with LG_ENODEVICE when no CUDA device is usable.
+ */
+#ifndef LGB200_H
+#define LGB200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LGB200_ABI_VERSION 1
+
+enum {
+    LG_OK = 0,
+    LG_EINVAL = -1,     /* bad argument / call order                                    */
+    LG_ENODEVICE = -2,  /* no usable CUDA device (there is no CPU fallback)             */
+    LG_ECUDA = -3,      /* a CUDA runtime call or kernel failed                         */
+    LG_ENOMEM = -4,     /* device or host allocation failed                             */
+    LG_ESIZE = -5,      /* size mismatch -- the ABI's form of LT/exception/exception.h:11-24
+                           SizeMismatchException (LT/rotational_system/rotational_system.h:69-70) */
+    LG_ECAPACITY = -6   /* a fixed-capacity table overflowed (contact slots per particle,
+                           bonds per particle, pairs >= 2^32); see lg_set_max_contacts  */
+};
+
+/* field ids: the six state vectors of LT/rotational_system/rotational_system.h:94-121,128 */
+enum { LG_X = 0, LG_V = 1, LG_A = 2, LG_THETA = 3, LG_OMEGA = 4, LG_ALPHA = 5 };
+
+/* Constructor arguments of LG/contact_force/contact_force.h:10-30 (and of the wall twin
+ * LG/contact_force/surface_contact_force.h:10-30) that are not common to the whole system. */
+typedef struct lg_contact_params {
+    double k, gamma_n;
+    double k_t, gamma_t, mu_s, phi_d;
+    double k_r, gamma_r, mu_r, phi_r;
+    double k_o, gamma_o, mu_o, phi_o;
+    double dt; /* the functor's own spring-update time step (contact_force.h:28,138) */
+} lg_contact_params;
+
+typedef struct lg_system lg_system;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+
+/* granular_system / granular_system_neighbor_list constructor, part 1
+ * (LG/granular_system/granular_system.h:53-64, granular_system_neighbor_list.h:54-64):
+ * n particles of equal radius r_part, mass and moment of inertia (the constants every reference
+ * functor receives, e.g. contact_force.h:25-27).  device = CUDA ordinal, or -1 for the current one. */
+int lg_create(int64_t n, double r_part, double mass, double inertia, int device, lg_system** out);
+int lg_destroy(lg_system* s);
+const char* lg_last_error(void);
+int lg_abi_version(void);
+
+/* ---- state ---------------------------------------------------------------------------------- */
+
+/* The x0, v0, theta0, omega0 vectors moved into rotational_generic_system
+ * (LT/rotational_system/rotational_system.h:52-66).  Copies host -> device; resets a, alpha to zero
+ * (:80,83-86) and re-arms the first-step half kick (LT/rotational_integrator/
+ * rotational_velocity_verlet_half.h:45-60). `n_check` must equal the n given to lg_create, else
+ * LG_ESIZE (rotational_system.h:69-70). */
+int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v, const double* theta,
+                 const double* omega);
+
+/* get_x / get_v / get_a / get_theta / get_omega / get_alpha (rotational_system.h:94-121): copies
+ * device -> host, in the caller's particle order.  Implies a stream synchronisation. */
+int lg_get_field(lg_system* s, int field, double* out_3n);
+
+/* Device-resident view of a field for callers that keep data on the GPU (3*n doubles, xyz-interleaved,
+ * in the caller's particle order as long as no reordering is active).  Valid until lg_destroy. */
+int lg_device_field(lg_system* s, int field, double** d_ptr);
+
+/* ---- binary force models (the members of LG/granular_system/binary_force_container.h:17-34) --- */
+
+/* contact_force_functor (LG/contact_force/contact_force.h:8-157). */
+int lg_set_contact(lg_system* s, const lg_contact_params* p);
+
+/* hamaker_functor (LG/hamaker_force/hamaker_force.h:19-48). */
+int lg_set_hamaker(lg_system* s, double A, double h0);
+
+/* sinter_functor constructor (LG/sinter_bridge/sinter_bridge.h:101-212): bonds every pair with
+ * |dist - 2 r| <= critical_separation using the positions of the last lg_set_state, drawing one unit
+ * vector per bond, in lexicographic (i < j) order, from `gen` (the random_unit_vector_generator
+ * argument, :124; redrawn while collinear with the bond axis, :171-175).  Also installs the embedded
+ * contact model (:134-135) from `contact` and arms the connector update of sinter_step_handler
+ * (:24-42,55-75).  n_bonds_out (nullable) receives the number of unordered bonds. */
+typedef void (*lg_unit_vector_fn)(void* user, double out_xyz[3]);
+int lg_build_sinter_bonds(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d,
+                          double critical_separation, lg_unit_vector_fn gen, void* user, int64_t* n_bonds_out);
+
+/* Same tables supplied explicitly (what sinter_bridge.h:139-141,185-209 hold after construction):
+ * n_ordered records (i, j), both orientations present, each with the 5 connectors attached to i
+ * (15 doubles) and 5 rest lengths. */
+int lg_set_bonds(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d, int64_t n_ordered,
+                 const int64_t* ij_pairs, const double* connectors_15, const double* rest_lengths_5);
+
+/* Capacity of the per-particle table of simultaneously overlapping non-bonded neighbours
+ * (replaces the dense N x N spring store of contact_force.h:53; default 16, kissing number is 12).
+ * Must be called before the first step. Exceeding it at run time makes the step return LG_ECAPACITY. */
+int lg_set_max_contacts(lg_system* s, int max_contacts);
+
+/* ---- unary force models (LG/granular_system/unary_force_container.h:17-34) --------------------- */
+
+/* triangular_facet<surface_contact_force_functor, surface_hamaker_functor>
+ * (LG/surface_force/triangular_facet.h:18-29; LG/contact_force/surface_contact_force.h:8-30;
+ * LG/hamaker_force/surface_hamaker_force.h:8-15).  surface_contact may be NULL (no wall contact);
+ * has_hamaker = 0 omits the wall van der Waals term.  Facets are folded in the order added. */
+int lg_add_facet(lg_system* s, const double vertices_9[9], const double v_facet[3],
+                 const lg_contact_params* surface_contact, int has_hamaker, double A, double h0, int* facet_id);
+/* triangular_facet::v_facet is a public data member (triangular_facet.h:69) */
+int lg_facet_set_velocity(lg_system* s, int facet_id, const double v_facet[3]);
+/* triangular_facet::update_positions(dt) (triangular_facet.h:62-66) */
+int lg_facet_update_positions(lg_system* s, int facet_id, double dt);
+/* triangular_facet::get_vertices() (:57-59) */
+int lg_facet_get_vertices(lg_system* s, int facet_id, double out_9[9]);
+
+/* ---- pair loop and integrator ------------------------------------------------------------------ */
+
+/* Selects the neighbor-list pair loop (LT/rotational_system/rotational_binary_system_neighbors_omp.h)
+ * with Verlet radius r_verlet; without this call the system is the all-pairs loop
+ * (LT/rotational_system/rotational_binary_system_omp.h:69-90).  As in the reference the list is
+ * empty until the first lg_update_neighbor_list (:66). */
+int lg_enable_neighbor_list(lg_system* s, double r_verlet);
+
+/* update_neighbor_list() (rotational_binary_system_neighbors_omp.h:102-116): rows
+ * { j != i : |x_i - x_j| < r_verlet }, ascending j, bit-identical predicate. */
+int lg_update_neighbor_list(lg_system* s);
+
+/* do_step(dt) (rotational_system.h:89-91 -> rotational_velocity_verlet_half.h:43-76). */
+int lg_do_step(lg_system* s, double dt);
+
+/* The driver loop of test/hamaker_neighbor.cpp:120-124 run without returning to the host:
+ *   for k in 0..n_steps: if (rebuild_every > 0 && step % rebuild_every == 0) update_neighbor_list();
+ *                        do_step(dt); if (move_facets) every facet.update_positions(dt);
+ * `step` is the system's own running count of do_step calls. */
+int lg_run(lg_system* s, double dt, int64_t n_steps, int64_t rebuild_every, int move_facets);
+
+/* reset_acceleration_buffers() (rotational_system.h:83-86). */
+int lg_reset_acceleration_buffers(lg_system* s);
+
+/* Blocks until all queued work of this system has finished; reports asynchronous errors
+ * (LG_ECUDA, LG_ECAPACITY). */
+int lg_synchronize(lg_system* s);
+
+/* ---- introspection used by the parity tests ---------------------------------------------------- */
+
+int lg_get_neighbor_count(lg_system* s, int64_t* n_pairs);
+/* row_ptr: n + 1 entries, cols: n_pairs entries (the private neighbor_list of
+ * rotational_binary_system_neighbors_omp.h:122 flattened to CSR). */
+int lg_get_neighbor_rows(lg_system* s, int64_t* row_ptr, int64_t* cols);
+/* the three springs of ordered pair (i, j): contact_springs[i * n + j] of contact_force.h:100,156 */
+int lg_get_contact_springs(lg_system* s, int64_t i, int64_t j, double out_9[9]);
+/* returns 1 in *bonded if (i, j) is bonded and copies spring_connectors[i * n + j] /
+ * spring_lengths[i * n + j] (sinter_bridge.h:139-140) */
+int lg_get_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double conn_15[15], double len_5[5]);
+
+/* counters: out[0] ordered neighbor pairs, [1] ordered pairs holding a contact-spring record,
+ * [2] ordered bonded pairs, [3] do_step calls so far, [4] neighbor rebuilds so far,
+ * [5] kernels launched so far, [6] number of cells of the last rebuild, [7] reserved */
+int lg_get_counters(lg_system* s, int64_t out_8[8]);
+
+/* Device reductions restating test/compute_energy.cpp:7-58 and test/mass_distribution.cpp:7-26
+ * (fixed-shape tree, deterministic run to run):
+ *   out[0] total kinetic energy   out[1] translational KE   out[2] rotational KE
+ *   out[3] |linear momentum|      out[4] |angular momentum|
+ *   out[5..7] centre of mass      out[8] radius of gyration */
+int lg_diagnostics(lg_system* s, double out_9[9]);
+
+/* Selects the force-kernel organisation: 0 = one thread per particle (simple, validation),
+ * 1 = tiled pair-parallel kernel (default).  Both give bit-identical results. */
+int lg_set_kernel_variant(lg_system* s, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LGB200_H */

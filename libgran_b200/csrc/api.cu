@@ -1,0 +1,876 @@
+// api.cu -- the extern "C" layer of include/lgb200/lgb200.h: owns the device buffers of one granular
+// system and sequences the kernels.  Host-side counterpart of
+//   LT/rotational_system/rotational_system.h:41-130               (state ownership, getters)
+//   LT/rotational_integrator/rotational_velocity_verlet_half.h:43-76 (do_step schedule, first-step kick)
+//   LT/rotational_system/rotational_binary_system_neighbors_omp.h:102-116 (update_neighbor_list)
+//   LG/sinter_bridge/sinter_bridge.h:148-211                      (bond construction, host, init only)
+// No CPU fallback exists: every compute entry point launches CUDA kernels or fails.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <memory>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/lgb200/lgb200.h"
+#include "system.h"
+
+namespace lg {
+thread_local int64_t g_launch_count = 0;
+}
+
+namespace {
+
+thread_local std::string g_error;
+
+int fail(int code, const std::string& msg) {
+    g_error = msg;
+    return code;
+}
+
+#define LG_CUDA(expr)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (expr);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(e_ == cudaErrorMemoryAllocation ? LG_ENOMEM : LG_ECUDA,                         \
+                        std::string(#expr) + ": " + cudaGetErrorString(e_));                            \
+    } while (0)
+
+#define LG_TRY(expr)              \
+    do {                          \
+        int rc_ = (expr);         \
+        if (rc_ != LG_OK) return rc_; \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;  // elements
+    ~DevBuf() { release(); }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    // grow-only; contents are NOT preserved
+    cudaError_t reserve(size_t elems, double headroom = 1.0) {
+        if (elems <= cap) return cudaSuccess;
+        release();
+        size_t want = (size_t)((double)elems * headroom) + 16;
+        cudaError_t e = cudaMalloc(&p, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+};
+
+}  // namespace
+
+using namespace lg;
+
+struct lg_system {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int64_t n = 0;
+    ModelParams mp{};
+    int mask = 0;  // binary models
+    int variant = 1;
+
+    DevBuf<double> x, v, a, th, w, al;
+    bool state_set = false;
+    bool kicked = false;
+
+    // neighbor rows
+    bool use_nl = false;
+    double r_verlet = 0.0;
+    bool allpairs_built = false;
+    DevBuf<uint32_t> row_ptr;
+    DevBuf<int32_t> cols;
+    DevBuf<uint8_t> tag;
+    int64_t n_pairs = 0;
+
+    // contact slots
+    int S = 16;
+    DevBuf<double> spr;
+    DevBuf<int32_t> sgid;
+    bool slots_ready = false;
+
+    // bonds
+    int64_t n_bonds = 0;  // ordered
+    DevBuf<uint32_t> bptr;
+    DevBuf<int32_t> bj, brev;
+    DevBuf<double> bconn, blen;
+    std::vector<uint32_t> h_bptr;
+    std::vector<int32_t> h_bj;
+
+    // facets
+    std::vector<Facet> facets;
+    std::vector<std::unique_ptr<DevBuf<double>>> wspr;
+    std::vector<std::unique_ptr<DevBuf<uint8_t>>> wact;
+
+    // cell-list scratch
+    DevBuf<double> bbox_scratch, bbox_out;
+    DevBuf<int32_t> cell_of, order;
+    DevBuf<uint32_t> cell_start, cell_cursor, scan_scratch;
+    int64_t last_cells = 0;
+
+    // diagnostics scratch
+    DevBuf<double> diag_partials, diag_out;
+    DevBuf<unsigned long long> counter;
+
+    DevBuf<int> err;
+    double* h_pinned = nullptr;  // 32 doubles of pinned scratch
+
+    int64_t steps = 0, rebuilds = 0;
+    int64_t launches0 = 0;
+};
+
+namespace {
+
+int check_async(lg_system* s) {
+    int h = 0;
+    LG_CUDA(cudaMemcpyAsync(&h, s->err.p, sizeof(int), cudaMemcpyDeviceToHost, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    if (h & ERR_SLOT_OVERFLOW)
+        return fail(LG_ECAPACITY, "a particle has more simultaneous contacts than lg_set_max_contacts allows");
+    if (h & ERR_BOND_LOOKUP) return fail(LG_ECAPACITY, "bond table lookup failed");
+    return LG_OK;
+}
+
+int ensure_slots(lg_system* s) {
+    if (s->slots_ready) return LG_OK;
+    const size_t n = (size_t)s->n;
+    LG_CUDA(s->spr.reserve(n * s->S * 9));
+    LG_CUDA(s->sgid.reserve(n * s->S));
+    LG_CUDA(cudaMemsetAsync(s->sgid.p, 0xff, n * s->S * sizeof(int32_t), s->stream));
+    s->slots_ready = true;
+    return LG_OK;
+}
+
+int ensure_pair_capacity(lg_system* s, int64_t pairs) {
+    if ((size_t)pairs > s->cols.cap) {
+        LG_CUDA(s->cols.reserve((size_t)pairs, 1.25));
+        LG_CUDA(s->tag.reserve(s->cols.cap));
+    }
+    return LG_OK;
+}
+
+int retag(lg_system* s) {
+    LG_TRY(ensure_slots(s));
+    launch_retag((int)s->n, s->row_ptr.p, s->cols.p, s->tag.p, s->sgid.p, s->spr.p, s->S,
+                 s->n_bonds > 0 ? s->bptr.p : nullptr, s->bj.p, s->err.p, s->stream);
+    LG_CUDA(cudaGetLastError());
+    return LG_OK;
+}
+
+int build_allpairs(lg_system* s) {
+    const int64_t n = s->n;
+    if (n > 65536) return fail(LG_ECAPACITY, "all-pairs loop supports n <= 65536; call lg_enable_neighbor_list");
+    const int64_t pairs = n * (n - 1);
+    LG_TRY(ensure_pair_capacity(s, pairs));
+    if (n == 1) {
+        LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, 2 * sizeof(uint32_t), s->stream));
+    } else {
+        launch_allpairs_fill((int)n, s->row_ptr.p, s->cols.p, s->stream);
+        LG_CUDA(cudaGetLastError());
+    }
+    s->n_pairs = pairs;
+    s->allpairs_built = true;
+    return retag(s);
+}
+
+int evaluate(lg_system* s) {
+    ForceArgs A{};
+    A.n = (int)s->n;
+    A.x = s->x.p; A.v = s->v.p; A.w = s->w.p; A.a = s->a.p; A.al = s->al.p;
+    A.row_ptr = s->row_ptr.p; A.cols = s->cols.p; A.tag = s->tag.p;
+    A.spr = s->spr.p; A.sgid = s->sgid.p; A.S = s->S;
+    A.bptr = s->bptr.p; A.bj = s->bj.p; A.brev = s->brev.p; A.bconn = s->bconn.p; A.blen = s->blen.p;
+    A.mp = s->mp;
+    A.n_facets = (int)s->facets.size();
+    for (int f = 0; f < A.n_facets; f++) {
+        A.facets[f] = s->facets[(size_t)f];
+        A.wspr[f] = s->wspr[(size_t)f]->p;
+        A.wact[f] = s->wact[(size_t)f]->p;
+    }
+    A.err = s->err.p;
+    launch_force(A, s->mask, s->variant, s->stream);
+    LG_CUDA(cudaGetLastError());
+    return LG_OK;
+}
+
+int prepare(lg_system* s) {
+    if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
+    if (s->mask == 0 && s->facets.empty()) return fail(LG_EINVAL, "no force model installed");
+    if ((s->mask & MODEL_CONTACT) && (s->mask & MODEL_SINTER))
+        return fail(LG_EINVAL, "contact and sinter models are mutually exclusive (sinter embeds contact)");
+    LG_TRY(ensure_slots(s));
+    if (!s->use_nl && !s->allpairs_built) LG_TRY(build_allpairs(s));
+    return LG_OK;
+}
+
+int step(lg_system* s, double dt) {
+    if (!s->kicked) {
+        // first call: evaluate, half kick back, evaluate again (rotational_velocity_verlet_half.h:45-60)
+        LG_TRY(evaluate(s));
+        launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
+        LG_CUDA(cudaGetLastError());
+        LG_TRY(evaluate(s));
+        s->kicked = true;
+    }
+    IntegrateArgs I{};
+    I.n = (int)s->n;
+    I.x = s->x.p; I.v = s->v.p; I.th = s->th.p; I.w = s->w.p; I.a = s->a.p; I.al = s->al.p;
+    I.bptr = s->n_bonds > 0 ? s->bptr.p : nullptr;
+    I.bconn = s->bconn.p;
+    I.dt = dt;
+    launch_integrate(I, s->stream);
+    LG_CUDA(cudaGetLastError());
+    LG_TRY(evaluate(s));
+    s->steps++;
+    return LG_OK;
+}
+
+int rebuild(lg_system* s) {
+    if (!s->use_nl) return LG_OK;  // granular_system (all pairs) has no update_neighbor_list
+    if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
+    LG_TRY(ensure_slots(s));
+    const int n = (int)s->n;
+    cudaStream_t st = s->stream;
+    // 1. bounding box -> grid
+    launch_bbox(n, s->x.p, s->bbox_scratch.p, s->bbox_out.p, st);
+    LG_CUDA(cudaGetLastError());
+    LG_CUDA(cudaMemcpyAsync(s->h_pinned, s->bbox_out.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    NeighborGrid g{};
+    double cell = s->r_verlet * (1.0 + 1e-6);
+    const double max_cells = 16.0 * (double)n + 65536.0;
+    for (;;) {
+        double total = 1.0;
+        for (int k = 0; k < 3; k++) {
+            double ext = s->h_pinned[3 + k] - s->h_pinned[k];
+            if (!(ext >= 0.0) || !std::isfinite(ext)) return fail(LG_EINVAL, "non-finite particle positions");
+            double d = std::floor(ext / cell) + 1.0;
+            g.dim[k] = d > 2.0e9 ? 2000000000 : (int)d;
+            total *= d;
+        }
+        if (total <= max_cells) {
+            g.n_cells = (int64_t)g.dim[0] * g.dim[1] * g.dim[2];
+            break;
+        }
+        cell *= 1.26;
+    }
+    g.cell = cell;
+    for (int k = 0; k < 3; k++) g.lo[k] = s->h_pinned[k];
+    s->last_cells = g.n_cells;
+    // 2. histogram, scan, scatter
+    const size_t nc1 = (size_t)g.n_cells + 1;
+    LG_CUDA(s->cell_start.reserve(nc1, 1.25));
+    LG_CUDA(s->cell_cursor.reserve(nc1, 1.25));
+    LG_CUDA(s->scan_scratch.reserve(scan_scratch_elems(std::max(nc1, (size_t)n + 1)), 1.25));
+    LG_CUDA(cudaMemsetAsync(s->cell_start.p, 0, nc1 * sizeof(uint32_t), st));
+    LG_CUDA(cudaMemsetAsync(s->cell_cursor.p, 0, nc1 * sizeof(uint32_t), st));
+    launch_cell_count(n, s->x.p, g, s->cell_of.p, s->cell_start.p, st);
+    launch_exclusive_scan_u32(s->cell_start.p, nc1, s->scan_scratch.p, st);
+    launch_cell_fill(n, s->cell_of.p, s->cell_start.p, s->cell_cursor.p, s->order.p, st);
+    // 3. rows: count, scan, fill + sort
+    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, st);
+    LG_CUDA(cudaMemsetAsync(s->row_ptr.p + n, 0, sizeof(uint32_t), st));
+    launch_exclusive_scan_u32(s->row_ptr.p, (size_t)n + 1, s->scan_scratch.p, st);
+    LG_CUDA(cudaGetLastError());
+    uint32_t total_pairs = 0;
+    LG_CUDA(cudaMemcpyAsync(&total_pairs, s->row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    s->n_pairs = (int64_t)total_pairs;
+    LG_TRY(ensure_pair_capacity(s, s->n_pairs));
+    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, s->cols.p, st);
+    LG_CUDA(cudaGetLastError());
+    s->rebuilds++;
+    return retag(s);
+}
+
+// ---- host-side bond CSR construction ---------------------------------------------------------------
+struct HostBond {
+    int64_t i, j;
+    double conn[15];
+    double len[5];
+};
+
+int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
+    // CSR by (i, j) ascending
+    std::sort(recs.begin(), recs.end(), [](HostBond const& a, HostBond const& b) { return a.i != b.i ? a.i < b.i : a.j < b.j; });
+    const size_t nb = recs.size();
+    const size_t n = (size_t)s->n;
+    std::vector<uint32_t> bptr(n + 1, 0);
+    for (auto const& r : recs) bptr[(size_t)r.i + 1]++;
+    for (size_t i = 0; i < n; i++) {
+        if (bptr[i + 1] > (uint32_t)kMaxBondsPerParticle)
+            return fail(LG_ECAPACITY, "more than 120 bonds on one particle");
+        bptr[i + 1] += bptr[i];
+    }
+    std::vector<int32_t> bj(nb), brev(nb);
+    std::vector<double> conn(nb * 15), len(nb * 5);
+    for (size_t b = 0; b < nb; b++) {
+        bj[b] = (int32_t)recs[b].j;
+        std::memcpy(&conn[b * 15], recs[b].conn, sizeof(recs[b].conn));
+        std::memcpy(&len[b * 5], recs[b].len, sizeof(recs[b].len));
+        if (b > 0 && recs[b].i == recs[b - 1].i && recs[b].j == recs[b - 1].j) return fail(LG_EINVAL, "duplicate bond record");
+    }
+    for (size_t b = 0; b < nb; b++) {
+        const size_t j = (size_t)recs[b].j;
+        const int32_t want = (int32_t)recs[b].i;
+        auto first = bj.begin() + bptr[j], last = bj.begin() + bptr[j + 1];
+        auto it = std::lower_bound(first, last, want);
+        if (it == last || *it != want) return fail(LG_EINVAL, "bond (i, j) given without its mirror (j, i)");
+        brev[b] = (int32_t)(it - bj.begin());
+    }
+    LG_CUDA(s->bptr.reserve(n + 1));
+    LG_CUDA(s->bj.reserve(nb));
+    LG_CUDA(s->brev.reserve(nb));
+    LG_CUDA(s->bconn.reserve(nb * 15));
+    LG_CUDA(s->blen.reserve(nb * 5));
+    LG_CUDA(cudaMemcpyAsync(s->bptr.p, bptr.data(), (n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
+    if (nb) {
+        LG_CUDA(cudaMemcpyAsync(s->bj.p, bj.data(), nb * sizeof(int32_t), cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->brev.p, brev.data(), nb * sizeof(int32_t), cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->bconn.p, conn.data(), nb * 15 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->blen.p, len.data(), nb * 5 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+    }
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    s->n_bonds = (int64_t)nb;
+    s->h_bptr = std::move(bptr);
+    s->h_bj = std::move(bj);
+    // existing rows (if any) need their tags refreshed
+    if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
+    return LG_OK;
+}
+
+void to_cp(const lg_contact_params* p, ContactParams& c) {
+    c.k = p->k; c.gamma_n = p->gamma_n;
+    c.k_t = p->k_t; c.gamma_t = p->gamma_t; c.mu_s = p->mu_s; c.phi_d = p->phi_d;
+    c.k_r = p->k_r; c.gamma_r = p->gamma_r; c.mu_r = p->mu_r; c.phi_r = p->phi_r;
+    c.k_o = p->k_o; c.gamma_o = p->gamma_o; c.mu_o = p->mu_o; c.phi_o = p->phi_o;
+    c.dt = p->dt;
+}
+
+double* field_ptr(lg_system* s, int field) {
+    switch (field) {
+        case LG_X: return s->x.p;
+        case LG_V: return s->v.p;
+        case LG_A: return s->a.p;
+        case LG_THETA: return s->th.p;
+        case LG_OMEGA: return s->w.p;
+        case LG_ALPHA: return s->al.p;
+        default: return nullptr;
+    }
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) {
+        cudaGetDevice(&prev);
+        if (prev != dev) cudaSetDevice(dev);
+        else prev = -1;
+    }
+    ~DeviceGuard() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
+}  // namespace
+
+#define LG_ENTER(s)                                             \
+    if ((s) == nullptr) return fail(LG_EINVAL, "null system"); \
+    DeviceGuard guard_((s)->device)
+
+extern "C" {
+
+const char* lg_last_error(void) { return g_error.c_str(); }
+int lg_abi_version(void) { return LGB200_ABI_VERSION; }
+
+int lg_create(int64_t n, double r_part, double mass, double inertia, int device, lg_system** out) {
+    if (out == nullptr) return fail(LG_EINVAL, "out is null");
+    *out = nullptr;
+    if (n <= 0 || n > 2000000000LL) return fail(LG_EINVAL, "n out of range");
+    if (!(r_part > 0.0) || !(mass > 0.0) || !(inertia > 0.0)) return fail(LG_EINVAL, "r_part, mass, inertia must be positive");
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count <= 0)
+        return fail(LG_ENODEVICE, std::string("no CUDA device available (there is no CPU fallback): ") +
+                                      (e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0"));
+    if (device < 0) {
+        LG_CUDA(cudaGetDevice(&device));
+    } else if (device >= count) {
+        return fail(LG_ENODEVICE, "device ordinal out of range");
+    }
+    std::unique_ptr<lg_system> s(new (std::nothrow) lg_system());
+    if (!s) return fail(LG_ENOMEM, "host allocation failed");
+    s->device = device;
+    DeviceGuard guard(device);
+    s->n = n;
+    s->mp.r = r_part;
+    s->mp.mass = mass;
+    s->mp.inertia = inertia;
+    LG_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    const size_t n3 = 3 * (size_t)n;
+    LG_CUDA(s->x.reserve(n3));
+    LG_CUDA(s->v.reserve(n3));
+    LG_CUDA(s->a.reserve(n3));
+    LG_CUDA(s->th.reserve(n3));
+    LG_CUDA(s->w.reserve(n3));
+    LG_CUDA(s->al.reserve(n3));
+    LG_CUDA(s->row_ptr.reserve((size_t)n + 1));
+    LG_CUDA(s->cols.reserve(16));
+    LG_CUDA(s->tag.reserve(16));
+    LG_CUDA(s->bptr.reserve((size_t)n + 1));
+    LG_CUDA(s->bj.reserve(16));
+    LG_CUDA(s->brev.reserve(16));
+    LG_CUDA(s->bconn.reserve(16));
+    LG_CUDA(s->blen.reserve(16));
+    LG_CUDA(s->cell_of.reserve((size_t)n));
+    LG_CUDA(s->order.reserve((size_t)n));
+    LG_CUDA(s->bbox_scratch.reserve(6 * 1024));
+    LG_CUDA(s->bbox_out.reserve(8));
+    LG_CUDA(s->diag_partials.reserve(12 * 512));
+    LG_CUDA(s->diag_out.reserve(16));
+    LG_CUDA(s->counter.reserve(2));
+    LG_CUDA(s->err.reserve(1));
+    LG_CUDA(cudaMemsetAsync(s->err.p, 0, sizeof(int), s->stream));
+    LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, ((size_t)n + 1) * sizeof(uint32_t), s->stream));
+    LG_CUDA(cudaMemsetAsync(s->bptr.p, 0, ((size_t)n + 1) * sizeof(uint32_t), s->stream));
+    LG_CUDA(cudaMemsetAsync(s->a.p, 0, n3 * sizeof(double), s->stream));
+    LG_CUDA(cudaMemsetAsync(s->al.p, 0, n3 * sizeof(double), s->stream));
+    LG_CUDA(cudaMallocHost(&s->h_pinned, 32 * sizeof(double)));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    s->launches0 = g_launch_count;
+    *out = s.release();
+    return LG_OK;
+}
+
+int lg_destroy(lg_system* s) {
+    if (s == nullptr) return LG_OK;
+    {
+        DeviceGuard guard(s->device);
+        if (s->stream) {
+            cudaStreamSynchronize(s->stream);
+            cudaStreamDestroy(s->stream);
+        }
+        if (s->h_pinned) cudaFreeHost(s->h_pinned);
+        delete s;  // DevBuf destructors free device memory while the device is current
+    }
+    return LG_OK;
+}
+
+int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v, const double* theta, const double* omega) {
+    LG_ENTER(s);
+    if (n_check != s->n)
+        return fail(LG_ESIZE, "size mismatch in arguments passed to lg_set_state (x0, v0, theta0, omega0 must hold n particles)");
+    if (!x || !v || !theta || !omega) return fail(LG_EINVAL, "null state pointer");
+    const size_t bytes = 3 * (size_t)s->n * sizeof(double);
+    LG_CUDA(cudaMemcpyAsync(s->x.p, x, bytes, cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaMemcpyAsync(s->v.p, v, bytes, cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaMemcpyAsync(s->th.p, theta, bytes, cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaMemcpyAsync(s->w.p, omega, bytes, cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaMemsetAsync(s->a.p, 0, bytes, s->stream));
+    LG_CUDA(cudaMemsetAsync(s->al.p, 0, bytes, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));  // the caller may reuse its buffers
+    s->state_set = true;
+    s->kicked = false;
+    return LG_OK;
+}
+
+int lg_get_field(lg_system* s, int field, double* out) {
+    LG_ENTER(s);
+    double* src = field_ptr(s, field);
+    if (!src || !out) return fail(LG_EINVAL, "bad field id or null output");
+    LG_CUDA(cudaMemcpyAsync(out, src, 3 * (size_t)s->n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    return check_async(s);
+}
+
+int lg_device_field(lg_system* s, int field, double** d_ptr) {
+    LG_ENTER(s);
+    double* src = field_ptr(s, field);
+    if (!src || !d_ptr) return fail(LG_EINVAL, "bad field id or null output");
+    *d_ptr = src;
+    return LG_OK;
+}
+
+int lg_set_contact(lg_system* s, const lg_contact_params* p) {
+    LG_ENTER(s);
+    if (!p) return fail(LG_EINVAL, "null params");
+    if (s->mask & MODEL_SINTER) return fail(LG_EINVAL, "sinter model already installed (it embeds the contact model)");
+    to_cp(p, s->mp.cp);
+    s->mask |= MODEL_CONTACT;
+    return LG_OK;
+}
+
+int lg_set_hamaker(lg_system* s, double A, double h0) {
+    LG_ENTER(s);
+    s->mp.hamaker_A = A;
+    s->mp.hamaker_h0 = h0;
+    s->mask |= MODEL_HAMAKER;
+    return LG_OK;
+}
+
+int lg_set_max_contacts(lg_system* s, int max_contacts) {
+    LG_ENTER(s);
+    if (s->slots_ready) return fail(LG_EINVAL, "lg_set_max_contacts must precede the first step / rebuild");
+    if (max_contacts < 1 || max_contacts > kMaxSlots) return fail(LG_EINVAL, "max_contacts must be in 1..120");
+    s->S = max_contacts;
+    return LG_OK;
+}
+
+int lg_set_bonds(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d, int64_t n_ordered,
+                 const int64_t* ij, const double* conn, const double* len) {
+    LG_ENTER(s);
+    if (!contact || n_ordered < 0 || (n_ordered > 0 && (!ij || !conn || !len))) return fail(LG_EINVAL, "bad bond arguments");
+    if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
+    std::vector<HostBond> recs((size_t)n_ordered);
+    for (int64_t b = 0; b < n_ordered; b++) {
+        HostBond& r = recs[(size_t)b];
+        r.i = ij[2 * b];
+        r.j = ij[2 * b + 1];
+        if (r.i < 0 || r.j < 0 || r.i >= s->n || r.j >= s->n || r.i == r.j) return fail(LG_EINVAL, "bond index out of range");
+        std::memcpy(r.conn, conn + 15 * b, sizeof(r.conn));
+        std::memcpy(r.len, len + 5 * b, sizeof(r.len));
+    }
+    to_cp(contact, s->mp.cp);
+    s->mp.k_d = k_d;
+    s->mp.gamma_d = gamma_d;
+    s->mask |= MODEL_SINTER;
+    return install_bonds(s, recs);
+}
+
+int lg_build_sinter_bonds(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d, double crit,
+                          lg_unit_vector_fn gen, void* user, int64_t* n_bonds_out) {
+    LG_ENTER(s);
+    if (!contact || !gen) return fail(LG_EINVAL, "null contact params or generator");
+    if (!s->state_set) return fail(LG_EINVAL, "lg_set_state must precede lg_build_sinter_bonds");
+    if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
+    const int64_t n = s->n;
+    const double r = s->mp.r;
+    std::vector<double> hx(3 * (size_t)n);
+    LG_CUDA(cudaMemcpyAsync(hx.data(), s->x.p, hx.size() * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    auto X = [&](int64_t i) { return mk3(hx[3 * (size_t)i], hx[3 * (size_t)i + 1], hx[3 * (size_t)i + 2]); };
+
+    // candidate partners j > i within 2r + crit (uniform host grid), visited in lexicographic order
+    // so that the generator is consumed exactly like the i < j double loop of sinter_bridge.h:148-149
+    const double range = 2.0 * r + crit;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int64_t i = 0; i < n; i++)
+        for (int k = 0; k < 3; k++) {
+            lo[k] = std::min(lo[k], hx[3 * (size_t)i + k]);
+            hi[k] = std::max(hi[k], hx[3 * (size_t)i + k]);
+        }
+    double cell = range * 1.0001;
+    int64_t dim[3];
+    for (;;) {
+        double total = 1.0;
+        for (int k = 0; k < 3; k++) {
+            double d = std::floor((hi[k] - lo[k]) / cell) + 1.0;
+            dim[k] = (int64_t)d;
+            total *= d;
+        }
+        if (total <= 16.0 * (double)n + 65536.0) break;
+        cell *= 1.26;
+    }
+    auto cell_of = [&](int64_t i, int64_t c[3]) {
+        for (int k = 0; k < 3; k++) {
+            int64_t t = (int64_t)std::floor((hx[3 * (size_t)i + k] - lo[k]) / cell);
+            c[k] = std::min(std::max<int64_t>(t, 0), dim[k] - 1);
+        }
+    };
+    const int64_t ncell = dim[0] * dim[1] * dim[2];
+    std::vector<int64_t> start((size_t)ncell + 1, 0), order((size_t)n), cidx((size_t)n);
+    for (int64_t i = 0; i < n; i++) {
+        int64_t c[3];
+        cell_of(i, c);
+        cidx[(size_t)i] = (c[0] * dim[1] + c[1]) * dim[2] + c[2];
+        start[(size_t)cidx[(size_t)i] + 1]++;
+    }
+    for (int64_t c = 0; c < ncell; c++) start[(size_t)c + 1] += start[(size_t)c];
+    {
+        std::vector<int64_t> cur(start.begin(), start.end() - 1);
+        for (int64_t i = 0; i < n; i++) order[(size_t)cur[(size_t)cidx[(size_t)i]]++] = i;  // ascending id inside a cell
+    }
+    std::vector<HostBond> recs;
+    std::vector<int64_t> cand;
+    int64_t bonds = 0;
+    for (int64_t i = 0; i < n - 1; i++) {
+        int64_t c[3];
+        cell_of(i, c);
+        cand.clear();
+        for (int64_t dx = -1; dx <= 1; dx++)
+            for (int64_t dy = -1; dy <= 1; dy++)
+                for (int64_t dz = -1; dz <= 1; dz++) {
+                    const int64_t cx = c[0] + dx, cy = c[1] + dy, cz = c[2] + dz;
+                    if (cx < 0 || cy < 0 || cz < 0 || cx >= dim[0] || cy >= dim[1] || cz >= dim[2]) continue;
+                    const int64_t cl = (cx * dim[1] + cy) * dim[2] + cz;
+                    for (int64_t q = start[(size_t)cl]; q < start[(size_t)cl + 1]; q++)
+                        if (order[(size_t)q] > i) cand.push_back(order[(size_t)q]);
+                }
+        std::sort(cand.begin(), cand.end());
+        const d3 part_i = X(i);
+        for (int64_t j : cand) {
+            const d3 part_j = X(j);
+            const double separation = norm(part_j - part_i) - 2.0 * r;
+            if (std::fabs(separation) > crit) continue;  // sinter_bridge.h:155-157
+            const d3 n_i = normalized(part_j - part_i);
+            const d3 n_j = -n_i;
+            d3 tv, db;
+            do {  // :171-175
+                double t[3];
+                gen(user, t);
+                tv = mk3(t[0], t[1], t[2]);
+                db = cross(tv, n_j);
+            } while (norm(db) == 0.0);
+            d3 ds = tv - dot(tv, n_i) * n_i;
+            db = db / sqrt(dot(db, db));
+            ds = ds / sqrt(dot(ds, ds));
+            HostBond bi{}, bjr{};
+            bi.i = i; bi.j = j; bjr.i = j; bjr.j = i;
+            const d3 ci[5] = {part_i + ds * r, part_i - ds * r, part_i + db * r, part_i - db * r, part_i + n_i * r};
+            const d3 cj[5] = {part_j + ds * r, part_j - ds * r, part_j + db * r, part_j - db * r, part_j + n_j * r};
+            for (int k = 0; k < 5; k++) {
+                store3(bi.conn + 3 * k, ci[k]);
+                store3(bjr.conn + 3 * k, cj[k]);
+                bi.len[k] = bjr.len[k] = (k < 4) ? 2.0 * r : 0.0;
+            }
+            recs.push_back(bi);
+            recs.push_back(bjr);
+            bonds++;
+        }
+    }
+    to_cp(contact, s->mp.cp);
+    s->mp.k_d = k_d;
+    s->mp.gamma_d = gamma_d;
+    s->mask |= MODEL_SINTER;
+    if (n_bonds_out) *n_bonds_out = bonds;
+    return install_bonds(s, recs);
+}
+
+int lg_add_facet(lg_system* s, const double vertices[9], const double v_facet[3], const lg_contact_params* sc, int has_hamaker,
+                 double A, double h0, int* facet_id) {
+    LG_ENTER(s);
+    if (!vertices || !v_facet) return fail(LG_EINVAL, "null facet data");
+    if (!sc && !has_hamaker) return fail(LG_EINVAL, "at least one surface force functor must be provided");
+    if ((int)s->facets.size() >= kMaxFacets) return fail(LG_ECAPACITY, "too many facets (max 8)");
+    Facet f{};
+    for (int k = 0; k < 3; k++) f.vtx[k] = mk3(vertices[3 * k], vertices[3 * k + 1], vertices[3 * k + 2]);
+    f.v = mk3(v_facet[0], v_facet[1], v_facet[2]);
+    facet_init_geometry(f);
+    f.has_contact = sc != nullptr;
+    f.has_hamaker = has_hamaker != 0;
+    if (sc) to_cp(sc, f.sp);
+    f.A = A;
+    f.h0 = h0;
+    auto ws = std::make_unique<DevBuf<double>>();
+    auto wa = std::make_unique<DevBuf<uint8_t>>();
+    LG_CUDA(ws->reserve((size_t)s->n * 9));
+    LG_CUDA(wa->reserve((size_t)s->n));
+    LG_CUDA(cudaMemsetAsync(ws->p, 0, (size_t)s->n * 9 * sizeof(double), s->stream));
+    LG_CUDA(cudaMemsetAsync(wa->p, 0, (size_t)s->n, s->stream));
+    s->facets.push_back(f);
+    s->wspr.push_back(std::move(ws));
+    s->wact.push_back(std::move(wa));
+    if (facet_id) *facet_id = (int)s->facets.size() - 1;
+    return LG_OK;
+}
+
+int lg_facet_set_velocity(lg_system* s, int id, const double v[3]) {
+    LG_ENTER(s);
+    if (id < 0 || id >= (int)s->facets.size() || !v) return fail(LG_EINVAL, "bad facet id");
+    s->facets[(size_t)id].v = mk3(v[0], v[1], v[2]);
+    return LG_OK;
+}
+
+int lg_facet_update_positions(lg_system* s, int id, double dt) {
+    LG_ENTER(s);
+    if (id < 0 || id >= (int)s->facets.size()) return fail(LG_EINVAL, "bad facet id");
+    Facet& f = s->facets[(size_t)id];
+    for (int k = 0; k < 3; k++) f.vtx[k] = f.vtx[k] + f.v * dt;  // triangular_facet.h:62-66
+    return LG_OK;
+}
+
+int lg_facet_get_vertices(lg_system* s, int id, double out[9]) {
+    LG_ENTER(s);
+    if (id < 0 || id >= (int)s->facets.size() || !out) return fail(LG_EINVAL, "bad facet id");
+    for (int k = 0; k < 3; k++) store3(out + 3 * k, s->facets[(size_t)id].vtx[k]);
+    return LG_OK;
+}
+
+int lg_enable_neighbor_list(lg_system* s, double r_verlet) {
+    LG_ENTER(s);
+    if (!(r_verlet > 0.0)) return fail(LG_EINVAL, "r_verlet must be positive");
+    s->use_nl = true;
+    s->r_verlet = r_verlet;
+    s->allpairs_built = false;
+    s->n_pairs = 0;
+    LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, ((size_t)s->n + 1) * sizeof(uint32_t), s->stream));
+    return LG_OK;
+}
+
+int lg_update_neighbor_list(lg_system* s) {
+    LG_ENTER(s);
+    return rebuild(s);
+}
+
+int lg_do_step(lg_system* s, double dt) {
+    LG_ENTER(s);
+    LG_TRY(prepare(s));
+    return step(s, dt);
+}
+
+int lg_run(lg_system* s, double dt, int64_t n_steps, int64_t rebuild_every, int move_facets) {
+    LG_ENTER(s);
+    LG_TRY(prepare(s));
+    for (int64_t k = 0; k < n_steps; k++) {
+        if (s->use_nl && rebuild_every > 0 && s->steps % rebuild_every == 0) LG_TRY(rebuild(s));
+        LG_TRY(step(s, dt));
+        if (move_facets)
+            for (auto& f : s->facets)
+                for (int q = 0; q < 3; q++) f.vtx[q] = f.vtx[q] + f.v * dt;
+    }
+    return LG_OK;
+}
+
+int lg_reset_acceleration_buffers(lg_system* s) {
+    LG_ENTER(s);
+    const size_t bytes = 3 * (size_t)s->n * sizeof(double);
+    LG_CUDA(cudaMemsetAsync(s->a.p, 0, bytes, s->stream));
+    LG_CUDA(cudaMemsetAsync(s->al.p, 0, bytes, s->stream));
+    return LG_OK;
+}
+
+int lg_synchronize(lg_system* s) {
+    LG_ENTER(s);
+    return check_async(s);
+}
+
+int lg_get_neighbor_count(lg_system* s, int64_t* n_pairs) {
+    LG_ENTER(s);
+    if (!n_pairs) return fail(LG_EINVAL, "null output");
+    if (!s->use_nl && !s->allpairs_built) {
+        *n_pairs = s->n * (s->n - 1);
+        return LG_OK;
+    }
+    *n_pairs = s->n_pairs;
+    return LG_OK;
+}
+
+int lg_get_neighbor_rows(lg_system* s, int64_t* row_ptr, int64_t* cols) {
+    LG_ENTER(s);
+    if (!row_ptr || !cols) return fail(LG_EINVAL, "null output");
+    if (!s->use_nl && !s->allpairs_built) {
+        LG_TRY(ensure_slots(s));
+        LG_TRY(build_allpairs(s));
+    }
+    const size_t n = (size_t)s->n, p = (size_t)s->n_pairs;
+    std::vector<uint32_t> hp(n + 1);
+    std::vector<int32_t> hc(p);
+    LG_CUDA(cudaMemcpyAsync(hp.data(), s->row_ptr.p, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
+    if (p) LG_CUDA(cudaMemcpyAsync(hc.data(), s->cols.p, p * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    for (size_t i = 0; i <= n; i++) row_ptr[i] = (int64_t)hp[i];
+    for (size_t k = 0; k < p; k++) cols[k] = (int64_t)hc[k];
+    return LG_OK;
+}
+
+int lg_get_contact_springs(lg_system* s, int64_t i, int64_t j, double out[9]) {
+    LG_ENTER(s);
+    if (!out || i < 0 || j < 0 || i >= s->n || j >= s->n) return fail(LG_EINVAL, "bad pair");
+    std::fill(out, out + 9, 0.0);
+    if (!s->slots_ready) return LG_OK;
+    std::vector<int32_t> ids((size_t)s->S);
+    LG_CUDA(cudaMemcpyAsync(ids.data(), s->sgid.p + (size_t)i * s->S, (size_t)s->S * sizeof(int32_t), cudaMemcpyDeviceToHost,
+                            s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    for (int q = 0; q < s->S; q++)
+        if (ids[(size_t)q] == (int32_t)j) {
+            LG_CUDA(cudaMemcpyAsync(out, s->spr.p + ((size_t)i * s->S + q) * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost,
+                                    s->stream));
+            LG_CUDA(cudaStreamSynchronize(s->stream));
+            break;
+        }
+    return LG_OK;
+}
+
+int lg_get_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double conn[15], double len[5]) {
+    LG_ENTER(s);
+    if (!bonded || !conn || !len || i < 0 || j < 0 || i >= s->n || j >= s->n) return fail(LG_EINVAL, "bad arguments");
+    *bonded = 0;
+    if (s->n_bonds == 0) return LG_OK;
+    for (uint32_t b = s->h_bptr[(size_t)i]; b < s->h_bptr[(size_t)i + 1]; b++)
+        if (s->h_bj[b] == (int32_t)j) {
+            LG_CUDA(cudaMemcpyAsync(conn, s->bconn.p + (size_t)b * 15, 15 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+            LG_CUDA(cudaMemcpyAsync(len, s->blen.p + (size_t)b * 5, 5 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+            LG_CUDA(cudaStreamSynchronize(s->stream));
+            *bonded = 1;
+            break;
+        }
+    return LG_OK;
+}
+
+int lg_get_counters(lg_system* s, int64_t out[8]) {
+    LG_ENTER(s);
+    if (!out) return fail(LG_EINVAL, "null output");
+    unsigned long long contacts = 0;
+    if (s->slots_ready) {
+        launch_count_slots((int)s->n, s->sgid.p, s->S, s->counter.p, s->stream);
+        LG_CUDA(cudaMemcpyAsync(&contacts, s->counter.p, sizeof(contacts), cudaMemcpyDeviceToHost, s->stream));
+        LG_CUDA(cudaStreamSynchronize(s->stream));
+    }
+    int64_t pairs = 0;
+    lg_get_neighbor_count(s, &pairs);
+    out[0] = pairs;
+    out[1] = (int64_t)contacts;
+    out[2] = s->n_bonds;
+    out[3] = s->steps;
+    out[4] = s->rebuilds;
+    out[5] = g_launch_count - s->launches0;
+    out[6] = s->last_cells;
+    out[7] = 0;
+    return LG_OK;
+}
+
+int lg_diagnostics(lg_system* s, double out[9]) {
+    LG_ENTER(s);
+    if (!out) return fail(LG_EINVAL, "null output");
+    if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
+    const int n = (int)s->n;
+    double* h = s->h_pinned;
+    launch_diag_sums(n, s->x.p, s->v.p, s->w.p, s->mp.mass, s->mp.inertia, nullptr, s->diag_partials.p, s->diag_out.p, 0,
+                     s->stream);
+    LG_CUDA(cudaMemcpyAsync(h, s->diag_out.p, 11 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    double com[3] = {h[8] / (double)n, h[9] / (double)n, h[10] / (double)n};
+    double sums[11];
+    std::memcpy(sums, h, sizeof(sums));
+    LG_CUDA(cudaMemcpyAsync(s->diag_out.p + 12, com, 3 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+    launch_diag_sums(n, s->x.p, s->v.p, s->w.p, s->mp.mass, s->mp.inertia, s->diag_out.p + 12, s->diag_partials.p,
+                     s->diag_out.p, 1, s->stream);
+    LG_CUDA(cudaMemcpyAsync(h, s->diag_out.p + 11, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    out[0] = sums[0] + sums[1];
+    out[1] = sums[0];
+    out[2] = sums[1];
+    out[3] = s->mp.mass * std::sqrt(sums[2] * sums[2] + sums[3] * sums[3] + sums[4] * sums[4]);
+    out[4] = std::sqrt(sums[5] * sums[5] + sums[6] * sums[6] + sums[7] * sums[7]);
+    out[5] = com[0];
+    out[6] = com[1];
+    out[7] = com[2];
+    out[8] = std::sqrt(h[0] / (double)n);
+    return LG_OK;
+}
+
+int lg_set_kernel_variant(lg_system* s, int variant) {
+    LG_ENTER(s);
+    if (variant != 0 && variant != 1) return fail(LG_EINVAL, "variant must be 0 or 1");
+    s->variant = variant;
+    return LG_OK;
+}
+
+}  // extern "C"

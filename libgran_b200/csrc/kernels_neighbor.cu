@@ -1,0 +1,446 @@
+// kernels_neighbor.cu -- cell-list rebuild of the neighbor rows (sm_100a).
+//
+// Replaces the O(N^2) update_neighbor_list() of
+// LT/rotational_system/rotational_binary_system_neighbors_omp.h:102-116:
+//     row(i) = { j != i : (x[i] - x[j]).norm() < r_verlet },  ascending j
+// by: bounding box -> cell index + histogram -> exclusive prefix scan -> counting-sort scatter ->
+// per-particle 27-cell sweep (count) -> scan -> sweep again (fill) -> per-row sort by particle id.
+// The cell grid is only a candidate filter (cell edge > r_verlet); membership is decided by the
+// reference's exact predicate: sqrt((dx*dx + dy*dy) + dz*dz) < r_verlet, FP64, no FMA contraction
+// (this file is compiled with --fmad=false), strict '<' -- so the pair set is bit-identical.
+#include "system.h"
+
+namespace lg {
+
+// ---- bounding box --------------------------------------------------------------------------------
+constexpr int kBboxThreads = 256;
+constexpr int kBboxMaxBlocks = 1024;
+
+__device__ __forceinline__ void warp_minmax(double* mn, double* mx) {
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            mn[k] = fmin(mn[k], __shfl_xor_sync(0xffffffffu, mn[k], off));
+            mx[k] = fmax(mx[k], __shfl_xor_sync(0xffffffffu, mx[k], off));
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kBboxThreads) bbox_partial_kernel(int n, const double* x, double* partial) {
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            const double c = x[3 * (size_t)i + k];
+            mn[k] = fmin(mn[k], c);
+            mx[k] = fmax(mx[k], c);
+        }
+    }
+    warp_minmax(mn, mx);
+    __shared__ double s[kBboxThreads / 32][6];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0)
+        for (int k = 0; k < 3; k++) {
+            s[warp][k] = mn[k];
+            s[warp][3 + k] = mx[k];
+        }
+    __syncthreads();
+    if (warp == 0) {
+        const bool have = lane < kBboxThreads / 32;
+        for (int k = 0; k < 3; k++) {
+            mn[k] = have ? s[lane][k] : 1e300;
+            mx[k] = have ? s[lane][3 + k] : -1e300;
+        }
+        warp_minmax(mn, mx);
+        if (lane == 0)
+            for (int k = 0; k < 3; k++) {
+                partial[blockIdx.x * 6 + k] = mn[k];
+                partial[blockIdx.x * 6 + 3 + k] = mx[k];
+            }
+    }
+}
+
+__global__ void __launch_bounds__(kBboxThreads) bbox_final_kernel(int n_partial, const double* partial, double* out) {
+    double mn[3] = {1e300, 1e300, 1e300}, mx[3] = {-1e300, -1e300, -1e300};
+    for (int b = threadIdx.x; b < n_partial; b += blockDim.x)
+        for (int k = 0; k < 3; k++) {
+            mn[k] = fmin(mn[k], partial[b * 6 + k]);
+            mx[k] = fmax(mx[k], partial[b * 6 + 3 + k]);
+        }
+    warp_minmax(mn, mx);
+    __shared__ double s[kBboxThreads / 32][6];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0)
+        for (int k = 0; k < 3; k++) {
+            s[warp][k] = mn[k];
+            s[warp][3 + k] = mx[k];
+        }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int wv = 1; wv < kBboxThreads / 32; wv++)
+            for (int k = 0; k < 3; k++) {
+                s[0][k] = fmin(s[0][k], s[wv][k]);
+                s[0][3 + k] = fmax(s[0][3 + k], s[wv][3 + k]);
+            }
+        for (int k = 0; k < 6; k++) out[k] = s[0][k];
+    }
+}
+
+// d_scratch: 6 * kBboxMaxBlocks doubles
+void launch_bbox(int n, const double* x, double* d_scratch, double* d_out, cudaStream_t st) {
+    int blocks = (n + kBboxThreads - 1) / kBboxThreads;
+    if (blocks > kBboxMaxBlocks) blocks = kBboxMaxBlocks;
+    if (blocks < 1) blocks = 1;
+    bbox_partial_kernel<<<blocks, kBboxThreads, 0, st>>>(n, x, d_scratch);
+    bbox_final_kernel<<<1, kBboxThreads, 0, st>>>(blocks, d_scratch, d_out);
+    g_launch_count += 2;
+}
+
+// ---- exclusive prefix scan of u32 (three-phase, hand-written) ----------------------------------------
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kScanThreads * kScanItems;  // 2048 elements per block
+
+__device__ __forceinline__ uint32_t block_exclusive_scan(uint32_t v, uint32_t* total) {
+    __shared__ uint32_t warp_sums[kScanThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t incl = v;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += t;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t ws = (lane < kScanThreads / 32) ? warp_sums[lane] : 0u;
+        uint32_t wincl = ws;
+#pragma unroll
+        for (int off = 1; off < 32; off <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, wincl, off);
+            if (lane >= off) wincl += t;
+        }
+        if (lane < kScanThreads / 32) warp_sums[lane] = wincl - ws;  // exclusive offsets of the warps
+        if (lane == kScanThreads / 32 - 1) *total = wincl;
+    }
+    __syncthreads();
+    const uint32_t res = warp_sums[warp] + (incl - v);
+    __syncthreads();
+    return res;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_tile_kernel(uint32_t* data, size_t n, uint32_t* tile_sums) {
+    __shared__ uint32_t total;
+    const size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
+    uint32_t item[kScanItems];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) {
+        item[k] = (base + k < n) ? data[base + k] : 0u;
+        sum += item[k];
+    }
+    uint32_t run = block_exclusive_scan(sum, &total);
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++) {
+        if (base + k < n) data[base + k] = run;
+        run += item[k];
+    }
+    if (threadIdx.x == 0 && tile_sums != nullptr) tile_sums[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(kScanThreads) scan_add_kernel(uint32_t* data, size_t n, const uint32_t* tile_offsets) {
+    const uint32_t off = tile_offsets[blockIdx.x];
+    const size_t base = (size_t)blockIdx.x * kScanTile + (size_t)threadIdx.x * kScanItems;
+#pragma unroll
+    for (int k = 0; k < kScanItems; k++)
+        if (base + k < n) data[base + k] += off;
+}
+
+size_t scan_scratch_elems(size_t n) {
+    size_t total = 0;
+    while (n > (size_t)kScanTile) {
+        n = (n + kScanTile - 1) / kScanTile;
+        total += n;
+    }
+    return total + 1;
+}
+
+void launch_exclusive_scan_u32(uint32_t* data, size_t n, uint32_t* scratch, cudaStream_t st) {
+    if (n == 0) return;
+    const size_t tiles = (n + kScanTile - 1) / kScanTile;
+    if (tiles == 1) {
+        scan_tile_kernel<<<1, kScanThreads, 0, st>>>(data, n, nullptr);
+        g_launch_count++;
+        return;
+    }
+    scan_tile_kernel<<<(unsigned)tiles, kScanThreads, 0, st>>>(data, n, scratch);
+    launch_exclusive_scan_u32(scratch, tiles, scratch + tiles, st);
+    scan_add_kernel<<<(unsigned)tiles, kScanThreads, 0, st>>>(data, n, scratch);
+    g_launch_count += 2;
+}
+
+// ---- cell list -------------------------------------------------------------------------------------
+__device__ __forceinline__ void cell_coords(const NeighborGrid& g, d3 p, int c[3]) {
+    const double q[3] = {(p.x - g.lo[0]) / g.cell, (p.y - g.lo[1]) / g.cell, (p.z - g.lo[2]) / g.cell};
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        int t = (int)floor(q[k]);
+        t = t < 0 ? 0 : t;
+        c[k] = t >= g.dim[k] ? g.dim[k] - 1 : t;
+    }
+}
+__device__ __forceinline__ int cell_linear(const NeighborGrid& g, int cx, int cy, int cz) {
+    return (cx * g.dim[1] + cy) * g.dim[2] + cz;
+}
+
+__global__ void __launch_bounds__(256)
+    cell_count_kernel(int n, const double* x, const NeighborGrid g, int32_t* cell_of, uint32_t* cell_count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int c[3];
+    cell_coords(g, load3(x + 3 * (size_t)i), c);
+    const int cl = cell_linear(g, c[0], c[1], c[2]);
+    cell_of[i] = cl;
+    atomicAdd(&cell_count[cl], 1u);  // integer histogram: the result does not depend on arrival order
+}
+
+__global__ void __launch_bounds__(256) cell_fill_kernel(int n, const int32_t* cell_of, const uint32_t* cell_start,
+                                                        uint32_t* cell_cursor, int32_t* order) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int cl = cell_of[i];
+    const uint32_t pos = atomicAdd(&cell_cursor[cl], 1u);
+    order[cell_start[cl] + pos] = i;  // order inside a cell is arbitrary; rows are sorted by id afterwards
+}
+
+void launch_cell_count(int n, const double* x, NeighborGrid g, int32_t* cell_of, uint32_t* cell_count, cudaStream_t st) {
+    cell_count_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, x, g, cell_of, cell_count);
+    g_launch_count++;
+}
+void launch_cell_fill(int n, const int32_t* cell_of, const uint32_t* cell_start, uint32_t* cell_cursor, int32_t* order,
+                      cudaStream_t st) {
+    cell_fill_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, cell_of, cell_start, cell_cursor, order);
+    g_launch_count++;
+}
+
+// The reference predicate, term order as Eigen evaluates (x[i] - x[j]).norm().
+__device__ __forceinline__ bool within_verlet(d3 xi, d3 xj, double r_verlet) {
+    const d3 d = xi - xj;
+    return sqrt((d.x * d.x + d.y * d.y) + d.z * d.z) < r_verlet;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(128)
+    row_sweep_kernel(int n, const double* x, const NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
+                     double r_verlet, uint32_t* row_count, const uint32_t* row_ptr, int32_t* cols) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const d3 xi = load3(x + 3 * (size_t)i);
+    int c[3];
+    cell_coords(g, xi, c);
+    uint32_t cnt = 0;
+    const uint32_t base = FILL ? row_ptr[i] : 0u;
+    for (int dx = -1; dx <= 1; dx++) {
+        const int cx = c[0] + dx;
+        if (cx < 0 || cx >= g.dim[0]) continue;
+        for (int dy = -1; dy <= 1; dy++) {
+            const int cy = c[1] + dy;
+            if (cy < 0 || cy >= g.dim[1]) continue;
+            // the three z-neighbours are contiguous in the cell order: one range
+            const int z0 = max(c[2] - 1, 0), z1 = min(c[2] + 1, g.dim[2] - 1);
+            const uint32_t s0 = cell_start[cell_linear(g, cx, cy, z0)];
+            const uint32_t s1 = cell_start[cell_linear(g, cx, cy, z1) + 1];
+            for (uint32_t s = s0; s < s1; s++) {
+                const int j = order[s];
+                if (j == i) continue;
+                if (within_verlet(xi, load3(x + 3 * (size_t)j), r_verlet)) {
+                    if (FILL) cols[base + cnt] = j;
+                    cnt++;
+                }
+            }
+        }
+    }
+    if (!FILL) {
+        row_count[i] = cnt;
+    } else {
+        // insertion sort of the row by particle id (rows are short; done once per rebuild)
+        int32_t* row = cols + base;
+        for (uint32_t a = 1; a < cnt; a++) {
+            const int32_t key = row[a];
+            int b = (int)a - 1;
+            while (b >= 0 && row[b] > key) {
+                row[b + 1] = row[b];
+                b--;
+            }
+            row[b + 1] = key;
+        }
+    }
+}
+
+void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
+                      double r_verlet, uint32_t* row_count, cudaStream_t st) {
+    row_sweep_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, row_count, nullptr,
+                                                             nullptr);
+    g_launch_count++;
+}
+void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
+                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, cudaStream_t st) {
+    row_sweep_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, nullptr, row_ptr, cols);
+    g_launch_count++;
+}
+
+// all-pairs loop (rotational_binary_system_omp.h:72-75): row(i) = every j != i, ascending
+__global__ void __launch_bounds__(256) allpairs_fill_kernel(int n, uint32_t* row_ptr, int32_t* cols) {
+    const int i = blockIdx.x;
+    const uint32_t base = (uint32_t)i * (uint32_t)(n - 1);
+    if (threadIdx.x == 0) {
+        row_ptr[i] = base;
+        if (i == n - 1) row_ptr[n] = (uint32_t)n * (uint32_t)(n - 1);
+    }
+    for (int j = threadIdx.x; j < n; j += blockDim.x)
+        if (j != i) cols[base + (uint32_t)(j < i ? j : j - 1)] = j;
+}
+void launch_allpairs_fill(int n, uint32_t* row_ptr, int32_t* cols, cudaStream_t st) {
+    allpairs_fill_kernel<<<n, 256, 0, st>>>(n, row_ptr, cols);
+    g_launch_count++;
+}
+
+// ---- tags: where does the history of pair p live? ----------------------------------------------------
+// Carries the sparse contact-spring records across a rebuild: a record keyed by partner id survives if the
+// partner is still in the row; otherwise it is dropped (the reference would have reset it on the last
+// visited non-overlapping evaluation before the pair left the list).
+__global__ void __launch_bounds__(128)
+    retag_kernel(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
+                 const uint32_t* bptr, const int32_t* bj, int* err) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t p0 = row_ptr[i], p1 = row_ptr[i + 1];
+    for (uint32_t p = p0; p < p1; p++) tag[p] = (uint8_t)kTagNone;
+    if (sgid != nullptr) {
+        for (int q = 0; q < S; q++) {
+            const int32_t partner = sgid[(size_t)i * S + q];
+            if (partner < 0) continue;
+            // binary search of partner in the sorted row
+            uint32_t lo = p0, hi = p1;
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (cols[mid] < partner) lo = mid + 1; else hi = mid;
+            }
+            if (lo < p1 && cols[lo] == partner)
+                tag[lo] = (uint8_t)q;
+            else
+                sgid[(size_t)i * S + q] = -1;
+        }
+    }
+    if (bptr != nullptr) {
+        const uint32_t b0 = bptr[i], b1 = bptr[i + 1];
+        for (uint32_t b = b0; b < b1; b++) {
+            const int32_t partner = bj[b];
+            uint32_t lo = p0, hi = p1;
+            while (lo < hi) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (cols[mid] < partner) lo = mid + 1; else hi = mid;
+            }
+            if (lo < p1 && cols[lo] == partner) {
+                if (tag[lo] != kTagNone) {  // a bonded pair must never own a contact slot
+                    sgid[(size_t)i * S + tag[lo]] = -1;
+                }
+                tag[lo] = (uint8_t)(kTagBond + (b - b0));
+            }
+            // a bonded partner outside the row is simply not visited, as in the reference
+        }
+    }
+    (void)spr;
+    (void)err;
+}
+
+void launch_retag(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
+                  const uint32_t* bptr, const int32_t* bj, int* err, cudaStream_t st) {
+    if (n <= 0) return;
+    retag_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, row_ptr, cols, tag, sgid, spr, S, bptr, bj, err);
+    g_launch_count++;
+}
+
+__global__ void __launch_bounds__(256) count_slots_kernel(size_t total, const int32_t* sgid, unsigned long long* out) {
+    unsigned long long c = 0;
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < total; k += (size_t)gridDim.x * blockDim.x)
+        c += sgid[k] >= 0 ? 1ull : 0ull;
+    for (int off = 16; off > 0; off >>= 1) c += __shfl_xor_sync(0xffffffffu, c, off);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);
+}
+void launch_count_slots(int n, const int32_t* sgid, int S, unsigned long long* d_out, cudaStream_t st) {
+    cudaMemsetAsync(d_out, 0, sizeof(unsigned long long), st);
+    if (n <= 0 || sgid == nullptr) return;
+    const size_t total = (size_t)n * S;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 2048) blocks = 2048;
+    count_slots_kernel<<<blocks, 256, 0, st>>>(total, sgid, d_out);
+    g_launch_count++;
+}
+
+// ---- diagnostics (test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26) --------------------
+// pass 0 sums: [0] m v.v/2  [1] I w.w/2  [2..4] sum v  [5..7] sum I w + x cross m v  [8..10] sum x
+// pass 1 sums: [11] sum |x - com|^2
+constexpr int kDiagThreads = 256;
+constexpr int kDiagMaxBlocks = 512;
+constexpr int kDiagSlots = 12;
+
+__global__ void __launch_bounds__(kDiagThreads)
+    diag_partial_kernel(int n, const double* x, const double* v, const double* w, double mass, double inertia,
+                        const double* com, double* partial, int pass) {
+    double s[kDiagSlots];
+#pragma unroll
+    for (int k = 0; k < kDiagSlots; k++) s[k] = 0.0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const d3 xi = load3(x + 3 * (size_t)i);
+        if (pass == 0) {
+            const d3 vi = load3(v + 3 * (size_t)i), wi = load3(w + 3 * (size_t)i);
+            s[0] += mass * dot(vi, vi) / 2.0;
+            s[1] += inertia * dot(wi, wi) / 2.0;
+            s[2] += vi.x; s[3] += vi.y; s[4] += vi.z;
+            const d3 l = inertia * wi + cross(xi, mass * vi);
+            s[5] += l.x; s[6] += l.y; s[7] += l.z;
+            s[8] += xi.x; s[9] += xi.y; s[10] += xi.z;
+        } else {
+            const d3 d = xi - mk3(com[0], com[1], com[2]);
+            s[11] += dot(d, d);
+        }
+    }
+    __shared__ double sh[kDiagThreads / 32][kDiagSlots];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < kDiagSlots; k++) {
+        double t = s[k];
+        for (int off = 16; off > 0; off >>= 1) t += __shfl_xor_sync(0xffffffffu, t, off);
+        if (lane == 0) sh[warp][k] = t;
+    }
+    __syncthreads();
+    if (threadIdx.x < kDiagSlots) {
+        double t = 0.0;
+        for (int wv = 0; wv < kDiagThreads / 32; wv++) t += sh[wv][threadIdx.x];
+        partial[blockIdx.x * kDiagSlots + threadIdx.x] = t;
+    }
+}
+
+__global__ void diag_final_kernel(int n_partial, const double* partial, double* out, int pass) {
+    const int k = threadIdx.x;
+    if (k >= kDiagSlots) return;
+    if ((pass == 0) != (k < 11)) return;
+    double t = 0.0;
+    for (int b = 0; b < n_partial; b++) t += partial[b * kDiagSlots + k];  // fixed order: deterministic
+    out[k] = t;
+}
+
+// d_partials: kDiagSlots * kDiagMaxBlocks doubles; d_out: 16 doubles
+void launch_diag_sums(int n, const double* x, const double* v, const double* w, double mass, double inertia,
+                      const double* com, double* d_partials, double* d_out, int pass, cudaStream_t st) {
+    int blocks = (n + kDiagThreads - 1) / kDiagThreads;
+    if (blocks > kDiagMaxBlocks) blocks = kDiagMaxBlocks;
+    if (blocks < 1) blocks = 1;
+    diag_partial_kernel<<<blocks, kDiagThreads, 0, st>>>(n, x, v, w, mass, inertia, com, d_partials, pass);
+    diag_final_kernel<<<1, 32, 0, st>>>(blocks, d_partials, d_out, pass);
+    g_launch_count += 2;
+}
+
+}  // namespace lg

@@ -1,0 +1,126 @@
+// system.h -- device-resident state of one granular system and the kernel launchers that act on it.
+//
+// Layout in HBM (all FP64 unless noted; n particles, P ordered neighbor pairs, S contact slots per
+// particle, Bd ordered bonds, F facets):
+//   x, v, a, theta, omega, alpha   3n doubles each, xyz-interleaved, caller's particle order
+//                                  (replaces the six std::vector<Eigen::Vector3d> of
+//                                  LT/rotational_system/rotational_system.h:128)
+//   row_ptr  u32[n+1], cols i32[P], tag u8[P]
+//                                  CSR neighbor rows, ascending j (replaces vector<vector<long>>,
+//                                  rotational_binary_system_neighbors_omp.h:122); tag[p] says where the
+//                                  pair's history lives: 0..S-1 contact slot, 128+k the k-th bond of i,
+//                                  255 nothing
+//   spr      9 doubles [n][S], sgid i32[n][S]
+//                                  sparse per-ORDERED-pair contact springs owned by i (replaces the dense
+//                                  N x N tuple store of contact_force.h:53,156); sgid = partner id or -1
+//   bptr u32[n+1], bj i32[Bd], brev i32[Bd], bconn 15 doubles [Bd], blen 5 doubles [Bd]
+//                                  bond CSR (replaces the dense tables of sinter_bridge.h:139-141 and the
+//                                  particle_to_connector_map :138)
+//   wspr 9 doubles [F][n], wact u8[F][n]
+//                                  wall springs per facet (surface_contact_force.h:53) + "may be non-zero" flag
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "physics.cuh"
+
+namespace lg {
+
+constexpr int kMaxFacets = 8;
+constexpr int kTagNone = 255;
+constexpr int kTagBond = 128;
+constexpr int kMaxBondsPerParticle = 120;
+constexpr int kMaxSlots = 120;
+
+// asynchronous error flags raised by kernels (checked at synchronisation points)
+enum : int { ERR_SLOT_OVERFLOW = 1, ERR_BOND_LOOKUP = 2 };
+
+struct ModelParams {
+    double r, mass, inertia;
+    ContactParams cp;
+    double hamaker_A, hamaker_h0;
+    double k_d, gamma_d;
+};
+
+struct ForceArgs {
+    int n;
+    const double* x;
+    const double* v;
+    const double* w;
+    double* a;
+    double* al;
+    const uint32_t* row_ptr;
+    const int32_t* cols;
+    uint8_t* tag;
+    double* spr;
+    int32_t* sgid;
+    int S;
+    const uint32_t* bptr;
+    const int32_t* bj;
+    const int32_t* brev;
+    const double* bconn;
+    const double* blen;
+    ModelParams mp;
+    int n_facets;
+    Facet facets[kMaxFacets];
+    double* wspr[kMaxFacets];
+    uint8_t* wact[kMaxFacets];
+    int* err;
+};
+
+struct IntegrateArgs {
+    int n;
+    double* x;
+    double* v;
+    double* th;
+    double* w;
+    const double* a;
+    const double* al;
+    const uint32_t* bptr;  // null when there are no bonds
+    double* bconn;
+    double dt;
+};
+
+struct NeighborGrid {
+    double lo[3];
+    double cell;
+    int dim[3];
+    int64_t n_cells;
+};
+
+// number of kernels launched by this thread (lg_get_counters[5]); bumped by every launcher
+extern thread_local int64_t g_launch_count;
+
+// ---- launchers (kernels_*.cu) ---------------------------------------------------------------------
+void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st);
+void launch_integrate(const IntegrateArgs& args, cudaStream_t st);
+void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, cudaStream_t st);
+
+// bounding box of x -> d_out[6] = {min xyz, max xyz}
+void launch_bbox(int n, const double* x, double* d_scratch, double* d_out, cudaStream_t st);
+// exclusive prefix sum of u32 (in place allowed); scratch must hold scan_scratch_elems(n) u32
+size_t scan_scratch_elems(size_t n);
+void launch_exclusive_scan_u32(uint32_t* data, size_t n, uint32_t* scratch, cudaStream_t st);
+
+void launch_cell_count(int n, const double* x, NeighborGrid g, int32_t* cell_of, uint32_t* cell_count, cudaStream_t st);
+void launch_cell_fill(int n, const int32_t* cell_of, const uint32_t* cell_start, uint32_t* cell_cursor, int32_t* order,
+                      cudaStream_t st);
+void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
+                      double r_verlet, uint32_t* row_count, cudaStream_t st);
+void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
+                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, cudaStream_t st);
+void launch_allpairs_fill(int n, uint32_t* row_ptr, int32_t* cols, cudaStream_t st);
+// recompute tag[] for every row from the slot table and the bond CSR; frees slots whose partner left the row
+void launch_retag(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
+                  const uint32_t* bptr, const int32_t* bj, int* err, cudaStream_t st);
+
+void launch_count_slots(int n, const int32_t* sgid, int S, unsigned long long* d_out, cudaStream_t st);
+// out[16]: sums for lg_diagnostics (pass 0) ; pass 1 adds sum |x - com|^2
+void launch_diag_sums(int n, const double* x, const double* v, const double* w, double mass, double inertia,
+                      const double* com, double* d_partials, double* d_out, int pass, cudaStream_t st);
+
+}  // namespace lg

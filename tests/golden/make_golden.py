@@ -71,6 +71,17 @@ def main():
         "aggregate_sinter_hamaker": (S.aggregate(), [1, 2, 500, 1000]),
         "surface_drop": (S.surface_drop(), [1, 2, 40000, 60000]),
     }
+    # branch-coverage inputs (contacts forming / sliding / separating, facet plane + edge + vertex, moving facet)
+    stress = {
+        "stress_contact_hamaker_facet": S.stress_block(models=S.MODEL_CONTACT | S.MODEL_HAMAKER | S.MODEL_FACET),
+        "stress_sinter_hamaker_facet": S.stress_block(models=S.MODEL_SINTER | S.MODEL_HAMAKER | S.MODEL_FACET),
+        "stress_sinter_allpairs": S.stress_block(nx=4, ny=4, nz=3, models=S.MODEL_SINTER, neighbor_list=False),
+    }
+    for name, scn in stress.items():
+        out = run_reference(scn, [1, 2, 50, 200], facet_every_step=True)
+        out["x0"], out["v0"], out["omega0"] = scn.x0, scn.v0, scn.omega0
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+        print(name, "ok")
     for name, (scn, cps) in cases.items():
         out = run_reference(scn, cps)
         out["x0"], out["v0"] = scn.x0, scn.v0
