@@ -3,6 +3,9 @@ import sys
 
 import pytest
 
+# the CPU checkers use OpenMP; on over-committed vCPUs a spinning barrier is pathologically slow
+os.environ.setdefault("OMP_WAIT_POLICY", "passive")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
