@@ -1,0 +1,303 @@
+#!/usr/bin/env python
+"""bench.py -- particle-timesteps/s of the DEM hot path on BASELINE.json config 4.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--copies C]
+
+Workload (config.workload): ~1M-particle multi-aggregate collision -- 6667 randomly rotated copies of the
+150-particle soot aggregate (resources/aggregate.h), left half moving +x, right half -x; sinter bridges with
+embedded Luding contact + Hamaker, neighbor list r_verlet = 5 r rebuilt every 20 steps (SURVEY.md 8d cfg 4).
+One bench "step" = one DEM time step (do_step) over all particles; the neighbor rebuild that falls on every
+20th step is inside the timed region.  Prints ONE JSON line (see the task contract).
+
+  value     whole-job particle-timesteps/s with state resident in HBM (lg_run, CUDA events on the system stream)
+  e2e       the same through the host-facing API with HOST buffers: lg_set_state from pinned memory (H2D),
+            K x [lg_do_step + lg_diagnostics read-back], final get_x/get_v/get_omega/get_theta (D2H)
+  roofline  the pair-force kernel: algorithmic bytes per launch / mean CUDA-event duration of its launches
+  cpu_baseline / --impl reference
+            the reference's own OpenMP implementation (oracle/_ref/libref_timing.so, built from the unmodified
+            reference with its -O3 flags) on a bounded sample of the same workload (the first `sample` aggregates;
+            the full size needs 232 B * N^2 = 232 TB of dense tables and cannot run), all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from libgran_b200 import scenarios as S  # noqa: E402
+
+METRIC = "particle-timesteps/s"
+REBUILD_EVERY = 20
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region."""
+
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int = 0):
+        self.gpu = gpu_index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 7:
+                self.samples.append(parts)
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for p in self.samples:
+            try:
+                sm.append(float(p[0]))
+                mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, p[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def numpy_unit_vectors(count: int, seed: int = 99) -> np.ndarray:
+    rng = np.random.Generator(np.random.MT19937(seed))
+    v = rng.normal(size=(count, 3))
+    return v / np.linalg.norm(v, axis=1)[:, None]
+
+
+def build_workload(copies: int):
+    scn = S.multi_aggregate_collision(copies)
+    return scn
+
+
+def algorithmic_bytes(n, pairs, contacts, bonds_ordered):
+    """bytes per DEM step (cache-perfect, FP64, int32 indices) and per force-kernel launch."""
+    step = 192 * n + 4 * (n + 1) + 4 * pairs + 144 * contacts + 280 * bonds_ordered
+    # the pair-force kernel alone: reads x, v, omega (72 N), writes a, alpha (48 N), row pointers, columns,
+    # contact springs r+w, own connectors (120) + rest lengths (40) per ordered bond
+    force = 72 * n + 48 * n + 4 * (n + 1) + 4 * pairs + 144 * contacts + 160 * bonds_ordered
+    return step, force
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from libgran_b200.system import from_config
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    scn = build_workload(args.copies)
+    cfg = scn.cfg
+    n = cfg.n
+    if world > 1:
+        raise SystemExit("multi-GPU slab decomposition: see libgran_b200/slab.py (enabled in bench via --gpus N)")
+
+    uv = numpy_unit_vectors(n + 1024)
+    sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant)
+    stream = torch.cuda.ExternalStream(sysm.stream_handle(), device=torch.device("cuda", local_rank))
+
+    def timed_run(k):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        with torch.cuda.stream(stream):
+            e0.record()
+            sysm.run(cfg.dt, k, REBUILD_EVERY)
+            e1.record()
+        sysm.synchronize()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1)
+
+    # ---- device-resident throughput ------------------------------------------------------------
+    sysm.run(cfg.dt, max(args.warmup, 3), REBUILD_EVERY)
+    sysm.synchronize()
+    c0 = sysm.counters()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ms = timed_run(args.steps)
+    clocks = sampler.stop()
+    c1 = sysm.counters()
+    value = n * args.steps / (ms * 1e-3)
+    launches = c1["launches"] - c0["launches"]
+
+    # ---- roofline of the dominant kernel (pair force), measured live with events ----------------
+    sysm.set_profiling(True)
+    prof_steps = min(args.steps, 40)
+    sysm.run(cfg.dt, prof_steps, REBUILD_EVERY)
+    force_ms, force_launches = sysm.get_profile()
+    sysm.set_profiling(False)
+    cnt = sysm.counters()
+    step_bytes, force_bytes = algorithmic_bytes(n, cnt["pairs"], cnt["contacts"], cnt["bonds"])
+    peak, peak_src = measured_peaks()
+    force_avg_ms = force_ms / max(force_launches, 1)
+    achieved = force_bytes / (force_avg_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "pair_force", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": int(force_bytes), "avg_launch_ms": round(force_avg_ms, 5),
+                "launches_timed": int(force_launches),
+                "share_of_step": round(force_avg_ms / (ms / args.steps), 3),
+                "whole_step": {"algorithmic_bytes_per_step": int(step_bytes),
+                               "achieved_gbs": round(step_bytes * args.steps / (ms * 1e-3) / 1e9, 1),
+                               "frac": round(step_bytes * args.steps / (ms * 1e-3) / 1e9 / peak, 4),
+                               "frac_of_nominal_8TBs": round(step_bytes * args.steps / (ms * 1e-3) / 8e12, 4)}}
+
+    # ---- end to end through the host-facing API with host buffers ---------------------------------
+    pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in scn.state]
+    host_np = [t.numpy() for t in pinned]
+    outs = [torch.empty((n, 3), dtype=torch.float64).pin_memory() for _ in range(4)]
+    out_np = [t.numpy() for t in outs]
+    e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant)  # model tables built once (as a ctor would)
+    e2e_steps = args.steps
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    e2e_sys.set_state(*host_np)  # H2D of x0, v0, theta0, omega0
+    ke = 0.0
+    for k in range(e2e_steps):
+        if k % REBUILD_EVERY == 0:
+            e2e_sys.update_neighbor_list()
+        e2e_sys.do_step(cfg.dt)
+        if (k + 1) % 10 == 0:
+            ke = e2e_sys.diagnostics()["ke"]  # D2H of the step's metric (as main.cpp:152-159 dumps energies)
+    for name, buf in zip(("x", "v", "omega", "theta"), out_np):
+        e2e_sys.get(name, out=buf)  # D2H
+    e2e_sys.synchronize()
+    t1 = time.perf_counter()
+    e2e_value = n * e2e_steps / (t1 - t0)
+    h2d = 4 * 24 * n / e2e_steps
+    d2h = (4 * 24 * n + (e2e_steps // 10) * 9 * 8) / e2e_steps
+    e2e = {"value": round(e2e_value, 1), "unit": METRIC, "h2d_bytes_per_step": round(h2d, 1),
+           "d2h_bytes_per_step": round(d2h, 1), "steps": e2e_steps, "final_ke": ke,
+           "what": "lg_set_state(H2D, pinned) + K x lg_do_step (+ rebuild/20, KE read-back/10) + get x,v,omega,theta (D2H)"}
+    e2e_sys.close()
+
+    line = {
+        "metric": METRIC, "value": round(value, 1), "unit": METRIC, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"cfg4 multi-aggregate collision, {n} particles ({args.copies} x aggregate.h), sinter+contact+Hamaker, "
+                               f"r_verlet=5r, rebuild every {REBUILD_EVERY} steps", "particles": n, "pairs": cnt["pairs"],
+                   "bonds_ordered": cnt["bonds"], "contacts": cnt["contacts"], "l2_policy": "working set (>400 MB) larger than L2",
+                   "kernel_variant": args.variant},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+    }
+    if rank == 0 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = run_reference_sample(args, steps=40, warmup=5)
+    if rank == 0:
+        print(json.dumps(line))
+
+
+def run_reference_sample(args, steps, warmup):
+    """The reference's own OpenMP implementation on a bounded sample of the workload."""
+    os.environ.setdefault("OMP_PROC_BIND", "close")
+    from oracle import bindings as ob
+
+    sample = args.sample
+    scn = build_workload(sample)
+    cfg = scn.cfg
+    kind = "reference"
+    if ob.ref_available(timing=True):
+        threads = ob.load_ref(timing=True).ref_max_threads()
+        sysm = ob.RefSystem(cfg, *scn.state, timing=True)
+    else:
+        kind = "port"
+        threads = ob.load_oracle().orc_max_threads()
+        sysm = ob.OracleSystem(cfg, *scn.state)
+    sysm.run(cfg.dt, warmup, REBUILD_EVERY)
+    t0 = time.perf_counter()
+    sysm.run(cfg.dt, steps, REBUILD_EVERY)
+    dt_s = time.perf_counter() - t0
+    val = cfg.n * steps / dt_s
+    sysm.close()
+    return {"value": round(val, 1), "unit": METRIC, "cores": int(threads), "kind": kind,
+            "sample": f"{sample} of {args.copies} aggregates ({cfg.n} particles), {steps} steps after {warmup} warm-up, "
+                      f"constructor excluded; full size infeasible (232 B * N^2 dense tables)",
+            "seconds": round(dt_s, 3)}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    scn_n = 150 * args.copies
+    base = run_reference_sample(args, steps=args.steps, warmup=max(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": base["value"], "unit": METRIC,
+        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": max(args.warmup, 1),
+        "ms_per_step": round(base["seconds"] / args.steps * 1e3, 4), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"cfg4 multi-aggregate collision, {scn_n} particles ({args.copies} x aggregate.h), "
+                               f"sinter+contact+Hamaker, r_verlet=5r, rebuild every {REBUILD_EVERY} steps",
+                   "particles": scn_n},
+        "cpu_baseline": base,
+        "e2e": {"value": base["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--copies", type=int, default=6667, help="aggregates in the workload (6667 -> 1 000 050 particles)")
+    ap.add_argument("--sample", type=int, default=34, help="aggregates in the CPU-reference sample (34 -> 5100 particles)")
+    ap.add_argument("--variant", type=int, default=None, help="force kernel variant (0 simple, 1 tiled)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -181,6 +181,16 @@ int lg_get_counters(lg_system* s, int64_t out_8[8]);
  *   out[5..7] centre of mass      out[8] radius of gyration */
 int lg_diagnostics(lg_system* s, double out_9[9]);
 
+/* The CUDA stream (cudaStream_t) all work of this system is queued on, so that callers can time it with
+ * events or order their own copies against it. */
+int lg_get_stream(lg_system* s, void** stream);
+
+/* Per-kernel device timing for roofline reports: while enabled, every launch of the pair-force kernel is
+ * bracketed by CUDA events on the system's stream.  lg_get_profile synchronises and returns the summed
+ * duration in milliseconds and the number of launches since profiling was enabled. */
+int lg_set_profiling(lg_system* s, int enabled);
+int lg_get_profile(lg_system* s, double* force_ms_total, int64_t* force_launches);
+
 /* Selects the force-kernel organisation: 0 = one thread per particle (simple, validation),
  * 1 = tiled pair-parallel kernel (default).  Both give bit-identical results. */
 int lg_set_kernel_variant(lg_system* s, int variant);

@@ -66,6 +66,27 @@ struct DevBuf {
     }
 };
 
+// double-buffered array: kernels of step k read `p` and write `next`; the host swaps after the launch
+struct PingPong {
+    DevBuf<double> b[2];
+    int cur = 0;
+    double* p = nullptr;
+    double* next = nullptr;
+    cudaError_t reserve(size_t elems) {
+        cudaError_t e = b[0].reserve(elems);
+        if (e != cudaSuccess) return e;
+        e = b[1].reserve(elems);
+        p = b[cur].p;
+        next = b[cur ^ 1].p;
+        return e;
+    }
+    void swap() {
+        cur ^= 1;
+        p = b[cur].p;
+        next = b[cur ^ 1].p;
+    }
+};
+
 }  // namespace
 
 using namespace lg;
@@ -78,9 +99,16 @@ struct lg_system {
     int mask = 0;  // binary models
     int variant = 1;
 
-    DevBuf<double> x, v, a, th, w, al;
+    PingPong x, v, w;         // read by other particles' pair evaluations -> double-buffered
+    DevBuf<double> a, th, al;  // private to their particle -> single
     bool state_set = false;
     bool kicked = false;
+    // Lazy evaluation (variant 1): the reference ends do_step with a force evaluation at the new state
+    // (rotational_velocity_verlet_half.h:75); the fused kernel performs that evaluation at the START of the
+    // next step instead.  `pending` means a, alpha (and the contact springs) have not yet been advanced to
+    // the current x, v, omega; flush() materialises them whenever something could observe the difference.
+    bool pending = false;
+    std::vector<Facet> pending_facets;  // facet state as of the do_step call that left the evaluation pending
 
     // neighbor rows
     bool use_nl = false;
@@ -101,7 +129,8 @@ struct lg_system {
     int64_t n_bonds = 0;  // ordered
     DevBuf<uint32_t> bptr;
     DevBuf<int32_t> bj, brev;
-    DevBuf<double> bconn, blen;
+    PingPong bconn;
+    DevBuf<double> blen;
     std::vector<uint32_t> h_bptr;
     std::vector<int32_t> h_bj;
 
@@ -125,6 +154,13 @@ struct lg_system {
 
     int64_t steps = 0, rebuilds = 0;
     int64_t launches0 = 0;
+
+    // optional per-kernel timing (lg_set_profiling)
+    bool profiling = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> prof_events;
+    size_t prof_used = 0;
+    double prof_ms = 0.0;
+    int64_t prof_count = 0;
 };
 
 namespace {
@@ -181,23 +217,82 @@ int build_allpairs(lg_system* s) {
     return retag(s);
 }
 
-int evaluate(lg_system* s) {
+int drain_profile(lg_system* s) {
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    for (size_t k = 0; k < s->prof_used; k++) {
+        float ms = 0.f;
+        LG_CUDA(cudaEventElapsedTime(&ms, s->prof_events[k].first, s->prof_events[k].second));
+        s->prof_ms += (double)ms;
+        s->prof_count++;
+    }
+    s->prof_used = 0;
+    return LG_OK;
+}
+
+int rows_per_block(const lg_system* s) {
+    // aim at ~1000 pairs (one tile) per CTA
+    const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 1.0;
+    int r = (int)std::lround(1000.0 / std::max(k_mean, 1.0));
+    r = std::max(8, std::min(r, tiled_max_rows_per_block()));
+    return r;
+}
+
+// One launch of the pair-force kernel at the current state.
+//   fused_dt < 0 : force only, a / alpha <- result (CLEAN afterwards)
+//   fused_dt >= 0: variant 1 only; force at the current state, then integrate with fused_dt into the next-step
+//                  buffers and swap them
+int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -1.0) {
     ForceArgs A{};
     A.n = (int)s->n;
     A.x = s->x.p; A.v = s->v.p; A.w = s->w.p; A.a = s->a.p; A.al = s->al.p;
     A.row_ptr = s->row_ptr.p; A.cols = s->cols.p; A.tag = s->tag.p;
     A.spr = s->spr.p; A.sgid = s->sgid.p; A.S = s->S;
-    A.bptr = s->bptr.p; A.bj = s->bj.p; A.brev = s->brev.p; A.bconn = s->bconn.p; A.blen = s->blen.p;
+    A.bptr = s->n_bonds > 0 ? s->bptr.p : nullptr;
+    A.bj = s->bj.p; A.brev = s->brev.p; A.bconn = s->bconn.p; A.blen = s->blen.p;
     A.mp = s->mp;
-    A.n_facets = (int)s->facets.size();
+    A.n_facets = (int)facets.size();
     for (int f = 0; f < A.n_facets; f++) {
-        A.facets[f] = s->facets[(size_t)f];
+        A.facets[f] = facets[(size_t)f];
         A.wspr[f] = s->wspr[(size_t)f]->p;
         A.wact[f] = s->wact[(size_t)f]->p;
     }
     A.err = s->err.p;
-    launch_force(A, s->mask, s->variant, s->stream);
+    A.rows_per_block = rows_per_block(s);
+    const bool fused = fused_dt >= 0.0;
+    A.dt = fused ? fused_dt : 0.0;
+    A.x_next = s->x.next; A.v_next = s->v.next; A.w_next = s->w.next; A.th = s->th.p; A.bconn_next = s->bconn.next;
+    if (s->profiling) {
+        if (s->prof_used == s->prof_events.size()) {
+            if (s->prof_used >= 4096) LG_TRY(drain_profile(s));
+            if (s->prof_used == s->prof_events.size()) {
+                cudaEvent_t e0, e1;
+                LG_CUDA(cudaEventCreate(&e0));
+                LG_CUDA(cudaEventCreate(&e1));
+                s->prof_events.emplace_back(e0, e1);
+            }
+        }
+        LG_CUDA(cudaEventRecord(s->prof_events[s->prof_used].first, s->stream));
+    }
+    if (fused)
+        launch_step_tiled(A, s->mask, true, s->stream);
+    else
+        launch_force(A, s->mask, s->variant, s->stream);
+    if (s->profiling) LG_CUDA(cudaEventRecord(s->prof_events[s->prof_used++].second, s->stream));
     LG_CUDA(cudaGetLastError());
+    if (fused) {
+        s->x.swap();
+        s->v.swap();
+        s->w.swap();
+        if (s->n_bonds > 0) s->bconn.swap();
+    }
+    return LG_OK;
+}
+
+// Materialise the evaluation a previous do_step left pending (a, alpha, contact springs at the current state).
+int flush(lg_system* s) {
+    if (!s->pending) return LG_OK;
+    LG_TRY(evaluate(s, s->pending_facets));
+    s->pending = false;
     return LG_OK;
 }
 
@@ -211,24 +306,42 @@ int prepare(lg_system* s) {
     return LG_OK;
 }
 
-int step(lg_system* s, double dt) {
-    if (!s->kicked) {
-        // first call: evaluate, half kick back, evaluate again (rotational_velocity_verlet_half.h:45-60)
-        LG_TRY(evaluate(s));
-        launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
-        LG_CUDA(cudaGetLastError());
-        LG_TRY(evaluate(s));
-        s->kicked = true;
-    }
+int integrate_in_place(lg_system* s, double dt) {
     IntegrateArgs I{};
     I.n = (int)s->n;
     I.x = s->x.p; I.v = s->v.p; I.th = s->th.p; I.w = s->w.p; I.a = s->a.p; I.al = s->al.p;
     I.bptr = s->n_bonds > 0 ? s->bptr.p : nullptr;
     I.bconn = s->bconn.p;
+    I.n_bonds = s->n_bonds;
     I.dt = dt;
     launch_integrate(I, s->stream);
     LG_CUDA(cudaGetLastError());
-    LG_TRY(evaluate(s));
+    return LG_OK;
+}
+
+int step(lg_system* s, double dt) {
+    if (!s->kicked) {
+        // first call: evaluate, half kick back, evaluate again (rotational_velocity_verlet_half.h:45-60)
+        LG_TRY(evaluate(s, s->facets));
+        launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
+        LG_CUDA(cudaGetLastError());
+        LG_TRY(evaluate(s, s->facets));
+        s->kicked = true;
+        s->pending = false;
+    }
+    if (s->variant == 0) {
+        // validation path: the reference's schedule literally -- integrate, then evaluate
+        LG_TRY(integrate_in_place(s, dt));
+        LG_TRY(evaluate(s, s->facets));
+    } else if (!s->pending) {
+        // a, alpha are current: integrate with them; the closing evaluation is left pending
+        LG_TRY(integrate_in_place(s, dt));
+        s->pending = true;
+    } else {
+        // steady state: ONE kernel = (pending evaluation of the previous step) + (this step's integration)
+        LG_TRY(evaluate(s, s->pending_facets, dt));
+    }
+    if (s->pending) s->pending_facets = s->facets;  // the closing evaluation sees the facets as they are now
     s->steps++;
     return LG_OK;
 }
@@ -237,6 +350,7 @@ int rebuild(lg_system* s) {
     if (!s->use_nl) return LG_OK;  // granular_system (all pairs) has no update_neighbor_list
     if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
     LG_TRY(ensure_slots(s));
+    LG_TRY(flush(s));  // the pending evaluation belongs to the OLD rows (it closed the previous do_step)
     const int n = (int)s->n;
     cudaStream_t st = s->stream;
     // 1. bounding box -> grid
@@ -329,7 +443,7 @@ int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
     LG_CUDA(s->bptr.reserve(n + 1));
     LG_CUDA(s->bj.reserve(nb));
     LG_CUDA(s->brev.reserve(nb));
-    LG_CUDA(s->bconn.reserve(nb * 15));
+    LG_CUDA(s->bconn.reserve(nb * 15 + 16));
     LG_CUDA(s->blen.reserve(nb * 5));
     LG_CUDA(cudaMemcpyAsync(s->bptr.p, bptr.data(), (n + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
     if (nb) {
@@ -458,6 +572,10 @@ int lg_destroy(lg_system* s) {
             cudaStreamDestroy(s->stream);
         }
         if (s->h_pinned) cudaFreeHost(s->h_pinned);
+        for (auto& ev : s->prof_events) {
+            cudaEventDestroy(ev.first);
+            cudaEventDestroy(ev.second);
+        }
         delete s;  // DevBuf destructors free device memory while the device is current
     }
     return LG_OK;
@@ -478,11 +596,13 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     LG_CUDA(cudaStreamSynchronize(s->stream));  // the caller may reuse its buffers
     s->state_set = true;
     s->kicked = false;
+    s->pending = false;
     return LG_OK;
 }
 
 int lg_get_field(lg_system* s, int field, double* out) {
     LG_ENTER(s);
+    if (field == LG_A || field == LG_ALPHA) LG_TRY(flush(s));
     double* src = field_ptr(s, field);
     if (!src || !out) return fail(LG_EINVAL, "bad field id or null output");
     LG_CUDA(cudaMemcpyAsync(out, src, 3 * (size_t)s->n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
@@ -491,6 +611,7 @@ int lg_get_field(lg_system* s, int field, double* out) {
 
 int lg_device_field(lg_system* s, int field, double** d_ptr) {
     LG_ENTER(s);
+    if (field == LG_A || field == LG_ALPHA) LG_TRY(flush(s));
     double* src = field_ptr(s, field);
     if (!src || !d_ptr) return fail(LG_EINVAL, "bad field id or null output");
     *d_ptr = src;
@@ -739,6 +860,7 @@ int lg_run(lg_system* s, double dt, int64_t n_steps, int64_t rebuild_every, int 
 
 int lg_reset_acceleration_buffers(lg_system* s) {
     LG_ENTER(s);
+    LG_TRY(flush(s));
     const size_t bytes = 3 * (size_t)s->n * sizeof(double);
     LG_CUDA(cudaMemsetAsync(s->a.p, 0, bytes, s->stream));
     LG_CUDA(cudaMemsetAsync(s->al.p, 0, bytes, s->stream));
@@ -784,6 +906,7 @@ int lg_get_contact_springs(lg_system* s, int64_t i, int64_t j, double out[9]) {
     if (!out || i < 0 || j < 0 || i >= s->n || j >= s->n) return fail(LG_EINVAL, "bad pair");
     std::fill(out, out + 9, 0.0);
     if (!s->slots_ready) return LG_OK;
+    LG_TRY(flush(s));
     std::vector<int32_t> ids((size_t)s->S);
     LG_CUDA(cudaMemcpyAsync(ids.data(), s->sgid.p + (size_t)i * s->S, (size_t)s->S * sizeof(int32_t), cudaMemcpyDeviceToHost,
                             s->stream));
@@ -818,6 +941,7 @@ int lg_get_counters(lg_system* s, int64_t out[8]) {
     LG_ENTER(s);
     if (!out) return fail(LG_EINVAL, "null output");
     unsigned long long contacts = 0;
+    LG_TRY(flush(s));
     if (s->slots_ready) {
         launch_count_slots((int)s->n, s->sgid.p, s->S, s->counter.p, s->stream);
         LG_CUDA(cudaMemcpyAsync(&contacts, s->counter.p, sizeof(contacts), cudaMemcpyDeviceToHost, s->stream));
@@ -866,9 +990,35 @@ int lg_diagnostics(lg_system* s, double out[9]) {
     return LG_OK;
 }
 
+int lg_get_stream(lg_system* s, void** stream) {
+    LG_ENTER(s);
+    if (!stream) return fail(LG_EINVAL, "null output");
+    *stream = (void*)s->stream;
+    return LG_OK;
+}
+
+int lg_set_profiling(lg_system* s, int enabled) {
+    LG_ENTER(s);
+    LG_TRY(drain_profile(s));
+    s->profiling = enabled != 0;
+    s->prof_ms = 0.0;
+    s->prof_count = 0;
+    return LG_OK;
+}
+
+int lg_get_profile(lg_system* s, double* ms, int64_t* count) {
+    LG_ENTER(s);
+    if (!ms || !count) return fail(LG_EINVAL, "null output");
+    LG_TRY(drain_profile(s));
+    *ms = s->prof_ms;
+    *count = s->prof_count;
+    return LG_OK;
+}
+
 int lg_set_kernel_variant(lg_system* s, int variant) {
     LG_ENTER(s);
     if (variant != 0 && variant != 1) return fail(LG_EINVAL, "variant must be 0 or 1");
+    LG_TRY(flush(s));
     s->variant = variant;
     return LG_OK;
 }

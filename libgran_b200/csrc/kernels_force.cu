@@ -166,12 +166,10 @@ static void launch_simple(const ForceArgs& args, cudaStream_t st) {
     g_launch_count++;
 }
 
-void launch_force_tiled(const ForceArgs& args, int mask, cudaStream_t st);  // kernels_force_tiled.cu
-
 void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st) {
     if (args.n <= 0) return;
     if (variant == 1) {
-        launch_force_tiled(args, mask, st);
+        launch_step_tiled(args, mask, false, st);
         return;
     }
     switch (mask & (MODEL_CONTACT | MODEL_HAMAKER | MODEL_SINTER)) {

@@ -1,7 +1,382 @@
-// kernels_force_tiled.cu -- placeholder: the tiled pair-parallel kernel is added in a later commit;
-// until then variant 1 routes to the simple kernel.
+// kernels_force_tiled.cu -- the production step kernel (sm_100a): pair-parallel force evaluation with an
+// ordered per-particle reduction, optionally fused with the velocity-Verlet update.
+//
+// Replaces, in ONE launch per time step,
+//   LT/rotational_system/rotational_binary_system_neighbors_omp.h:78-98   (pair loop, ascending j)
+//   LG/granular_system/binary_force_container.h:20-32                     (functor fold per pair)
+//   LG/contact_force/contact_force.h:57-147, LG/hamaker_force/hamaker_force.h:28-43,
+//   LG/sinter_bridge/sinter_bridge.h:214-259                              (force laws, via physics.cuh)
+//   LT/rotational_integrator/rotational_velocity_verlet_half.h:63-73      (integrate, MODE_FUSED)
+//   LG/sinter_bridge/sinter_bridge.h:24-42,55-75                          (connector update, MODE_FUSED)
+//
+// Organisation (one CTA of 256 threads owns `rows_per_block` consecutive particles):
+//   stage   x, v, omega of the CTA's particles and its slice of the row / bond pointers -> shared memory
+//   per tile of up to 1024 consecutive neighbor pairs of those rows:
+//     phase A  one thread per PAIR: geometry, Hamaker, contact test (the cheap, uniform work);
+//              pairs that need the expensive laws (bonded, overlapping) are compacted into a list with
+//              warp ballots so that phase B runs with full lanes instead of diverging inside phase A
+//     phase B  one thread per HEAVY pair: sinter-bridge springs or Luding contact with its history springs
+//     phase C  one thread per PARTICLE: adds its pairs' contributions from shared memory in ascending-j
+//              order -- the reference's accumulation order, so a / alpha are bit-identical to it; no
+//              atomics, deterministic
+//   finalize unary (facet) forces, then either write a, alpha (MODE_FORCE) or integrate v, x, omega, theta
+//            into the next-step buffers and move the particle's bridge connectors (MODE_FUSED), with
+//            coalesced stores staged through shared memory.
+// Particle state is never modified in place while other CTAs may still read it: x, v, omega and the
+// connectors are double-buffered (A.x / A.x_next ...), swapped by the host after the launch.
 #include "system.h"
+
 namespace lg {
-void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st);
-void launch_force_tiled(const ForceArgs& args, int mask, cudaStream_t st) { launch_force(args, mask, 0, st); }
+
+namespace {
+
+constexpr int TB = 256;     // threads per CTA
+constexpr int TILE = 1024;  // pairs per tile
+constexpr int RMAX = 128;   // max particles per CTA
+
+enum : int { MODE_FORCE = 0, MODE_FUSED = 1 };
+enum : int { KIND_LIGHT = 0, KIND_BOND = 1, KIND_CONTACT = 2 };
+
+struct Smem {
+    double tile[6 * TILE];  // a.x a.y a.z alpha.x alpha.y alpha.z, structure-of-arrays over the tile
+    double st[RMAX * 9];    // x, v, omega of the CTA's particles
+    uint32_t sptr[RMAX + 1];
+    uint32_t sbptr[RMAX + 1];
+    uint16_t heavy[TILE];
+    int cnt[2];
+};
+
+__device__ __forceinline__ Springs ld_springs(const double* p) {
+    Springs s;
+    s.xi[0] = load3(p);
+    s.xi[1] = load3(p + 3);
+    s.xi[2] = load3(p + 6);
+    return s;
 }
+__device__ __forceinline__ void st_springs(double* p, const Springs& s) {
+    store3(p, s.xi[0]);
+    store3(p + 3, s.xi[1]);
+    store3(p + 6, s.xi[2]);
+}
+
+// largest r in [0, nrows) with ptr[r] <= p (ptr[nrows] > p guaranteed by the caller)
+__device__ __forceinline__ int find_row(const uint32_t* ptr, int nrows, uint32_t p) {
+    int lo = 0, hi = nrows;
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (ptr[mid] <= p) lo = mid; else hi = mid - 1;
+    }
+    return lo;
+}
+
+// unary forces: right fold over facets, see kernels_force.cu:unary_accel
+__device__ __forceinline__ Accel unary_forces(const ForceArgs& A, int i, d3 xi, d3 vi, d3 wi) {
+    Accel total = zero_accel();
+    for (int f = A.n_facets - 1; f >= 0; f--) {
+        const Facet& F = A.facets[f];
+        const d3 xf = facet_closest_point(F, xi);
+        const PairGeom g = pair_geometry(xi, xf);
+        Accel c = zero_accel();
+        if (F.has_contact) {
+            const double overlap = contact_overlap(g, A.mp.r);
+            double* sp = A.wspr[f] + (size_t)i * 9;
+            const uint8_t act = A.wact[f][i];
+            if (overlap <= 0) {
+                if (act) {
+                    Springs z;
+                    z.xi[0] = z.xi[1] = z.xi[2] = zero3();
+                    st_springs(sp, z);
+                    A.wact[f][i] = 0;
+                }
+            } else {
+                Springs s;
+                if (act) s = ld_springs(sp); else s.xi[0] = s.xi[1] = s.xi[2] = zero3();
+                c = wall_contact_force(F.sp, A.mp.r, A.mp.mass, A.mp.inertia, g, overlap, vi, F.v, wi, s);
+                st_springs(sp, s);
+                if (!act) A.wact[f][i] = 1;
+            }
+        }
+        if (F.has_hamaker) {
+            const Accel h = Accel{wall_hamaker_accel(F.A, F.h0, A.mp.r, A.mp.mass, g), zero3()};
+            c = F.has_contact ? c + h : h;
+        }
+        total = (f == A.n_facets - 1) ? c : c + total;
+    }
+    return total;
+}
+
+template <int MASK, int MODE>
+__global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
+    constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
+    constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
+    constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
+
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int R = A.rows_per_block;
+    const int i0 = blockIdx.x * R;
+    const int nrows = min(R, A.n - i0);
+    const bool have_bonds = kSinter && A.bptr != nullptr;
+
+    // ---- stage the CTA's particles (coalesced: 3 * nrows consecutive doubles per field) ----------------
+    for (int idx = tid; idx < 3 * nrows; idx += TB) {
+        const int r = idx / 3, c = idx - 3 * r;
+        const size_t gidx = 3 * (size_t)i0 + idx;
+        sm.st[r * 9 + c] = A.x[gidx];
+        sm.st[r * 9 + 3 + c] = A.v[gidx];
+        sm.st[r * 9 + 6 + c] = A.w[gidx];
+    }
+    for (int idx = tid; idx <= nrows; idx += TB) {
+        sm.sptr[idx] = A.row_ptr[i0 + idx];
+        sm.sbptr[idx] = have_bonds ? A.bptr[i0 + idx] : 0u;
+    }
+    if (tid == 0) sm.cnt[0] = sm.cnt[1] = 0;
+    __syncthreads();
+
+    const uint32_t p_begin = sm.sptr[0], p_end = sm.sptr[nrows];
+    d3 acc_a = zero3(), acc_al = zero3();  // meaningful for tid < nrows
+
+    auto particle = [&](int r, int which) -> d3 { return load3(sm.st + r * 9 + 3 * which); };
+    auto neighbour = [&](int j, int which, const double* gsrc) -> d3 {
+        const unsigned rj = (unsigned)(j - i0);
+        return rj < (unsigned)nrows ? load3(sm.st + rj * 9 + 3 * which) : load3(gsrc + 3 * (size_t)j);
+    };
+
+    for (uint32_t tile_start = p_begin; tile_start < p_end; tile_start += TILE) {
+        const int cntp = (int)min((uint32_t)TILE, p_end - tile_start);
+
+        // ---- phase A: light work for every pair, classify ------------------------------------------------
+        for (int qb = 0; qb < cntp; qb += TB) {
+            const int q = qb + tid;
+            int kind = KIND_LIGHT;
+            if (q < cntp) {
+                const uint32_t p = tile_start + q;
+                const int r = find_row(sm.sptr, nrows, p);
+                const int j = A.cols[p];
+                const d3 xi = particle(r, 0);
+                const d3 xj = neighbour(j, 0, A.x);
+                const PairGeom g = pair_geometry(xi, xj);
+                if constexpr (kContact) {
+                    const int t = A.tag[p];
+                    if (kSinter && t >= kTagBond && t != kTagNone) {
+                        kind = KIND_BOND;
+                    } else {
+                        const double overlap = contact_overlap(g, 2.0 * A.mp.r);
+                        if (overlap <= 0) {
+                            if (t != kTagNone) {  // reset_springs (contact_force.h:68-71)
+                                A.sgid[(size_t)(i0 + r) * A.S + t] = -1;
+                                A.tag[p] = (uint8_t)kTagNone;
+                            }
+                        } else {
+                            kind = KIND_CONTACT;
+                        }
+                    }
+                }
+                d3 h = zero3();
+                if constexpr (kHamaker) h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
+                sm.tile[0 * TILE + q] = h.x;
+                sm.tile[1 * TILE + q] = h.y;
+                sm.tile[2 * TILE + q] = h.z;
+                sm.tile[3 * TILE + q] = 0.0;
+                sm.tile[4 * TILE + q] = 0.0;
+                sm.tile[5 * TILE + q] = 0.0;
+            }
+            if constexpr (kContact) {
+                const unsigned mb = __ballot_sync(0xffffffffu, kind == KIND_BOND);
+                const unsigned mc = __ballot_sync(0xffffffffu, kind == KIND_CONTACT);
+                if (mb | mc) {
+                    int base_b = 0, base_c = 0;
+                    if (lane == 0) {
+                        if (mb) base_b = atomicAdd(&sm.cnt[0], __popc(mb));  // list position only; results unaffected
+                        if (mc) base_c = atomicAdd(&sm.cnt[1], __popc(mc));
+                    }
+                    base_b = __shfl_sync(0xffffffffu, base_b, 0);
+                    base_c = __shfl_sync(0xffffffffu, base_c, 0);
+                    const unsigned lt = (1u << lane) - 1u;
+                    if (kind == KIND_BOND) sm.heavy[base_b + __popc(mb & lt)] = (uint16_t)q;
+                    if (kind == KIND_CONTACT) sm.heavy[TILE - 1 - (base_c + __popc(mc & lt))] = (uint16_t)q;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase B: bonded and overlapping pairs, densely packed -----------------------------------------
+        if constexpr (kContact) {
+            const int nB = sm.cnt[0], nC = sm.cnt[1];
+            for (int e = tid; e < nB + nC; e += TB) {
+                const bool is_bond = e < nB;
+                const int q = is_bond ? sm.heavy[e] : sm.heavy[TILE - 1 - (e - nB)];
+                const uint32_t p = tile_start + q;
+                const int r = find_row(sm.sptr, nrows, p);
+                const int i = i0 + r;
+                const int j = A.cols[p];
+                const d3 xi = particle(r, 0), vi = particle(r, 1), wi = particle(r, 2);
+                const d3 xj = neighbour(j, 0, A.x), vj = neighbour(j, 1, A.v), wj = neighbour(j, 2, A.w);
+                const int t = A.tag[p];
+                Accel c;
+                if (kSinter && is_bond) {
+                    const uint32_t b = sm.sbptr[r] + (uint32_t)(t - kTagBond);
+                    const double* ci = A.bconn + (size_t)b * 15;
+                    const double* cj = A.bconn + (size_t)A.brev[b] * 15;
+                    const double* len = A.blen + (size_t)b * 5;
+                    d3 force = zero3(), torque = zero3();
+#pragma unroll 1
+                    for (int k = 0; k < 5; k++)
+                        bonded_spring(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi, vj,
+                                      wi, wj, force, torque);
+                    c = Accel{force / A.mp.mass, torque / A.mp.inertia};
+                } else {
+                    const PairGeom g = pair_geometry(xi, xj);
+                    const double overlap = contact_overlap(g, 2.0 * A.mp.r);
+                    int slot = t;
+                    Springs s;
+                    if (t == kTagNone) {  // first overlapping evaluation: claim a free slot of particle i
+                        slot = -1;
+                        for (int k = 0; k < A.S; k++)
+                            if (atomicCAS(&A.sgid[(size_t)i * A.S + k], -1, j) == -1) {  // bookkeeping only
+                                slot = k;
+                                break;
+                            }
+                        s.xi[0] = s.xi[1] = s.xi[2] = zero3();
+                        if (slot >= 0) A.tag[p] = (uint8_t)slot; else atomicOr(A.err, ERR_SLOT_OVERFLOW);
+                    } else {
+                        s = ld_springs(A.spr + ((size_t)i * A.S + slot) * 9);
+                    }
+                    c = contact_force(A.mp.cp, A.mp.r, A.mp.mass, A.mp.inertia, g, overlap, vi, vj, wi, wj, s);
+                    if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
+                }
+                if constexpr (kHamaker) {  // pair value = (contact | sinter)(i,j) + hamaker(i,j)
+                    sm.tile[0 * TILE + q] = c.a.x + sm.tile[0 * TILE + q];
+                    sm.tile[1 * TILE + q] = c.a.y + sm.tile[1 * TILE + q];
+                    sm.tile[2 * TILE + q] = c.a.z + sm.tile[2 * TILE + q];
+                } else {
+                    sm.tile[0 * TILE + q] = c.a.x;
+                    sm.tile[1 * TILE + q] = c.a.y;
+                    sm.tile[2 * TILE + q] = c.a.z;
+                }
+                sm.tile[3 * TILE + q] = c.alpha.x;
+                sm.tile[4 * TILE + q] = c.alpha.y;
+                sm.tile[5 * TILE + q] = c.alpha.z;
+            }
+            __syncthreads();
+        }
+
+        // ---- phase C: ordered per-particle accumulation (ascending j) ----------------------------------------
+        if (tid < nrows) {
+            const uint32_t lo = max(sm.sptr[tid], tile_start);
+            const uint32_t hi = min(sm.sptr[tid + 1], tile_start + (uint32_t)cntp);
+            for (uint32_t p = lo; p < hi; p++) {
+                const int q = (int)(p - tile_start);
+                acc_a.x += sm.tile[0 * TILE + q];
+                acc_a.y += sm.tile[1 * TILE + q];
+                acc_a.z += sm.tile[2 * TILE + q];
+                acc_al.x += sm.tile[3 * TILE + q];
+                acc_al.y += sm.tile[4 * TILE + q];
+                acc_al.z += sm.tile[5 * TILE + q];
+            }
+        }
+        if (tid == 0) sm.cnt[0] = sm.cnt[1] = 0;
+        __syncthreads();
+    }
+
+    // ---- finalize: unary forces, then output through shared memory (the tile area is free now) --------------
+    double* out = sm.tile;  // [0,3R) [3R,6R) ... blocks of 3 * RMAX doubles
+    constexpr int OB = 3 * RMAX;
+    if (tid < nrows) {
+        const int i = i0 + tid;
+        const d3 xi = particle(tid, 0), vi = particle(tid, 1), wi = particle(tid, 2);
+        if (A.n_facets > 0) {
+            const Accel u = unary_forces(A, i, xi, vi, wi);
+            acc_a += u.a;
+            acc_al += u.alpha;
+        }
+        if constexpr (MODE == MODE_FORCE) {
+            store3(out + 0 * OB + 3 * tid, acc_a);
+            store3(out + 1 * OB + 3 * tid, acc_al);
+        } else {
+            const double dt = A.dt;
+            const d3 v = vi + acc_a * dt;    // increment_v(n, a * dt)
+            const d3 dx = v * dt;            // increment_x(n, v * dt), v already updated
+            const d3 x = xi + dx;
+            const d3 w = wi + acc_al * dt;   // increment_omega
+            const d3 dth = w * dt;           // increment_theta, omega already updated
+            store3(out + 0 * OB + 3 * tid, x);
+            store3(out + 1 * OB + 3 * tid, v);
+            store3(out + 2 * OB + 3 * tid, w);
+            store3(out + 3 * OB + 3 * tid, dth);
+            store3(out + 4 * OB + 3 * tid, dx);
+        }
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 3 * nrows; idx += TB) {
+        const size_t gidx = 3 * (size_t)i0 + idx;
+        if constexpr (MODE == MODE_FORCE) {
+            A.a[gidx] = out[0 * OB + idx];
+            A.al[gidx] = out[1 * OB + idx];
+        } else {
+            A.x_next[gidx] = out[0 * OB + idx];
+            A.v_next[gidx] = out[1 * OB + idx];
+            A.w_next[gidx] = out[2 * OB + idx];
+            A.th[gidx] = A.th[gidx] + out[3 * OB + idx];
+        }
+    }
+    if constexpr (MODE == MODE_FUSED && kSinter) {
+        if (have_bonds) {
+            // connectors of the CTA's particles: c += dx ; c += dtheta x (c - x_new)   (sinter_bridge.h:36-41,67-74)
+            const uint32_t b0 = sm.sbptr[0];
+            const int ncon = (int)(sm.sbptr[nrows] - b0) * 5;
+            for (int cq = tid; cq < ncon; cq += TB) {
+                const uint32_t b = b0 + (uint32_t)(cq / 5);
+                const int r = find_row(sm.sbptr, nrows, b);
+                const size_t off = (size_t)b0 * 15 + 3 * (size_t)cq;
+                d3 ck = load3(A.bconn + off) + load3(out + 4 * OB + 3 * r);
+                const d3 sv = ck - load3(out + 0 * OB + 3 * r);
+                ck = ck + cross(load3(out + 3 * OB + 3 * r), sv);
+                store3(A.bconn_next + off, ck);
+            }
+        }
+    }
+}
+
+template <int MASK, int MODE>
+void launch_one(const ForceArgs& args, cudaStream_t st) {
+    static bool configured = false;  // per instantiation
+    if (!configured) {
+        cudaFuncSetAttribute(step_tiled_kernel<MASK, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        configured = true;
+    }
+    const int R = args.rows_per_block;
+    const int blocks = (args.n + R - 1) / R;
+    step_tiled_kernel<MASK, MODE><<<blocks, TB, sizeof(Smem), st>>>(args);
+    g_launch_count++;
+}
+
+template <int MODE>
+void launch_mode(const ForceArgs& args, int mask, cudaStream_t st) {
+    switch (mask & (MODEL_CONTACT | MODEL_HAMAKER | MODEL_SINTER)) {
+        case MODEL_CONTACT: launch_one<MODEL_CONTACT, MODE>(args, st); break;
+        case MODEL_CONTACT | MODEL_HAMAKER: launch_one<MODEL_CONTACT | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_SINTER: launch_one<MODEL_SINTER, MODE>(args, st); break;
+        case MODEL_SINTER | MODEL_HAMAKER: launch_one<MODEL_SINTER | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_HAMAKER: launch_one<MODEL_HAMAKER, MODE>(args, st); break;
+        default: launch_one<0, MODE>(args, st); break;
+    }
+}
+
+}  // namespace
+
+int tiled_max_rows_per_block() { return RMAX; }
+
+// fused == false: a, alpha <- forces at (x, v, omega)                    [MODE_FORCE]
+// fused == true : additionally integrates into x_next, v_next, w_next, th, bconn_next  [MODE_FUSED]
+void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {
+    if (args.n <= 0) return;
+    if (fused)
+        launch_mode<MODE_FUSED>(args, mask, st);
+    else
+        launch_mode<MODE_FORCE>(args, mask, st);
+}
+
+}  // namespace lg

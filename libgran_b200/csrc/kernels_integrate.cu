@@ -1,50 +1,65 @@
-// kernels_integrate.cu -- the leap-frog ("velocity Verlet half") update.
+// kernels_integrate.cu -- the stand-alone leap-frog ("velocity Verlet half") update, in place.
 //
-// Replaces the serial loop of LT/rotational_integrator/rotational_velocity_verlet_half.h:63-73 with the
-// default step handler (LT/rotational_step_handler/rotational_step_handler.h:19-68) or, when bonds
-// exist, the sinter step handler (LG/sinter_bridge/sinter_bridge.h:24-42,55-75):
+// Used on the first step, after a neighbor rebuild and by the validation path; in steady state the update is
+// fused into the step kernel (kernels_force_tiled.cu).  Replaces the serial loop of
+// LT/rotational_integrator/rotational_velocity_verlet_half.h:63-73 with the default step handler
+// (LT/rotational_step_handler/rotational_step_handler.h:19-68) or, when bonds exist, the sinter step handler
+// (LG/sinter_bridge/sinter_bridge.h:24-42,55-75):
 //   v += a dt ; x += v dt (updated v) ; omega += alpha dt ; theta += omega dt (updated omega)
 //   each connector c of each bond of the particle: c += dx ; c += dtheta x (c - x_new)
 // and the first-call half kick back v -= a dt/2, omega -= alpha dt/2 (:51-57).
-// Every particle touches only its own rows, so one thread per particle is race free.
 #include "system.h"
 
 namespace lg {
 
-__global__ void __launch_bounds__(256) integrate_kernel(const IntegrateArgs A) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= A.n) return;
-    const size_t o = 3 * (size_t)i;
-    const double dt = A.dt;
-    d3 v = load3(A.v + o) + load3(A.a + o) * dt;  // increment_v(n, a * dt)
-    store3(A.v + o, v);
-    const d3 dx = v * dt;  // increment_x(n, v * dt) with v already updated (:64,69-70)
-    const d3 x = load3(A.x + o) + dx;
-    store3(A.x + o, x);
-    d3 w = load3(A.w + o) + load3(A.al + o) * dt;  // increment_omega
-    store3(A.w + o, w);
-    const d3 dth = w * dt;  // increment_theta with omega already updated (:66,71-72)
-    store3(A.th + o, load3(A.th + o) + dth);
-    if (A.bptr != nullptr) {
-        const uint32_t b0 = A.bptr[i], b1 = A.bptr[i + 1];
-        for (uint32_t b = b0; b < b1; b++) {
-            double* c = A.bconn + (size_t)b * 15;
-#pragma unroll
-            for (int k = 0; k < 5; k++) {
-                d3 ck = load3(c + 3 * k) + dx;  // sinter_bridge.h:36-41
-                const d3 sv = ck - x;           // :70-71, x already incremented
-                ck = ck + cross(dth, sv);
-                store3(c + 3 * k, ck);
-            }
-        }
+// flat over the 3n components: every operation of the particle update is component-wise
+__global__ void __launch_bounds__(256) integrate_particles_kernel(int n3, double* x, double* v, double* th, double* w,
+                                                                  const double* a, const double* al, double dt) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n3) return;
+    const double vk = v[k] + a[k] * dt;  // increment_v(n, a * dt)
+    v[k] = vk;
+    x[k] = x[k] + vk * dt;  // increment_x(n, v * dt) with v already updated (:64,69-70)
+    const double wk = w[k] + al[k] * dt;  // increment_omega
+    w[k] = wk;
+    th[k] = th[k] + wk * dt;  // increment_theta with omega already updated (:66,71-72)
+}
+
+// one thread per connector; runs after integrate_particles_kernel, so v, x, w already hold the new values and
+// dx = v_new * dt, dtheta = omega_new * dt are recomputed with the very same operands
+__global__ void __launch_bounds__(256) integrate_connectors_kernel(int n, int64_t n_conn, const uint32_t* bptr, double* bconn,
+                                                                   const double* x, const double* v, const double* w, double dt) {
+    const int64_t cq = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (cq >= n_conn) return;
+    const uint32_t b = (uint32_t)(cq / 5);
+    int lo = 0, hi = n;  // owner: largest i with bptr[i] <= b
+    while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (bptr[mid] <= b) lo = mid; else hi = mid - 1;
     }
+    const size_t o = 3 * (size_t)lo;
+    const d3 dx = load3(v + o) * dt;
+    const d3 dth = load3(w + o) * dt;
+    double* c = bconn + 3 * (size_t)cq;
+    d3 ck = load3(c) + dx;                // sinter_bridge.h:36-41
+    const d3 sv = ck - load3(x + o);      // :70-71, x already incremented
+    ck = ck + cross(dth, sv);
+    store3(c, ck);
 }
 
 void launch_integrate(const IntegrateArgs& args, cudaStream_t st) {
     if (args.n <= 0) return;
     const int threads = 256;
-    integrate_kernel<<<(args.n + threads - 1) / threads, threads, 0, st>>>(args);
+    const int n3 = 3 * args.n;
+    integrate_particles_kernel<<<(n3 + threads - 1) / threads, threads, 0, st>>>(n3, args.x, args.v, args.th, args.w, args.a,
+                                                                               args.al, args.dt);
     g_launch_count++;
+    if (args.bptr != nullptr && args.n_bonds > 0) {
+        const int64_t n_conn = args.n_bonds * 5;
+        integrate_connectors_kernel<<<(unsigned)((n_conn + threads - 1) / threads), threads, 0, st>>>(
+            args.n, n_conn, args.bptr, args.bconn, args.x, args.v, args.w, args.dt);
+        g_launch_count++;
+    }
 }
 
 // rotational_velocity_verlet_half.h:51-57: increment_v(n, -a * dt / 2.0), increment_omega(n, -alpha * dt / 2.0)

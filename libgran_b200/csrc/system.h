@@ -70,6 +70,14 @@ struct ForceArgs {
     double* wspr[kMaxFacets];
     uint8_t* wact[kMaxFacets];
     int* err;
+    // tiled / fused kernel only
+    int rows_per_block;
+    double dt;          // integration step of the fused update
+    double* x_next;     // next-step buffers (double-buffered state)
+    double* v_next;
+    double* w_next;
+    double* th;         // theta is private to its particle: updated in place
+    double* bconn_next;
 };
 
 struct IntegrateArgs {
@@ -82,6 +90,7 @@ struct IntegrateArgs {
     const double* al;
     const uint32_t* bptr;  // null when there are no bonds
     double* bconn;
+    int64_t n_bonds;       // ordered bonds
     double dt;
 };
 
@@ -97,6 +106,9 @@ extern thread_local int64_t g_launch_count;
 
 // ---- launchers (kernels_*.cu) ---------------------------------------------------------------------
 void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st);
+// tiled kernel: force only (fused == false) or force + integrate into the next-step buffers (fused == true)
+void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st);
+int tiled_max_rows_per_block();
 void launch_integrate(const IntegrateArgs& args, cudaStream_t st);
 void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, cudaStream_t st);
 

@@ -28,7 +28,7 @@ ABI_SYMBOLS = (
     "lg_facet_set_velocity", "lg_facet_update_positions", "lg_facet_get_vertices", "lg_enable_neighbor_list",
     "lg_update_neighbor_list", "lg_do_step", "lg_run", "lg_reset_acceleration_buffers", "lg_synchronize",
     "lg_get_neighbor_count", "lg_get_neighbor_rows", "lg_get_contact_springs", "lg_get_bond", "lg_get_counters",
-    "lg_diagnostics", "lg_set_kernel_variant",
+    "lg_diagnostics", "lg_set_kernel_variant", "lg_get_stream", "lg_set_profiling", "lg_get_profile",
 )
 
 
@@ -101,6 +101,9 @@ def load_library(path: Optional[str] = None):
     lib.lg_get_counters.argtypes = [vp, ip]
     lib.lg_diagnostics.argtypes = [vp, dp]
     lib.lg_set_kernel_variant.argtypes = [vp, C.c_int]
+    lib.lg_get_stream.argtypes = [vp, C.POINTER(vp)]
+    lib.lg_set_profiling.argtypes = [vp, C.c_int]
+    lib.lg_get_profile.argtypes = [vp, dp, ip]
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("lg_last_error",):
@@ -272,6 +275,20 @@ class GranularSystem:
     def get_theta(self): return self.get("theta")
     def get_omega(self): return self.get("omega")
     def get_alpha(self): return self.get("alpha")
+
+    def stream_handle(self) -> int:
+        """cudaStream_t of the system, e.g. for torch.cuda.ExternalStream."""
+        p = C.c_void_p()
+        self._check(self.lib.lg_get_stream(self.h, C.byref(p)))
+        return int(p.value or 0)
+
+    def set_profiling(self, on: bool):
+        self._check(self.lib.lg_set_profiling(self.h, int(bool(on))))
+
+    def get_profile(self):
+        ms, cnt = C.c_double(0.0), C.c_int64(0)
+        self._check(self.lib.lg_get_profile(self.h, C.byref(ms), C.byref(cnt)))
+        return float(ms.value), int(cnt.value)
 
     def device_ptr(self, name: str) -> int:
         p = C.c_void_p()
