@@ -189,6 +189,12 @@ def run_ours(args):
                                "frac": round(step_bytes * args.steps / (ms * 1e-3) / 1e9 / peak, 4),
                                "frac_of_nominal_8TBs": round(step_bytes * args.steps / (ms * 1e-3) / 8e12, 4)}}
 
+    if args.kernel_only:
+        if rank == 0:
+            print(json.dumps({"value": round(value, 1), "ms_per_step": round(ms / args.steps, 5), "roofline": roofline,
+                              "gpu_launches": int(launches), "clocks": clocks, "lib": os.environ.get("LGB200_LIB", "default")}))
+        return
+
     # ---- end to end through the host-facing API with host buffers ---------------------------------
     pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in scn.state]
     host_np = [t.numpy() for t in pinned]
@@ -292,6 +298,7 @@ def main():
     ap.add_argument("--sample", type=int, default=34, help="aggregates in the CPU-reference sample (34 -> 5100 particles)")
     ap.add_argument("--variant", type=int, default=None, help="force kernel variant (0 simple, 1 tiled)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel-only", action="store_true", help="tuning runs: device-resident throughput + roofline only")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

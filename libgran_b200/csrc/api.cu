@@ -230,9 +230,9 @@ int drain_profile(lg_system* s) {
 }
 
 int rows_per_block(const lg_system* s) {
-    // aim at ~1000 pairs (one tile) per CTA
+    // aim at one (almost full) tile of pairs per CTA
     const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 1.0;
-    int r = (int)std::lround(1000.0 / std::max(k_mean, 1.0));
+    int r = (int)std::lround(0.977 * tiled_tile_pairs() / std::max(k_mean, 1.0));
     r = std::max(8, std::min(r, tiled_max_rows_per_block()));
     return r;
 }

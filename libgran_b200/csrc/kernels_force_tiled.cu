@@ -30,19 +30,38 @@ namespace lg {
 
 namespace {
 
-constexpr int TB = 256;     // threads per CTA
-constexpr int TILE = 1024;  // pairs per tile
-constexpr int RMAX = 128;   // max particles per CTA
+// Tunables (compile-time; -DLG_TB=... builds an experimental library, see scripts/build_variants.sh)
+#ifndef LG_TB
+#define LG_TB 256
+#endif
+#ifndef LG_TILE
+#define LG_TILE 1024
+#endif
+#ifndef LG_RMAX
+#define LG_RMAX 128
+#endif
+#ifndef LG_MINB
+#define LG_MINB 2
+#endif
+constexpr int TB = LG_TB;      // threads per CTA
+constexpr int TILE = LG_TILE;  // pairs per tile
+constexpr int RMAX = LG_RMAX;  // max particles per CTA (<= TB)
+constexpr int TS = TILE + 1;   // padded component stride of the tile (bank spread for phase C)
+static_assert(RMAX <= TB, "one staging pass per CTA");
+static_assert(15 * RMAX <= 6 * TS, "the output staging area reuses the tile");
 
 enum : int { MODE_FORCE = 0, MODE_FUSED = 1 };
 enum : int { KIND_LIGHT = 0, KIND_BOND = 1, KIND_CONTACT = 2 };
 
 struct Smem {
-    double tile[6 * TILE];  // a.x a.y a.z alpha.x alpha.y alpha.z, structure-of-arrays over the tile
+    double tile[6 * TS];    // a.x a.y a.z alpha.x alpha.y alpha.z, structure-of-arrays over the tile
     double st[RMAX * 9];    // x, v, omega of the CTA's particles
+    double acc[RMAX * 6];   // running a, alpha of the CTA's particles ([row][component])
+    double sth[RMAX * 3];   // theta of the CTA's particles (MODE_FUSED)
     uint32_t sptr[RMAX + 1];
     uint32_t sbptr[RMAX + 1];
     uint16_t heavy[TILE];
+    uint8_t srow[TILE];     // local row of every pair of the tile (written by the row owners, replaces a search)
     int cnt[2];
 };
 
@@ -105,8 +124,8 @@ __device__ __forceinline__ Accel unary_forces(const ForceArgs& A, int i, d3 xi, 
     return total;
 }
 
-template <int MASK, int MODE>
-__global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
+template <int MASK, int MODE, bool FACETS>
+__global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
     constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
@@ -127,16 +146,23 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
         sm.st[r * 9 + c] = A.x[gidx];
         sm.st[r * 9 + 3 + c] = A.v[gidx];
         sm.st[r * 9 + 6 + c] = A.w[gidx];
+        if constexpr (MODE == MODE_FUSED) sm.sth[idx] = A.th[gidx];
     }
-    for (int idx = tid; idx <= nrows; idx += TB) {
-        sm.sptr[idx] = A.row_ptr[i0 + idx];
-        sm.sbptr[idx] = have_bonds ? A.bptr[i0 + idx] : 0u;
+    for (int idx = tid; idx < 6 * nrows; idx += TB) sm.acc[idx] = 0.0;
+    const uint32_t p_begin = A.row_ptr[i0];
+    if (tid <= nrows) {
+        const uint32_t rp = A.row_ptr[i0 + tid];
+        sm.sptr[tid] = rp;
+        sm.sbptr[tid] = have_bonds ? A.bptr[i0 + tid] : 0u;
+        if (tid < nrows) {  // local-row map of the first tile
+            const uint32_t lo = rp - p_begin, hi = min(A.row_ptr[i0 + tid + 1] - p_begin, (uint32_t)TILE);
+            for (uint32_t q = lo; q < hi; q++) sm.srow[q] = (uint8_t)tid;
+        }
     }
     if (tid == 0) sm.cnt[0] = sm.cnt[1] = 0;
     __syncthreads();
 
-    const uint32_t p_begin = sm.sptr[0], p_end = sm.sptr[nrows];
-    d3 acc_a = zero3(), acc_al = zero3();  // meaningful for tid < nrows
+    const uint32_t p_end = sm.sptr[nrows];
 
     auto particle = [&](int r, int which) -> d3 { return load3(sm.st + r * 9 + 3 * which); };
     auto neighbour = [&](int j, int which, const double* gsrc) -> d3 {
@@ -148,18 +174,29 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
         const int cntp = (int)min((uint32_t)TILE, p_end - tile_start);
 
         // ---- phase A: light work for every pair, classify ------------------------------------------------
+        // columns / tags of the next pass are requested before the current pass computes (latency hiding)
+        int j_cur = 0, t_cur = kTagNone;
+        if (tid < cntp) {
+            j_cur = A.cols[tile_start + tid];
+            if constexpr (kContact) t_cur = A.tag[tile_start + tid];
+        }
         for (int qb = 0; qb < cntp; qb += TB) {
             const int q = qb + tid;
+            int j_nxt = 0, t_nxt = kTagNone;
+            if (q + TB < cntp) {
+                j_nxt = A.cols[tile_start + q + TB];
+                if constexpr (kContact) t_nxt = A.tag[tile_start + q + TB];
+            }
             int kind = KIND_LIGHT;
             if (q < cntp) {
                 const uint32_t p = tile_start + q;
-                const int r = find_row(sm.sptr, nrows, p);
-                const int j = A.cols[p];
+                const int r = sm.srow[q];
+                const int j = j_cur;
                 const d3 xi = particle(r, 0);
                 const d3 xj = neighbour(j, 0, A.x);
                 const PairGeom g = pair_geometry(xi, xj);
                 if constexpr (kContact) {
-                    const int t = A.tag[p];
+                    const int t = t_cur;
                     if (kSinter && t >= kTagBond && t != kTagNone) {
                         kind = KIND_BOND;
                     } else {
@@ -176,12 +213,12 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
                 }
                 d3 h = zero3();
                 if constexpr (kHamaker) h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
-                sm.tile[0 * TILE + q] = h.x;
-                sm.tile[1 * TILE + q] = h.y;
-                sm.tile[2 * TILE + q] = h.z;
-                sm.tile[3 * TILE + q] = 0.0;
-                sm.tile[4 * TILE + q] = 0.0;
-                sm.tile[5 * TILE + q] = 0.0;
+                sm.tile[0 * TS + q] = h.x;
+                sm.tile[1 * TS + q] = h.y;
+                sm.tile[2 * TS + q] = h.z;
+                sm.tile[3 * TS + q] = 0.0;
+                sm.tile[4 * TS + q] = 0.0;
+                sm.tile[5 * TS + q] = 0.0;
             }
             if constexpr (kContact) {
                 const unsigned mb = __ballot_sync(0xffffffffu, kind == KIND_BOND);
@@ -199,6 +236,8 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
                     if (kind == KIND_CONTACT) sm.heavy[TILE - 1 - (base_c + __popc(mc & lt))] = (uint16_t)q;
                 }
             }
+            j_cur = j_nxt;
+            t_cur = t_nxt;
         }
         __syncthreads();
 
@@ -209,7 +248,7 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
                 const bool is_bond = e < nB;
                 const int q = is_bond ? sm.heavy[e] : sm.heavy[TILE - 1 - (e - nB)];
                 const uint32_t p = tile_start + q;
-                const int r = find_row(sm.sptr, nrows, p);
+                const int r = sm.srow[q];
                 const int i = i0 + r;
                 const int j = A.cols[p];
                 const d3 xi = particle(r, 0), vi = particle(r, 1), wi = particle(r, 2);
@@ -248,33 +287,41 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
                     if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
                 }
                 if constexpr (kHamaker) {  // pair value = (contact | sinter)(i,j) + hamaker(i,j)
-                    sm.tile[0 * TILE + q] = c.a.x + sm.tile[0 * TILE + q];
-                    sm.tile[1 * TILE + q] = c.a.y + sm.tile[1 * TILE + q];
-                    sm.tile[2 * TILE + q] = c.a.z + sm.tile[2 * TILE + q];
+                    sm.tile[0 * TS + q] = c.a.x + sm.tile[0 * TS + q];
+                    sm.tile[1 * TS + q] = c.a.y + sm.tile[1 * TS + q];
+                    sm.tile[2 * TS + q] = c.a.z + sm.tile[2 * TS + q];
                 } else {
-                    sm.tile[0 * TILE + q] = c.a.x;
-                    sm.tile[1 * TILE + q] = c.a.y;
-                    sm.tile[2 * TILE + q] = c.a.z;
+                    sm.tile[0 * TS + q] = c.a.x;
+                    sm.tile[1 * TS + q] = c.a.y;
+                    sm.tile[2 * TS + q] = c.a.z;
                 }
-                sm.tile[3 * TILE + q] = c.alpha.x;
-                sm.tile[4 * TILE + q] = c.alpha.y;
-                sm.tile[5 * TILE + q] = c.alpha.z;
+                sm.tile[3 * TS + q] = c.alpha.x;
+                sm.tile[4 * TS + q] = c.alpha.y;
+                sm.tile[5 * TS + q] = c.alpha.z;
             }
             __syncthreads();
         }
 
-        // ---- phase C: ordered per-particle accumulation (ascending j) ----------------------------------------
-        if (tid < nrows) {
-            const uint32_t lo = max(sm.sptr[tid], tile_start);
-            const uint32_t hi = min(sm.sptr[tid + 1], tile_start + (uint32_t)cntp);
-            for (uint32_t p = lo; p < hi; p++) {
-                const int q = (int)(p - tile_start);
-                acc_a.x += sm.tile[0 * TILE + q];
-                acc_a.y += sm.tile[1 * TILE + q];
-                acc_a.z += sm.tile[2 * TILE + q];
-                acc_al.x += sm.tile[3 * TILE + q];
-                acc_al.y += sm.tile[4 * TILE + q];
-                acc_al.z += sm.tile[5 * TILE + q];
+        // ---- phase C: ordered accumulation (ascending j), one thread per (particle, component) ----------------
+        for (int wk = tid; wk < 6 * nrows; wk += TB) {
+            const int r = wk / 6, c = wk - 6 * r;
+            const uint32_t lo = max(sm.sptr[r], tile_start) - tile_start;
+            const uint32_t hi = min(sm.sptr[r + 1], tile_start + (uint32_t)cntp) - tile_start;
+            if (lo < hi && sm.sptr[r + 1] > tile_start) {
+                const double* t = sm.tile + c * TS;
+                double a = sm.acc[wk];
+                for (uint32_t q = lo; q < hi; q++) a += t[q];
+                sm.acc[wk] = a;
+            }
+        }
+        if (tile_start + TILE < p_end) {  // local-row map of the next tile (srow is not read in phase C)
+            const uint32_t nxt = tile_start + TILE;
+            if (tid < nrows) {
+                const uint32_t r0 = sm.sptr[tid], r1 = sm.sptr[tid + 1];
+                if (r1 > nxt && r0 < nxt + TILE) {
+                    const uint32_t lo = max(r0, nxt) - nxt, hi = min(r1 - nxt, (uint32_t)TILE);
+                    for (uint32_t q = lo; q < hi; q++) sm.srow[q] = (uint8_t)tid;
+                }
             }
         }
         if (tid == 0) sm.cnt[0] = sm.cnt[1] = 0;
@@ -285,10 +332,10 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
     double* out = sm.tile;  // [0,3R) [3R,6R) ... blocks of 3 * RMAX doubles
     constexpr int OB = 3 * RMAX;
     if (tid < nrows) {
-        const int i = i0 + tid;
         const d3 xi = particle(tid, 0), vi = particle(tid, 1), wi = particle(tid, 2);
-        if (A.n_facets > 0) {
-            const Accel u = unary_forces(A, i, xi, vi, wi);
+        d3 acc_a = load3(sm.acc + 6 * tid), acc_al = load3(sm.acc + 6 * tid + 3);
+        if constexpr (FACETS) {
+            const Accel u = unary_forces(A, i0 + tid, xi, vi, wi);
             acc_a += u.a;
             acc_al += u.alpha;
         }
@@ -319,7 +366,7 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
             A.x_next[gidx] = out[0 * OB + idx];
             A.v_next[gidx] = out[1 * OB + idx];
             A.w_next[gidx] = out[2 * OB + idx];
-            A.th[gidx] = A.th[gidx] + out[3 * OB + idx];
+            A.th[gidx] = sm.sth[idx] + out[3 * OB + idx];
         }
     }
     if constexpr (MODE == MODE_FUSED && kSinter) {
@@ -340,34 +387,44 @@ __global__ void __launch_bounds__(TB, 2) step_tiled_kernel(const __grid_constant
     }
 }
 
-template <int MASK, int MODE>
+template <int MASK, int MODE, bool FACETS>
 void launch_one(const ForceArgs& args, cudaStream_t st) {
     static bool configured = false;  // per instantiation
     if (!configured) {
-        cudaFuncSetAttribute(step_tiled_kernel<MASK, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Smem));
+        cudaFuncSetAttribute(step_tiled_kernel<MASK, MODE, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)sizeof(Smem));
         configured = true;
     }
     const int R = args.rows_per_block;
     const int blocks = (args.n + R - 1) / R;
-    step_tiled_kernel<MASK, MODE><<<blocks, TB, sizeof(Smem), st>>>(args);
+    step_tiled_kernel<MASK, MODE, FACETS><<<blocks, TB, sizeof(Smem), st>>>(args);
     g_launch_count++;
+}
+
+template <int MASK, int MODE>
+void launch_facets(const ForceArgs& args, cudaStream_t st) {
+    if (args.n_facets > 0)
+        launch_one<MASK, MODE, true>(args, st);
+    else
+        launch_one<MASK, MODE, false>(args, st);
 }
 
 template <int MODE>
 void launch_mode(const ForceArgs& args, int mask, cudaStream_t st) {
     switch (mask & (MODEL_CONTACT | MODEL_HAMAKER | MODEL_SINTER)) {
-        case MODEL_CONTACT: launch_one<MODEL_CONTACT, MODE>(args, st); break;
-        case MODEL_CONTACT | MODEL_HAMAKER: launch_one<MODEL_CONTACT | MODEL_HAMAKER, MODE>(args, st); break;
-        case MODEL_SINTER: launch_one<MODEL_SINTER, MODE>(args, st); break;
-        case MODEL_SINTER | MODEL_HAMAKER: launch_one<MODEL_SINTER | MODEL_HAMAKER, MODE>(args, st); break;
-        case MODEL_HAMAKER: launch_one<MODEL_HAMAKER, MODE>(args, st); break;
-        default: launch_one<0, MODE>(args, st); break;
+        case MODEL_CONTACT: launch_facets<MODEL_CONTACT, MODE>(args, st); break;
+        case MODEL_CONTACT | MODEL_HAMAKER: launch_facets<MODEL_CONTACT | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_SINTER: launch_facets<MODEL_SINTER, MODE>(args, st); break;
+        case MODEL_SINTER | MODEL_HAMAKER: launch_facets<MODEL_SINTER | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_HAMAKER: launch_facets<MODEL_HAMAKER, MODE>(args, st); break;
+        default: launch_facets<0, MODE>(args, st); break;
     }
 }
 
 }  // namespace
 
 int tiled_max_rows_per_block() { return RMAX; }
+int tiled_tile_pairs() { return TILE; }
 
 // fused == false: a, alpha <- forces at (x, v, omega)                    [MODE_FORCE]
 // fused == true : additionally integrates into x_next, v_next, w_next, th, bconn_next  [MODE_FUSED]

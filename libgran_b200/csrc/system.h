@@ -109,6 +109,7 @@ void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st)
 // tiled kernel: force only (fused == false) or force + integrate into the next-step buffers (fused == true)
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st);
 int tiled_max_rows_per_block();
+int tiled_tile_pairs();
 void launch_integrate(const IntegrateArgs& args, cudaStream_t st);
 void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, cudaStream_t st);
 

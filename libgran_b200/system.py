@@ -64,7 +64,8 @@ def load_library(path: Optional[str] = None):
     global _LIB
     if _LIB is not None and path is None:
         return _LIB
-    path = path or LIB_PATH
+    # LGB200_LIB selects an experimental build of the same ABI (kernel tuning sweeps); never a CPU path
+    path = path or os.environ.get("LGB200_LIB") or LIB_PATH
     if not os.path.exists(path):
         raise RuntimeError(
             f"{path} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
@@ -109,7 +110,7 @@ def load_library(path: Optional[str] = None):
         if name not in ("lg_last_error",):
             fn.restype = C.c_int if name != "lg_last_error" else C.c_char_p
     lib.lg_last_error.restype = C.c_char_p
-    if path == LIB_PATH:
+    if path == (os.environ.get("LGB200_LIB") or LIB_PATH):
         _LIB = lib
     return lib
 
