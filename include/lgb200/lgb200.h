@@ -109,6 +109,21 @@ int lg_build_sinter_bonds(lg_system* s, const lg_contact_params* contact, double
 int lg_set_bonds(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d, int64_t n_ordered,
                  const int64_t* ij_pairs, const double* connectors_15, const double* rest_lengths_5);
 
+/* The same construction split in two so that it can run where the reference runs it -- inside the
+ * sinter_functor constructor, before any system exists (test/sintered.cpp:106-107 builds the functor first,
+ * the system at :122-127).  lg_bond_table_create is pure host code (no CUDA device needed): it scans
+ * x (3 * n doubles) for bonds exactly like sinter_bridge.h:148-211 and consumes `gen` in the same order.
+ * lg_set_bond_table installs the result (with the embedded contact model, :134-135) into a system;
+ * lg_bond_table_records copies out 2 * count ordered records in the layout lg_set_bonds takes. */
+typedef struct lg_bond_table lg_bond_table;
+int lg_bond_table_create(int64_t n, const double* x_3n, double r_part, double critical_separation,
+                         lg_unit_vector_fn gen, void* user, lg_bond_table** out);
+int lg_bond_table_count(const lg_bond_table* t, int64_t* n_bonds);
+int lg_bond_table_records(const lg_bond_table* t, int64_t* ij_pairs, double* connectors_15, double* rest_lengths_5);
+int lg_bond_table_destroy(lg_bond_table* t);
+int lg_set_bond_table(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d,
+                      const lg_bond_table* t);
+
 /* Capacity of the per-particle table of simultaneously overlapping non-bonded neighbours
  * (replaces the dense N x N spring store of contact_force.h:53; default 16, kissing number is 12).
  * Must be called before the first step. Exceeding it at run time makes the step return LG_ECAPACITY. */
@@ -124,6 +139,9 @@ int lg_add_facet(lg_system* s, const double vertices_9[9], const double v_facet[
                  const lg_contact_params* surface_contact, int has_hamaker, double A, double h0, int* facet_id);
 /* triangular_facet::v_facet is a public data member (triangular_facet.h:69) */
 int lg_facet_set_velocity(lg_system* s, int facet_id, const double v_facet[3]);
+/* overwrite the three vertices (the header-template triangular_facet keeps its own host copy, moved by
+ * update_positions, and pushes it before every step) */
+int lg_facet_set_vertices(lg_system* s, int facet_id, const double vertices_9[9]);
 /* triangular_facet::update_positions(dt) (triangular_facet.h:62-66) */
 int lg_facet_update_positions(lg_system* s, int facet_id, double dt);
 /* triangular_facet::get_vertices() (:57-59) */

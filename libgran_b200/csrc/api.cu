@@ -412,6 +412,16 @@ struct HostBond {
     double len[5];
 };
 
+}  // namespace
+
+struct lg_bond_table {
+    int64_t n = 0;
+    int64_t bonds = 0;  // unordered
+    std::vector<HostBond> recs;  // ordered records, two per bond
+};
+
+namespace {
+
 int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
     // CSR by (i, j) ascending
     std::sort(recs.begin(), recs.end(), [](HostBond const& a, HostBond const& b) { return a.i != b.i ? a.i < b.i : a.j < b.j; });
@@ -459,6 +469,102 @@ int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
     // existing rows (if any) need their tags refreshed
     if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
     return LG_OK;
+}
+
+// Host-side restatement of the bond scan of sinter_functor's constructor (sinter_bridge.h:148-211) on a uniform
+// grid instead of the O(N^2) double loop; pairs are still visited in lexicographic (i < j) order so the
+// generator is consumed exactly like the reference.  Needs no GPU.
+static void scan_bonds(int64_t n, const std::vector<double>& hx, double r, double crit, lg_unit_vector_fn gen, void* user,
+                       std::vector<HostBond>& recs, int64_t& bonds) {
+    auto X = [&](int64_t i) { return mk3(hx[3 * (size_t)i], hx[3 * (size_t)i + 1], hx[3 * (size_t)i + 2]); };
+
+    // candidate partners j > i within 2r + crit (uniform host grid), visited in lexicographic order
+    // so that the generator is consumed exactly like the i < j double loop of sinter_bridge.h:148-149
+    const double range = 2.0 * r + crit;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int64_t i = 0; i < n; i++)
+        for (int k = 0; k < 3; k++) {
+            lo[k] = std::min(lo[k], hx[3 * (size_t)i + k]);
+            hi[k] = std::max(hi[k], hx[3 * (size_t)i + k]);
+        }
+    double cell = range * 1.0001;
+    int64_t dim[3];
+    for (;;) {
+        double total = 1.0;
+        for (int k = 0; k < 3; k++) {
+            double d = std::floor((hi[k] - lo[k]) / cell) + 1.0;
+            dim[k] = (int64_t)d;
+            total *= d;
+        }
+        if (total <= 16.0 * (double)n + 65536.0) break;
+        cell *= 1.26;
+    }
+    auto cell_of = [&](int64_t i, int64_t c[3]) {
+        for (int k = 0; k < 3; k++) {
+            int64_t t = (int64_t)std::floor((hx[3 * (size_t)i + k] - lo[k]) / cell);
+            c[k] = std::min(std::max<int64_t>(t, 0), dim[k] - 1);
+        }
+    };
+    const int64_t ncell = dim[0] * dim[1] * dim[2];
+    std::vector<int64_t> start((size_t)ncell + 1, 0), order((size_t)n), cidx((size_t)n);
+    for (int64_t i = 0; i < n; i++) {
+        int64_t c[3];
+        cell_of(i, c);
+        cidx[(size_t)i] = (c[0] * dim[1] + c[1]) * dim[2] + c[2];
+        start[(size_t)cidx[(size_t)i] + 1]++;
+    }
+    for (int64_t c = 0; c < ncell; c++) start[(size_t)c + 1] += start[(size_t)c];
+    {
+        std::vector<int64_t> cur(start.begin(), start.end() - 1);
+        for (int64_t i = 0; i < n; i++) order[(size_t)cur[(size_t)cidx[(size_t)i]]++] = i;  // ascending id inside a cell
+    }
+    std::vector<int64_t> cand;
+    bonds = 0;
+    for (int64_t i = 0; i < n - 1; i++) {
+        int64_t c[3];
+        cell_of(i, c);
+        cand.clear();
+        for (int64_t dx = -1; dx <= 1; dx++)
+            for (int64_t dy = -1; dy <= 1; dy++)
+                for (int64_t dz = -1; dz <= 1; dz++) {
+                    const int64_t cx = c[0] + dx, cy = c[1] + dy, cz = c[2] + dz;
+                    if (cx < 0 || cy < 0 || cz < 0 || cx >= dim[0] || cy >= dim[1] || cz >= dim[2]) continue;
+                    const int64_t cl = (cx * dim[1] + cy) * dim[2] + cz;
+                    for (int64_t q = start[(size_t)cl]; q < start[(size_t)cl + 1]; q++)
+                        if (order[(size_t)q] > i) cand.push_back(order[(size_t)q]);
+                }
+        std::sort(cand.begin(), cand.end());
+        const d3 part_i = X(i);
+        for (int64_t j : cand) {
+            const d3 part_j = X(j);
+            const double separation = norm(part_j - part_i) - 2.0 * r;
+            if (std::fabs(separation) > crit) continue;  // sinter_bridge.h:155-157
+            const d3 n_i = normalized(part_j - part_i);
+            const d3 n_j = -n_i;
+            d3 tv, db;
+            do {  // :171-175
+                double t[3];
+                gen(user, t);
+                tv = mk3(t[0], t[1], t[2]);
+                db = cross(tv, n_j);
+            } while (norm(db) == 0.0);
+            d3 ds = tv - dot(tv, n_i) * n_i;
+            db = db / sqrt(dot(db, db));
+            ds = ds / sqrt(dot(ds, ds));
+            HostBond bi{}, bjr{};
+            bi.i = i; bi.j = j; bjr.i = j; bjr.j = i;
+            const d3 ci[5] = {part_i + ds * r, part_i - ds * r, part_i + db * r, part_i - db * r, part_i + n_i * r};
+            const d3 cj[5] = {part_j + ds * r, part_j - ds * r, part_j + db * r, part_j - db * r, part_j + n_j * r};
+            for (int k = 0; k < 5; k++) {
+                store3(bi.conn + 3 * k, ci[k]);
+                store3(bjr.conn + 3 * k, cj[k]);
+                bi.len[k] = bjr.len[k] = (k < 4) ? 2.0 * r : 0.0;
+            }
+            recs.push_back(bi);
+            recs.push_back(bjr);
+            bonds++;
+        }
+    }
 }
 
 void to_cp(const lg_contact_params* p, ContactParams& c) {
@@ -671,105 +777,66 @@ int lg_build_sinter_bonds(lg_system* s, const lg_contact_params* contact, double
     if (!s->state_set) return fail(LG_EINVAL, "lg_set_state must precede lg_build_sinter_bonds");
     if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
     const int64_t n = s->n;
-    const double r = s->mp.r;
     std::vector<double> hx(3 * (size_t)n);
     LG_CUDA(cudaMemcpyAsync(hx.data(), s->x.p, hx.size() * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
-    auto X = [&](int64_t i) { return mk3(hx[3 * (size_t)i], hx[3 * (size_t)i + 1], hx[3 * (size_t)i + 2]); };
-
-    // candidate partners j > i within 2r + crit (uniform host grid), visited in lexicographic order
-    // so that the generator is consumed exactly like the i < j double loop of sinter_bridge.h:148-149
-    const double range = 2.0 * r + crit;
-    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-    for (int64_t i = 0; i < n; i++)
-        for (int k = 0; k < 3; k++) {
-            lo[k] = std::min(lo[k], hx[3 * (size_t)i + k]);
-            hi[k] = std::max(hi[k], hx[3 * (size_t)i + k]);
-        }
-    double cell = range * 1.0001;
-    int64_t dim[3];
-    for (;;) {
-        double total = 1.0;
-        for (int k = 0; k < 3; k++) {
-            double d = std::floor((hi[k] - lo[k]) / cell) + 1.0;
-            dim[k] = (int64_t)d;
-            total *= d;
-        }
-        if (total <= 16.0 * (double)n + 65536.0) break;
-        cell *= 1.26;
-    }
-    auto cell_of = [&](int64_t i, int64_t c[3]) {
-        for (int k = 0; k < 3; k++) {
-            int64_t t = (int64_t)std::floor((hx[3 * (size_t)i + k] - lo[k]) / cell);
-            c[k] = std::min(std::max<int64_t>(t, 0), dim[k] - 1);
-        }
-    };
-    const int64_t ncell = dim[0] * dim[1] * dim[2];
-    std::vector<int64_t> start((size_t)ncell + 1, 0), order((size_t)n), cidx((size_t)n);
-    for (int64_t i = 0; i < n; i++) {
-        int64_t c[3];
-        cell_of(i, c);
-        cidx[(size_t)i] = (c[0] * dim[1] + c[1]) * dim[2] + c[2];
-        start[(size_t)cidx[(size_t)i] + 1]++;
-    }
-    for (int64_t c = 0; c < ncell; c++) start[(size_t)c + 1] += start[(size_t)c];
-    {
-        std::vector<int64_t> cur(start.begin(), start.end() - 1);
-        for (int64_t i = 0; i < n; i++) order[(size_t)cur[(size_t)cidx[(size_t)i]]++] = i;  // ascending id inside a cell
-    }
     std::vector<HostBond> recs;
-    std::vector<int64_t> cand;
     int64_t bonds = 0;
-    for (int64_t i = 0; i < n - 1; i++) {
-        int64_t c[3];
-        cell_of(i, c);
-        cand.clear();
-        for (int64_t dx = -1; dx <= 1; dx++)
-            for (int64_t dy = -1; dy <= 1; dy++)
-                for (int64_t dz = -1; dz <= 1; dz++) {
-                    const int64_t cx = c[0] + dx, cy = c[1] + dy, cz = c[2] + dz;
-                    if (cx < 0 || cy < 0 || cz < 0 || cx >= dim[0] || cy >= dim[1] || cz >= dim[2]) continue;
-                    const int64_t cl = (cx * dim[1] + cy) * dim[2] + cz;
-                    for (int64_t q = start[(size_t)cl]; q < start[(size_t)cl + 1]; q++)
-                        if (order[(size_t)q] > i) cand.push_back(order[(size_t)q]);
-                }
-        std::sort(cand.begin(), cand.end());
-        const d3 part_i = X(i);
-        for (int64_t j : cand) {
-            const d3 part_j = X(j);
-            const double separation = norm(part_j - part_i) - 2.0 * r;
-            if (std::fabs(separation) > crit) continue;  // sinter_bridge.h:155-157
-            const d3 n_i = normalized(part_j - part_i);
-            const d3 n_j = -n_i;
-            d3 tv, db;
-            do {  // :171-175
-                double t[3];
-                gen(user, t);
-                tv = mk3(t[0], t[1], t[2]);
-                db = cross(tv, n_j);
-            } while (norm(db) == 0.0);
-            d3 ds = tv - dot(tv, n_i) * n_i;
-            db = db / sqrt(dot(db, db));
-            ds = ds / sqrt(dot(ds, ds));
-            HostBond bi{}, bjr{};
-            bi.i = i; bi.j = j; bjr.i = j; bjr.j = i;
-            const d3 ci[5] = {part_i + ds * r, part_i - ds * r, part_i + db * r, part_i - db * r, part_i + n_i * r};
-            const d3 cj[5] = {part_j + ds * r, part_j - ds * r, part_j + db * r, part_j - db * r, part_j + n_j * r};
-            for (int k = 0; k < 5; k++) {
-                store3(bi.conn + 3 * k, ci[k]);
-                store3(bjr.conn + 3 * k, cj[k]);
-                bi.len[k] = bjr.len[k] = (k < 4) ? 2.0 * r : 0.0;
-            }
-            recs.push_back(bi);
-            recs.push_back(bjr);
-            bonds++;
-        }
-    }
+    scan_bonds(n, hx, s->mp.r, crit, gen, user, recs, bonds);
     to_cp(contact, s->mp.cp);
     s->mp.k_d = k_d;
     s->mp.gamma_d = gamma_d;
     s->mask |= MODEL_SINTER;
     if (n_bonds_out) *n_bonds_out = bonds;
+    return install_bonds(s, recs);
+}
+
+int lg_bond_table_create(int64_t n, const double* x, double r_part, double crit, lg_unit_vector_fn gen, void* user,
+                         lg_bond_table** out) {
+    if (!out) return fail(LG_EINVAL, "out is null");
+    *out = nullptr;
+    if (n <= 0 || !x || !gen || !(r_part > 0.0)) return fail(LG_EINVAL, "bad arguments to lg_bond_table_create");
+    std::unique_ptr<lg_bond_table> t(new (std::nothrow) lg_bond_table());
+    if (!t) return fail(LG_ENOMEM, "host allocation failed");
+    t->n = n;
+    std::vector<double> hx(x, x + 3 * (size_t)n);
+    scan_bonds(n, hx, r_part, crit, gen, user, t->recs, t->bonds);
+    *out = t.release();
+    return LG_OK;
+}
+
+int lg_bond_table_count(const lg_bond_table* t, int64_t* n_bonds) {
+    if (!t || !n_bonds) return fail(LG_EINVAL, "null bond table");
+    *n_bonds = t->bonds;
+    return LG_OK;
+}
+
+int lg_bond_table_records(const lg_bond_table* t, int64_t* ij, double* conn, double* len) {
+    if (!t || !ij || !conn || !len) return fail(LG_EINVAL, "null bond table or output");
+    for (size_t b = 0; b < t->recs.size(); b++) {
+        ij[2 * b] = t->recs[b].i;
+        ij[2 * b + 1] = t->recs[b].j;
+        std::memcpy(conn + 15 * b, t->recs[b].conn, sizeof(t->recs[b].conn));
+        std::memcpy(len + 5 * b, t->recs[b].len, sizeof(t->recs[b].len));
+    }
+    return LG_OK;
+}
+
+int lg_bond_table_destroy(lg_bond_table* t) {
+    delete t;
+    return LG_OK;
+}
+
+int lg_set_bond_table(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d, const lg_bond_table* t) {
+    LG_ENTER(s);
+    if (!contact || !t) return fail(LG_EINVAL, "null contact params or bond table");
+    if (t->n != s->n) return fail(LG_ESIZE, "bond table was built for a different particle count");
+    if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
+    std::vector<HostBond> recs = t->recs;
+    to_cp(contact, s->mp.cp);
+    s->mp.k_d = k_d;
+    s->mp.gamma_d = gamma_d;
+    s->mask |= MODEL_SINTER;
     return install_bonds(s, recs);
 }
 
@@ -805,6 +872,14 @@ int lg_facet_set_velocity(lg_system* s, int id, const double v[3]) {
     LG_ENTER(s);
     if (id < 0 || id >= (int)s->facets.size() || !v) return fail(LG_EINVAL, "bad facet id");
     s->facets[(size_t)id].v = mk3(v[0], v[1], v[2]);
+    return LG_OK;
+}
+
+int lg_facet_set_vertices(lg_system* s, int id, const double vertices[9]) {
+    LG_ENTER(s);
+    if (id < 0 || id >= (int)s->facets.size() || !vertices) return fail(LG_EINVAL, "bad facet id");
+    Facet& f = s->facets[(size_t)id];
+    for (int k = 0; k < 3; k++) f.vtx[k] = mk3(vertices[3 * k], vertices[3 * k + 1], vertices[3 * k + 2]);
     return LG_OK;
 }
 

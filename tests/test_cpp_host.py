@@ -1,0 +1,145 @@
+"""The C++ header-template API (include/libgran/**, include/libtimestep/**) over the C ABI.
+
+* CPU: the driver of tests/cpp builds; the constructor's SizeMismatchException fires before any device work
+  (reference rotational_system.h:69-70); the host-only bond-table builder (sinter_functor's constructor,
+  reference sinter_bridge.h:148-211) gives the oracle's bonds bit for bit; where the reference checkout exists,
+  its five registered test drivers compile UNMODIFIED against these headers (-DLIBGRAN_B200_DROP_IN).
+* GPU: scenarios driven through the C++ templates equal the CPU oracle bit for bit; the reference's own drivers,
+  built against this backend, reach their hard-coded +-1 % targets (exit code 0).
+"""
+import ctypes as C
+import os
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+
+from libgran_b200 import scenarios as S
+
+from helpers import FIELDS, advance, unit_vectors_for
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CPP = os.path.join(HERE, "cpp")
+BUILD = os.path.join(CPP, "_build")
+DRIVER = os.path.join(BUILD, "template_driver")
+DROPIN = ["sintered", "hamaker_neighbor", "hamaker", "contact", "surface"]
+HAVE_REF = os.path.isdir("/root/reference/test")
+
+
+def build_driver():
+    subprocess.check_call(["make", "-C", CPP, "-s", "all"], stdout=subprocess.DEVNULL)
+    return DRIVER
+
+
+def write_case(path, scn, n_steps, move_facets, uv):
+    cfg = scn.cfg
+    uv = np.zeros((0, 3)) if uv is None else np.ascontiguousarray(uv, dtype=np.float64)
+    every = cfg.rebuild_every if cfg.use_neighbor_list else 0
+    with open(path, "wb") as f:
+        f.write(struct.pack("<7q", cfg.n, cfg.model_mask, int(cfg.use_neighbor_list), n_steps, every, int(move_facets), len(uv)))
+        dbl = [cfg.r_part, cfg.mass, cfg.inertia, cfg.r_verlet, cfg.dt, *cfg.contact, cfg.hamaker_A, cfg.hamaker_h0, cfg.k_d,
+               cfg.gamma_d, cfg.critical_separation, *np.asarray(cfg.facet_vertices, dtype=np.float64).reshape(-1), *cfg.facet_v,
+               *cfg.surf_contact, cfg.surf_A, cfg.surf_h0]
+        assert len(dbl) == 54
+        f.write(struct.pack("<54d", *dbl))
+        for a in scn.state:
+            f.write(np.ascontiguousarray(a, dtype=np.float64).tobytes())
+        f.write(uv.tobytes())
+
+
+def test_driver_builds_and_size_mismatch_throws(tmp_path, oracle):
+    drv = build_driver()
+    scn = S.slab_and_projectile(S.MODEL_CONTACT, neighbor_list=False)
+    case = str(tmp_path / "case.bin")
+    write_case(case, scn, 1, False, None)
+    res = subprocess.run([drv, case, str(tmp_path / "out.bin"), "--size-mismatch"], capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    assert "SizeMismatchException" in res.stdout
+
+
+def test_bond_table_host_builder_matches_oracle(lib, oracle):
+    """lg_bond_table_create needs no GPU: same bonds, connectors and rest lengths as the oracle's constructor."""
+    scn = S.aggregate()
+    cfg = scn.cfg
+    uv = unit_vectors_for(cfg, oracle)
+    x = np.ascontiguousarray(scn.x0, dtype=np.float64)
+    FN = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(C.c_double))
+    state = {"k": 0}
+
+    def cb(_user, out):
+        v = uv[state["k"]]
+        state["k"] += 1
+        out[0], out[1], out[2] = v
+
+    tbl = C.c_void_p()
+    lib.lg_bond_table_create.argtypes = [C.c_int64, C.c_void_p, C.c_double, C.c_double, FN, C.c_void_p, C.POINTER(C.c_void_p)]
+    rc = lib.lg_bond_table_create(cfg.n, x.ctypes.data, cfg.r_part, cfg.critical_separation, FN(cb), None, C.byref(tbl))
+    assert rc == 0
+    nb = C.c_int64()
+    lib.lg_bond_table_count.argtypes = [C.c_void_p, C.POINTER(C.c_int64)]
+    assert lib.lg_bond_table_count(tbl, C.byref(nb)) == 0
+    cpu = oracle.OracleSystem(cfg, *scn.state)
+    assert 2 * nb.value == cpu.n_bonds() == 300  # aggregate.h has 150 bonds (oracle counts ordered)
+    ij = np.zeros((2 * nb.value, 2), dtype=np.int64)
+    conn = np.zeros((2 * nb.value, 15))
+    ln = np.zeros((2 * nb.value, 5))
+    lib.lg_bond_table_records.argtypes = [C.c_void_p] * 4
+    assert lib.lg_bond_table_records(tbl, ij.ctypes.data, conn.ctypes.data, ln.ctypes.data) == 0
+    for b in range(len(ij)):
+        ref = cpu.bond(int(ij[b, 0]), int(ij[b, 1]))
+        assert ref is not None
+        c_ref, l_ref = ref
+        assert np.array_equal(np.asarray(c_ref).reshape(-1), conn[b]) and np.array_equal(np.asarray(l_ref).reshape(-1), ln[b])
+    lib.lg_bond_table_destroy.argtypes = [C.c_void_p]
+    lib.lg_bond_table_destroy(tbl)
+
+
+@pytest.mark.skipif(not HAVE_REF, reason="reference checkout not present (GPU box)")
+def test_reference_drivers_compile_unmodified():
+    """`granular_system` -> this backend with zero source edits: the reference's registered test drivers
+    (CMakeLists.txt:78-83) are compiled where they lie with -DLIBGRAN_B200_DROP_IN and this repo's include/ first."""
+    subprocess.check_call(["make", "-C", CPP, "-s", "-j8", "dropin"], stdout=subprocess.DEVNULL)
+    for name in DROPIN:
+        assert os.path.exists(os.path.join(BUILD, "dropin", name + "_b200"))
+
+
+CASES = [
+    ("slab c allpairs", lambda: S.slab_and_projectile(S.MODEL_CONTACT, False), 400, False),
+    ("slab c+h nl", lambda: S.slab_and_projectile(S.MODEL_CONTACT | S.MODEL_HAMAKER, True), 400, False),
+    ("lattice s allpairs", lambda: S.sintered_lattice(), 400, False),
+    ("aggregate s+h nl", lambda: S.aggregate(), 200, False),
+    ("surface drop", lambda: S.surface_drop(), 400, False),
+    ("stress s+h+f nl", lambda: S.stress_block(models=S.MODEL_SINTER | S.MODEL_HAMAKER | S.MODEL_FACET), 150, True),
+    ("stress c+h+f nl", lambda: S.stress_block(models=S.MODEL_CONTACT | S.MODEL_HAMAKER | S.MODEL_FACET), 150, True),
+]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,make,steps,moves", CASES, ids=[c[0] for c in CASES])
+def test_cpp_templates_match_oracle(tmp_path, oracle, name, make, steps, moves):
+    drv = build_driver() if not os.path.exists(DRIVER) else DRIVER
+    scn = make()
+    cfg = scn.cfg
+    case, out = str(tmp_path / "case.bin"), str(tmp_path / "out.bin")
+    write_case(case, scn, steps, moves, unit_vectors_for(cfg, oracle))
+    res = subprocess.run([drv, case, out], capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr
+    got = np.fromfile(out, dtype=np.float64).reshape(6, cfg.n, 3)
+    cpu = oracle.OracleSystem(cfg, *scn.state)
+    advance(cpu, cfg, 0, steps, moves)
+    for k, f in enumerate(("x", "v", "theta", "omega", "a", "alpha")):
+        assert np.array_equal(got[k], cpu.get(f)), f"{name}: {f} differs from the oracle"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", DROPIN)
+def test_reference_driver_reaches_its_targets_on_gpu(name):
+    """The reference's own known-answer tests (hard-coded targets at +-1 %: test/sintered.cpp:144-145,
+    test/hamaker_neighbor.cpp:129-131, test/hamaker.cpp:127-129, test/contact.cpp:111-112, test/surface.cpp:117),
+    unmodified sources, running on the CUDA backend.  Built by `make -C tests/cpp dropin` in the build container."""
+    exe = os.path.join(BUILD, "dropin", name + "_b200")
+    if not os.path.exists(exe):
+        pytest.skip("drop-in binaries were not built (no reference checkout at build time)")
+    res = subprocess.run([exe], capture_output=True, text=True, timeout=900)
+    assert res.returncode == 0, f"{name}: exit {res.returncode}\n{res.stdout[-500:]}\n{res.stderr[-500:]}"
