@@ -199,6 +199,41 @@ int lg_get_counters(lg_system* s, int64_t out_8[8]);
  *   out[5..7] centre of mass      out[8] radius of gyration */
 int lg_diagnostics(lg_system* s, double out_9[9]);
 
+/* ---- slab decomposition (no reference counterpart -- the reference is single-process) ----
+ * One lg_system per rank holds that rank's owned particles and its ghosts, ordered by global particle id.  The
+ * functions below move device-resident tables in and out of a system (d_* = device pointers on its device) so that
+ * the launcher (libgran_b200/slab.py, or any C++ host with its own transport) can repartition and exchange halos. */
+
+/* Materialises a pending closing force evaluation so that a, alpha and the contact
+ * springs correspond to the current x, v, omega. */
+int lg_flush(lg_system* s);
+/* First half of the very first do_step (rotational_velocity_verlet_half.h:45-57): evaluate, then v -= a dt/2,
+ * omega -= alpha dt/2 for the particles with rows.  The caller refreshes ghost v, omega and then calls lg_do_step,
+ * which resumes at the second evaluation (:59). */
+int lg_first_half_kick(lg_system* s, double dt);
+/* lg_set_state from device memory, including a and alpha (nullable = zero) and the integrator phase:
+ * kicked != 0 means the first-step half kick has already been applied to this state. */
+int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, const double* d_theta,
+                           const double* d_omega, const double* d_a, const double* d_alpha, int kicked);
+/* n bytes: 1 = owned (gets neighbor rows, is integrated by force), 0 = ghost (rows stay empty).  NULL clears. */
+int lg_set_owned_device(lg_system* s, const uint8_t* d_owned);
+/* The sparse contact-spring table: S slots per particle; sgid[i*S+k] = partner index or -1, spr[(i*S+k)*9..]. */
+int lg_export_slots(lg_system* s, int* S, int32_t** d_sgid, double** d_spr);
+int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_spr);
+/* The bond CSR (rows ascending in partner index): bptr[n+1], bj[nb], connectors[nb][15], rest lengths[nb][5];
+ * brev[b] = record index of the mirror (j, i), or b itself when the mirror is not held locally. */
+int lg_export_bonds(lg_system* s, int64_t* n_ordered, uint32_t** d_bptr, int32_t** d_bj, double** d_bconn,
+                    double** d_blen);
+int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d,
+                           int64_t n_ordered, const uint32_t* d_bptr, const int32_t* d_bj, const int32_t* d_brev,
+                           const double* d_bconn, const double* d_blen);
+/* Halo staging on the system's stream: gathers x, v, omega of particles d_idx[0..n_part) (9 doubles each) followed
+ * by the connector blocks of bond records d_rec[0..n_rec) (15 doubles each) into d_out; unpack scatters the same
+ * layout into the ghost slots. */
+int lg_halo_pack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec, double* d_out);
+int lg_halo_unpack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec,
+                   const double* d_in);
+
 /* The CUDA stream (cudaStream_t) all work of this system is queued on, so that callers can time it with
  * events or order their own copies against it. */
 int lg_get_stream(lg_system* s, void** stream);

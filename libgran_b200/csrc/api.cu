@@ -103,6 +103,9 @@ struct lg_system {
     DevBuf<double> a, th, al;  // private to their particle -> single
     bool state_set = false;
     bool kicked = false;
+    bool half_kicked = false;  // lg_first_half_kick ran: the first do_step resumes at its second evaluation
+    DevBuf<uint8_t> owned;     // slab decomposition: 1 = owned, 0 = ghost (rows stay empty); unused when !has_owned
+    bool has_owned = false;
     // Lazy evaluation (variant 1): the reference ends do_step with a force evaluation at the new state
     // (rotational_velocity_verlet_half.h:75); the fused kernel performs that evaluation at the START of the
     // next step instead.  `pending` means a, alpha (and the contact springs) have not yet been advanced to
@@ -322,11 +325,14 @@ int integrate_in_place(lg_system* s, double dt) {
 int step(lg_system* s, double dt) {
     if (!s->kicked) {
         // first call: evaluate, half kick back, evaluate again (rotational_velocity_verlet_half.h:45-60)
-        LG_TRY(evaluate(s, s->facets));
-        launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
-        LG_CUDA(cudaGetLastError());
+        if (!s->half_kicked) {
+            LG_TRY(evaluate(s, s->facets));
+            launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
+            LG_CUDA(cudaGetLastError());
+        }
         LG_TRY(evaluate(s, s->facets));
         s->kicked = true;
+        s->half_kicked = false;
         s->pending = false;
     }
     if (s->variant == 0) {
@@ -390,7 +396,8 @@ int rebuild(lg_system* s) {
     launch_exclusive_scan_u32(s->cell_start.p, nc1, s->scan_scratch.p, st);
     launch_cell_fill(n, s->cell_of.p, s->cell_start.p, s->cell_cursor.p, s->order.p, st);
     // 3. rows: count, scan, fill + sort
-    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, st);
+    const uint8_t* owned = s->has_owned ? s->owned.p : nullptr;
+    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, owned, st);
     LG_CUDA(cudaMemsetAsync(s->row_ptr.p + n, 0, sizeof(uint32_t), st));
     launch_exclusive_scan_u32(s->row_ptr.p, (size_t)n + 1, s->scan_scratch.p, st);
     LG_CUDA(cudaGetLastError());
@@ -399,7 +406,7 @@ int rebuild(lg_system* s) {
     LG_CUDA(cudaStreamSynchronize(st));
     s->n_pairs = (int64_t)total_pairs;
     LG_TRY(ensure_pair_capacity(s, s->n_pairs));
-    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, s->cols.p, st);
+    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, s->cols.p, owned, st);
     LG_CUDA(cudaGetLastError());
     s->rebuilds++;
     return retag(s);
@@ -702,6 +709,7 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     LG_CUDA(cudaStreamSynchronize(s->stream));  // the caller may reuse its buffers
     s->state_set = true;
     s->kicked = false;
+    s->half_kicked = false;
     s->pending = false;
     return LG_OK;
 }
@@ -1062,6 +1070,149 @@ int lg_diagnostics(lg_system* s, double out[9]) {
     out[6] = com[1];
     out[7] = com[2];
     out[8] = std::sqrt(h[0] / (double)n);
+    return LG_OK;
+}
+
+// ---- slab decomposition support ------------------------------------------------------
+int lg_flush(lg_system* s) {
+    LG_ENTER(s);
+    if (!s->state_set) return LG_OK;
+    return flush(s);
+}
+
+int lg_first_half_kick(lg_system* s, double dt) {
+    LG_ENTER(s);
+    LG_TRY(prepare(s));
+    if (s->kicked || s->half_kicked) return LG_OK;
+    LG_TRY(evaluate(s, s->facets));
+    launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
+    LG_CUDA(cudaGetLastError());
+    s->half_kicked = true;
+    return LG_OK;
+}
+
+int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, const double* d_theta, const double* d_omega,
+                           const double* d_a, const double* d_alpha, int kicked) {
+    LG_ENTER(s);
+    if (!d_x || !d_v || !d_theta || !d_omega) return fail(LG_EINVAL, "null state pointer");
+    const size_t bytes = 3 * (size_t)s->n * sizeof(double);
+    cudaStream_t st = s->stream;
+    LG_CUDA(cudaMemcpyAsync(s->x.p, d_x, bytes, cudaMemcpyDeviceToDevice, st));
+    LG_CUDA(cudaMemcpyAsync(s->v.p, d_v, bytes, cudaMemcpyDeviceToDevice, st));
+    LG_CUDA(cudaMemcpyAsync(s->th.p, d_theta, bytes, cudaMemcpyDeviceToDevice, st));
+    LG_CUDA(cudaMemcpyAsync(s->w.p, d_omega, bytes, cudaMemcpyDeviceToDevice, st));
+    if (d_a) LG_CUDA(cudaMemcpyAsync(s->a.p, d_a, bytes, cudaMemcpyDeviceToDevice, st)); else LG_CUDA(cudaMemsetAsync(s->a.p, 0, bytes, st));
+    if (d_alpha) LG_CUDA(cudaMemcpyAsync(s->al.p, d_alpha, bytes, cudaMemcpyDeviceToDevice, st)); else LG_CUDA(cudaMemsetAsync(s->al.p, 0, bytes, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    s->state_set = true;
+    s->kicked = kicked != 0;
+    s->half_kicked = false;
+    s->pending = false;
+    return LG_OK;
+}
+
+int lg_set_owned_device(lg_system* s, const uint8_t* d_owned) {
+    LG_ENTER(s);
+    if (!d_owned) {
+        s->has_owned = false;
+        return LG_OK;
+    }
+    LG_CUDA(s->owned.reserve((size_t)s->n));
+    LG_CUDA(cudaMemcpyAsync(s->owned.p, d_owned, (size_t)s->n, cudaMemcpyDeviceToDevice, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    s->has_owned = true;
+    return LG_OK;
+}
+
+int lg_export_slots(lg_system* s, int* S, int32_t** d_sgid, double** d_spr) {
+    LG_ENTER(s);
+    if (!S || !d_sgid || !d_spr) return fail(LG_EINVAL, "null output");
+    LG_TRY(ensure_slots(s));
+    LG_TRY(flush(s));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    *S = s->S;
+    *d_sgid = s->sgid.p;
+    *d_spr = s->spr.p;
+    return LG_OK;
+}
+
+int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_spr) {
+    LG_ENTER(s);
+    if (!d_sgid || !d_spr) return fail(LG_EINVAL, "null slot tables");
+    LG_TRY(ensure_slots(s));
+    const size_t cells = (size_t)s->n * (size_t)s->S;
+    LG_CUDA(cudaMemcpyAsync(s->sgid.p, d_sgid, cells * sizeof(int32_t), cudaMemcpyDeviceToDevice, s->stream));
+    LG_CUDA(cudaMemcpyAsync(s->spr.p, d_spr, cells * 9 * sizeof(double), cudaMemcpyDeviceToDevice, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
+    return LG_OK;
+}
+
+int lg_export_bonds(lg_system* s, int64_t* n_ordered, uint32_t** d_bptr, int32_t** d_bj, double** d_bconn, double** d_blen) {
+    LG_ENTER(s);
+    if (!n_ordered || !d_bptr || !d_bj || !d_bconn || !d_blen) return fail(LG_EINVAL, "null output");
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    *n_ordered = s->n_bonds;
+    *d_bptr = s->bptr.p;
+    *d_bj = s->bj.p;
+    *d_bconn = s->bconn.p;
+    *d_blen = s->blen.p;
+    return LG_OK;
+}
+
+int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d, int64_t nb,
+                           const uint32_t* d_bptr, const int32_t* d_bj, const int32_t* d_brev, const double* d_bconn,
+                           const double* d_blen) {
+    LG_ENTER(s);
+    if (!contact || nb < 0 || !d_bptr || (nb > 0 && (!d_bj || !d_brev || !d_bconn || !d_blen)))
+        return fail(LG_EINVAL, "bad bond arguments");
+    if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
+    const size_t n = (size_t)s->n;
+    cudaStream_t st = s->stream;
+    LG_CUDA(s->bptr.reserve(n + 1));
+    LG_CUDA(s->bj.reserve((size_t)nb + 16));
+    LG_CUDA(s->brev.reserve((size_t)nb + 16));
+    LG_CUDA(s->bconn.reserve((size_t)nb * 15 + 16));
+    LG_CUDA(s->blen.reserve((size_t)nb * 5 + 16));
+    LG_CUDA(cudaMemcpyAsync(s->bptr.p, d_bptr, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    std::vector<uint32_t> bptr(n + 1);
+    std::vector<int32_t> bj((size_t)nb);
+    LG_CUDA(cudaMemcpyAsync(bptr.data(), d_bptr, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    if (nb) {
+        LG_CUDA(cudaMemcpyAsync(s->bj.p, d_bj, (size_t)nb * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+        LG_CUDA(cudaMemcpyAsync(s->brev.p, d_brev, (size_t)nb * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+        LG_CUDA(cudaMemcpyAsync(s->bconn.p, d_bconn, (size_t)nb * 15 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+        LG_CUDA(cudaMemcpyAsync(s->blen.p, d_blen, (size_t)nb * 5 * sizeof(double), cudaMemcpyDeviceToDevice, st));
+        LG_CUDA(cudaMemcpyAsync(bj.data(), d_bj, (size_t)nb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    }
+    LG_CUDA(cudaStreamSynchronize(st));
+    if (bptr[n] != (uint32_t)nb) return fail(LG_EINVAL, "bptr[n] does not match the number of bond records");
+    for (size_t i = 0; i < n; i++)
+        if (bptr[i + 1] - bptr[i] > (uint32_t)kMaxBondsPerParticle) return fail(LG_ECAPACITY, "more than 120 bonds on one particle");
+    to_cp(contact, s->mp.cp);
+    s->mp.k_d = k_d;
+    s->mp.gamma_d = gamma_d;
+    s->mask |= MODEL_SINTER;
+    s->n_bonds = nb;
+    s->h_bptr = std::move(bptr);
+    s->h_bj = std::move(bj);
+    if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
+    return LG_OK;
+}
+
+int lg_halo_pack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec, double* d_out) {
+    LG_ENTER(s);
+    if (n_part < 0 || n_rec < 0 || (n_part > 0 && !d_idx) || (n_rec > 0 && !d_rec) || !d_out) return fail(LG_EINVAL, "bad halo arguments");
+    launch_halo_pack(n_part, d_idx, n_rec, d_rec, s->x.p, s->v.p, s->w.p, s->bconn.p, d_out, s->stream);
+    LG_CUDA(cudaGetLastError());
+    return LG_OK;
+}
+
+int lg_halo_unpack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec, const double* d_in) {
+    LG_ENTER(s);
+    if (n_part < 0 || n_rec < 0 || (n_part > 0 && !d_idx) || (n_rec > 0 && !d_rec) || !d_in) return fail(LG_EINVAL, "bad halo arguments");
+    launch_halo_unpack(n_part, d_idx, n_rec, d_rec, s->x.p, s->v.p, s->w.p, s->bconn.p, d_in, s->stream);
+    LG_CUDA(cudaGetLastError());
     return LG_OK;
 }
 

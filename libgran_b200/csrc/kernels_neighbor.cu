@@ -233,9 +233,13 @@ __device__ __forceinline__ bool within_verlet(d3 xi, d3 xj, double r_verlet) {
 template <bool FILL>
 __global__ void __launch_bounds__(128)
     row_sweep_kernel(int n, const double* x, const NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                     double r_verlet, uint32_t* row_count, const uint32_t* row_ptr, int32_t* cols) {
+                     double r_verlet, uint32_t* row_count, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (owned != nullptr && !owned[i]) {  // ghost particle (slab decomposition): its forces belong to another rank
+        if (!FILL) row_count[i] = 0u;
+        return;
+    }
     const d3 xi = load3(x + 3 * (size_t)i);
     int c[3];
     cell_coords(g, xi, c);
@@ -279,14 +283,15 @@ __global__ void __launch_bounds__(128)
 }
 
 void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                      double r_verlet, uint32_t* row_count, cudaStream_t st) {
+                      double r_verlet, uint32_t* row_count, const uint8_t* owned, cudaStream_t st) {
     row_sweep_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, row_count, nullptr,
-                                                             nullptr);
+                                                             nullptr, owned);
     g_launch_count++;
 }
 void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, cudaStream_t st) {
-    row_sweep_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, nullptr, row_ptr, cols);
+                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned, cudaStream_t st) {
+    row_sweep_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, nullptr, row_ptr, cols,
+                                                            owned);
     g_launch_count++;
 }
 

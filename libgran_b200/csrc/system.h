@@ -123,9 +123,9 @@ void launch_cell_count(int n, const double* x, NeighborGrid g, int32_t* cell_of,
 void launch_cell_fill(int n, const int32_t* cell_of, const uint32_t* cell_start, uint32_t* cell_cursor, int32_t* order,
                       cudaStream_t st);
 void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                      double r_verlet, uint32_t* row_count, cudaStream_t st);
+                      double r_verlet, uint32_t* row_count, const uint8_t* owned, cudaStream_t st);
 void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, cudaStream_t st);
+                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned, cudaStream_t st);
 void launch_allpairs_fill(int n, uint32_t* row_ptr, int32_t* cols, cudaStream_t st);
 // recompute tag[] for every row from the slot table and the bond CSR; frees slots whose partner left the row
 void launch_retag(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
@@ -135,5 +135,11 @@ void launch_count_slots(int n, const int32_t* sgid, int S, unsigned long long* d
 // out[16]: sums for lg_diagnostics (pass 0) ; pass 1 adds sum |x - com|^2
 void launch_diag_sums(int n, const double* x, const double* v, const double* w, double mass, double inertia,
                       const double* com, double* d_partials, double* d_out, int pass, cudaStream_t st);
+
+// slab decomposition: ghost staging (kernels_halo.cu)
+void launch_halo_pack(int n_part, const int32_t* idx, int n_rec, const int32_t* rec, const double* x, const double* v,
+                      const double* w, const double* bconn, double* out, cudaStream_t st);
+void launch_halo_unpack(int n_part, const int32_t* idx, int n_rec, const int32_t* rec, double* x, double* v, double* w,
+                        double* bconn, const double* in, cudaStream_t st);
 
 }  // namespace lg

@@ -29,6 +29,11 @@ ABI_SYMBOLS = (
     "lg_update_neighbor_list", "lg_do_step", "lg_run", "lg_reset_acceleration_buffers", "lg_synchronize",
     "lg_get_neighbor_count", "lg_get_neighbor_rows", "lg_get_contact_springs", "lg_get_bond", "lg_get_counters",
     "lg_diagnostics", "lg_set_kernel_variant", "lg_get_stream", "lg_set_profiling", "lg_get_profile",
+    "lg_bond_table_create", "lg_bond_table_count", "lg_bond_table_records", "lg_bond_table_destroy", "lg_set_bond_table",
+    "lg_facet_set_vertices",
+    # slab decomposition support
+    "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
+    "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
 )
 
 
@@ -105,6 +110,23 @@ def load_library(path: Optional[str] = None):
     lib.lg_get_stream.argtypes = [vp, C.POINTER(vp)]
     lib.lg_set_profiling.argtypes = [vp, C.c_int]
     lib.lg_get_profile.argtypes = [vp, dp, ip]
+    lib.lg_bond_table_create.argtypes = [C.c_int64, vp, C.c_double, C.c_double, UNIT_VECTOR_FN, vp, C.POINTER(vp)]
+    lib.lg_bond_table_count.argtypes = [vp, ip]
+    lib.lg_bond_table_records.argtypes = [vp, vp, vp, vp]
+    lib.lg_bond_table_destroy.argtypes = [vp]
+    lib.lg_set_bond_table.argtypes = [vp, cpp, C.c_double, C.c_double, vp]
+    lib.lg_facet_set_vertices.argtypes = [vp, C.c_int, dp]
+    # slab decomposition support: device pointers travel as plain integers
+    lib.lg_flush.argtypes = [vp]
+    lib.lg_first_half_kick.argtypes = [vp, C.c_double]
+    lib.lg_import_state_device.argtypes = [vp, vp, vp, vp, vp, vp, vp, C.c_int]
+    lib.lg_set_owned_device.argtypes = [vp, vp]
+    lib.lg_export_slots.argtypes = [vp, C.POINTER(C.c_int), C.POINTER(vp), C.POINTER(vp)]
+    lib.lg_import_slots_device.argtypes = [vp, vp, vp]
+    lib.lg_export_bonds.argtypes = [vp, ip, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp)]
+    lib.lg_import_bonds_device.argtypes = [vp, cpp, C.c_double, C.c_double, C.c_int64, vp, vp, vp, vp, vp]
+    lib.lg_halo_pack.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp]
+    lib.lg_halo_unpack.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp]
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("lg_last_error",):
