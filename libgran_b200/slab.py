@@ -1,0 +1,380 @@
+"""1-D slab decomposition of a granular system over several GPUs.
+
+One process per GPU.  ``torch.distributed`` is the plumbing (NCCL between GPUs, gloo in the CPU tests); every
+per-particle computation stays in the CUDA library behind the C ABI.  The reference has no distributed path, so
+nothing here restates reference code; what must hold is that a decomposed run returns the *same bits* as the
+single-GPU run, which it does because each rank keeps its local particles ordered by global id (ascending local
+neighbor index == ascending global index == the reference's accumulation order).
+
+Layout of this module
+  * plan functions (pure torch, any device, any backend): slab bounds, owners, ghost destinations, the record
+    streams that move particles between ranks, re-localisation of what arrived, halo request lists.  They are
+    what tests/test_slab_plan.py drives on CPU tensors with gloo, world_size 2.
+  * ``SlabSystem``: the GPU driver -- owns one ``lg_system`` per rank, repartitions when particles have moved more
+    than half the skin, exchanges ghost x, v, omega and bond connectors after every step.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Dict, List, Optional, Tuple
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+# columns of the three record streams (all float64 rows; integer columns are int64 bit patterns)
+P_INT, P_DBL = 3, 18   # gid, kind (0 owned / 1 ghost), new owner rank | x v theta omega a alpha
+B_INT, B_DBL = 2, 20   # gid_i, gid_j | 5 connectors of i (15), 5 rest lengths
+C_INT, C_DBL = 2, 9    # gid_i, gid_j | 3 history springs of the ordered pair (i, j)
+
+
+# =================================================================================================
+# small helpers
+# =================================================================================================
+def _i2f(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.int64).contiguous().view(torch.float64)
+
+
+def _f2i(t: torch.Tensor) -> torch.Tensor:
+    return t.contiguous().view(torch.int64)
+
+
+def ragged_expand(starts: torch.Tensor, counts: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """For segments [starts[k], starts[k] + counts[k]) return (segment id, element index) of every element."""
+    counts = counts.to(torch.int64)
+    total = int(counts.sum())
+    dev = counts.device
+    if total == 0:
+        z = torch.zeros(0, dtype=torch.int64, device=dev)
+        return z, z.clone()
+    seg = torch.repeat_interleave(torch.arange(len(counts), device=dev), counts)
+    first = torch.cumsum(counts, 0) - counts
+    offs = torch.arange(total, device=dev) - first[seg]
+    return seg, starts.to(torch.int64)[seg] + offs
+
+
+def lookup_sorted(sorted_keys: torch.Tensor, query: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Positions of `query` in ascending `sorted_keys` and a mask of the ones actually present."""
+    if len(sorted_keys) == 0:
+        return torch.zeros_like(query), torch.zeros_like(query, dtype=torch.bool)
+    pos = torch.searchsorted(sorted_keys, query)
+    pos_c = pos.clamp(max=len(sorted_keys) - 1)
+    return pos_c, sorted_keys[pos_c] == query
+
+
+# =================================================================================================
+# plan: who owns what, who needs which ghosts
+# =================================================================================================
+def slab_bounds(coord_owned: torch.Tensor, world: int, group=None) -> torch.Tensor:
+    """Inner slab boundaries (world - 1 values) at particle-count quantiles of the slab-axis coordinate of ALL
+    particles.  Every rank passes the coordinates of the particles it currently owns and gets identical bounds."""
+    dev = coord_owned.device
+    if world == 1:
+        return torch.zeros(0, dtype=torch.float64, device=dev)
+    counts = torch.zeros(world, dtype=torch.int64, device=dev)
+    mine = torch.tensor([len(coord_owned)], dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(counts, mine, group=group)
+    cmax = int(counts.max())
+    padded = torch.full((cmax,), float("inf"), dtype=torch.float64, device=dev)
+    padded[: len(coord_owned)] = coord_owned
+    everything = torch.empty(world * cmax, dtype=torch.float64, device=dev)
+    dist.all_gather_into_tensor(everything, padded, group=group)
+    xs, _ = torch.sort(everything)  # the +inf padding sorts to the end
+    n = int(counts.sum())
+    cuts = [(k * n) // world for k in range(1, world)]
+    idx = torch.tensor(cuts, dtype=torch.int64, device=dev).clamp(1, max(n - 1, 1))
+    return 0.5 * (xs[idx - 1] + xs[idx])
+
+
+def owner_of(coord: torch.Tensor, inner_bounds: torch.Tensor) -> torch.Tensor:
+    """Rank owning each coordinate: the number of inner bounds <= coord."""
+    if len(inner_bounds) == 0:
+        return torch.zeros(len(coord), dtype=torch.int64, device=coord.device)
+    return torch.bucketize(coord, inner_bounds, right=True)
+
+
+def ghost_destinations(coord: torch.Tensor, owner: torch.Tensor, inner_bounds: torch.Tensor, r_ghost: float,
+                       world: int) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(particle index, rank) for every rank other than the owner whose slab, widened by r_ghost on both sides,
+    contains the particle."""
+    dev = coord.device
+    if world == 1 or len(coord) == 0:
+        z = torch.zeros(0, dtype=torch.int64, device=dev)
+        return z, z.clone()
+    ninf = torch.tensor([-float("inf")], dtype=torch.float64, device=dev)
+    pinf = torch.tensor([float("inf")], dtype=torch.float64, device=dev)
+    lo = torch.cat([ninf, inner_bounds]) - r_ghost   # [world]
+    hi = torch.cat([inner_bounds, pinf]) + r_ghost
+    inside = (coord[:, None] >= lo[None, :]) & (coord[:, None] < hi[None, :])
+    inside[torch.arange(len(coord), device=dev), owner] = False
+    p, r = torch.nonzero(inside, as_tuple=True)
+    return p, r
+
+
+def all_to_all_rows(rows: torch.Tensor, dest: torch.Tensor, world: int, group=None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Send row k of `rows` (float64 [m, c]) to rank dest[k]; returns the rows received (grouped by source rank in
+    rank order, each group in the sender's order) and the source rank of every received row."""
+    dev = rows.device
+    order = torch.argsort(dest, stable=True)
+    rows = rows[order].contiguous()
+    send_counts = torch.bincount(dest, minlength=world).to(torch.int64)
+    recv_counts = torch.empty_like(send_counts)
+    if world == 1:
+        return rows, torch.zeros(len(rows), dtype=torch.int64, device=dev)
+    dist.all_to_all_single(recv_counts, send_counts, group=group)
+    sc, rc = send_counts.tolist(), recv_counts.tolist()
+    out = torch.empty((sum(rc), rows.shape[1]), dtype=rows.dtype, device=dev)
+    dist.all_to_all_single(out, rows, rc, sc, group=group)
+    src = torch.repeat_interleave(torch.arange(world, device=dev), recv_counts)
+    return out, src
+
+
+# =================================================================================================
+# local tables and the record streams that move them
+# =================================================================================================
+@dataclass
+class LocalTables:
+    """Everything one rank holds, in local order (ascending global id).  Pure data, any device."""
+
+    gid: torch.Tensor      # int64 [n]
+    owned: torch.Tensor    # bool  [n]
+    src: torch.Tensor      # int64 [n]  rank the record came from (the owner, for ghosts)
+    state: torch.Tensor    # float64 [n, 18]  x v theta omega a alpha
+    S: int
+    sgid: torch.Tensor     # int32 [n, S]  local partner index or -1
+    spr: torch.Tensor      # float64 [n, S, 9]
+    bptr: torch.Tensor     # int32 [n + 1]
+    bj: torch.Tensor       # int32 [nb]  local partner index, ascending inside a row
+    brev: torch.Tensor     # int32 [nb]  record index of the mirror (j, i)
+    bconn: torch.Tensor    # float64 [nb, 15]
+    blen: torch.Tensor     # float64 [nb, 5]
+
+    @property
+    def n(self) -> int:
+        return len(self.gid)
+
+    @property
+    def n_bonds(self) -> int:
+        return len(self.bj)
+
+
+def bond_rows(t: LocalTables) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(row pointer int64 [n + 1], bond-stream rows [nb, 22] in local record order) of a rank's bond table."""
+    dev = t.gid.device
+    if hasattr(t, "global_bonds"):  # initial block distribution: records already carry global ids
+        B = t.global_bonds
+        li = _f2i(B[:, 0].contiguous()) - int(t.gid[0]) if len(B) else torch.zeros(0, dtype=torch.int64, device=dev)
+        o = torch.argsort(li, stable=True)
+        bptr = torch.zeros(t.n + 1, dtype=torch.int64, device=dev)
+        if len(li):
+            bptr[1:] = torch.cumsum(torch.bincount(li, minlength=t.n), 0)
+        return bptr, B[o]
+    bptr = t.bptr.to(torch.int64)
+    if t.n_bonds == 0:
+        return bptr, torch.zeros((0, B_INT + B_DBL), dtype=torch.float64, device=dev)
+    rec_owner = torch.repeat_interleave(torch.arange(t.n, device=dev), bptr[1:] - bptr[:-1])
+    rows = torch.cat([_i2f(t.gid[rec_owner])[:, None], _i2f(t.gid[t.bj.to(torch.int64)])[:, None], t.bconn, t.blen], dim=1)
+    return bptr, rows
+
+
+def make_streams(t: LocalTables, coord_axis: int, inner_bounds: torch.Tensor, r_ghost: float, world: int):
+    """Record streams for a repartition: every OWNED particle goes to its new owner (full record with its contact
+    springs and bond rows) and, as a ghost (state + bond rows), to every other rank whose widened slab holds it.
+    Returns [(rows, dest)] for the particle, bond and contact streams."""
+    dev = t.gid.device
+    own_idx = torch.nonzero(t.owned, as_tuple=True)[0]
+    coord = t.state[own_idx, coord_axis]
+    owner = owner_of(coord, inner_bounds)
+    gp, gr = ghost_destinations(coord, owner, inner_bounds, r_ghost, world)
+    ship_p = torch.cat([own_idx, own_idx[gp]])           # local index of the shipped particle
+    ship_dest = torch.cat([owner, gr])
+    ship_kind = torch.cat([torch.zeros_like(owner), torch.ones_like(gr)])
+    ship_owner = torch.cat([owner, owner[gp]])
+    # particle stream
+    P = torch.cat([_i2f(t.gid[ship_p])[:, None], _i2f(ship_kind)[:, None], _i2f(ship_owner)[:, None], t.state[ship_p]], dim=1)
+    # bond stream: all records of every shipped particle
+    bptr, rows = bond_rows(t)
+    nb_of = bptr[1:] - bptr[:-1]
+    seg, rec = ragged_expand(bptr[ship_p], nb_of[ship_p])
+    B = rows[rec] if len(rec) else torch.zeros((0, B_INT + B_DBL), dtype=torch.float64, device=dev)
+    B_dest = ship_dest[seg]
+    # contact stream: active slots of owned particles, to the new owner only
+    sg = t.sgid[own_idx].to(torch.int64)                  # [n_own, S]
+    act_p, act_k = torch.nonzero(sg >= 0, as_tuple=True)
+    ci = t.gid[own_idx[act_p]]
+    cj = t.gid[sg[act_p, act_k]]
+    Cs = torch.cat([_i2f(ci)[:, None], _i2f(cj)[:, None], t.spr[own_idx[act_p], act_k]], dim=1) if len(act_p) else \
+        torch.zeros((0, C_INT + C_DBL), dtype=torch.float64, device=dev)
+    C_dest = owner[act_p]
+    return (P, ship_dest), (B, B_dest), (Cs, C_dest)
+
+
+def relocalize(P: torch.Tensor, P_src: torch.Tensor, B: torch.Tensor, Cs: torch.Tensor, S: int) -> LocalTables:
+    """Build a rank's local tables from the records it received (its own included)."""
+    dev = P.device
+    gid_all = _f2i(P[:, 0].contiguous())
+    order = torch.argsort(gid_all, stable=True)
+    gid = gid_all[order]
+    if len(gid) > 1 and bool((gid[1:] == gid[:-1]).any()):
+        raise RuntimeError("slab repartition: a particle arrived twice on one rank")
+    kind = _f2i(P[:, 1].contiguous())[order]
+    n = len(gid)
+    owned = kind == 0
+    state = P[order, P_INT:].contiguous()
+    src = _f2i(P[:, 2].contiguous())[order]  # the particle's (new) owner rank
+    # ---- bonds ---------------------------------------------------------------------------------
+    bi_g, bj_g = _f2i(B[:, 0].contiguous()), _f2i(B[:, 1].contiguous())
+    li, ok_i = lookup_sorted(gid, bi_g)
+    lj, ok_j = lookup_sorted(gid, bj_g)
+    if len(li) and not bool(ok_i.all()):
+        raise RuntimeError("slab repartition: bond record without its particle")
+    if len(li) and bool((owned[li] & ~ok_j).any()):
+        raise RuntimeError("slab repartition: a bonded partner of an owned particle is outside the ghost margin "
+                           "(increase skin)")
+    keep = ok_j
+    li, lj, Bk = li[keep], lj[keep], B[keep]
+    key = li * max(n, 1) + lj
+    bo = torch.argsort(key, stable=True)
+    key, li, lj, Bk = key[bo], li[bo], lj[bo], Bk[bo]
+    if len(key) > 1 and bool((key[1:] == key[:-1]).any()):
+        raise RuntimeError("slab repartition: duplicate bond record")
+    bptr = torch.zeros(n + 1, dtype=torch.int64, device=dev)
+    if len(li):
+        bptr[1:] = torch.cumsum(torch.bincount(li, minlength=n), 0)
+    rev_pos, rev_ok = lookup_sorted(key, lj * max(n, 1) + li)
+    if len(key) and not bool(rev_ok.all()):
+        raise RuntimeError("slab repartition: bond record without its mirror")
+    # ---- contact springs ---------------------------------------------------------------------------
+    sgid = torch.full((n, S), -1, dtype=torch.int32, device=dev)
+    spr = torch.zeros((n, S, 9), dtype=torch.float64, device=dev)
+    if len(Cs):
+        ci, ok_ci = lookup_sorted(gid, _f2i(Cs[:, 0].contiguous()))
+        cj, ok_cj = lookup_sorted(gid, _f2i(Cs[:, 1].contiguous()))
+        if not bool((ok_ci & ok_cj).all()):
+            raise RuntimeError("slab repartition: a contact partner is outside the ghost margin")
+        co = torch.argsort(ci * max(n, 1) + cj, stable=True)
+        ci, cj, Ck = ci[co], cj[co], Cs[co]
+        first = torch.cumsum(torch.bincount(ci, minlength=n), 0) - torch.bincount(ci, minlength=n)
+        slot = torch.arange(len(ci), device=dev) - first[ci]
+        if int(slot.max()) >= S:
+            raise RuntimeError("slab repartition: more simultaneous contacts than max_contacts")
+        sgid[ci, slot] = cj.to(torch.int32)
+        spr[ci, slot] = Ck[:, C_INT:]
+    return LocalTables(gid=gid, owned=owned, src=src, state=state, S=S, sgid=sgid, spr=spr,
+                       bptr=bptr.to(torch.int32), bj=lj.to(torch.int32), brev=rev_pos.to(torch.int32),
+                       bconn=Bk[:, B_INT:B_INT + 15].contiguous(), blen=Bk[:, B_INT + 15:].contiguous())
+
+
+def repartition_tables(t: LocalTables, coord_axis: int, r_ghost: float, world: int, group=None) -> Tuple[LocalTables, torch.Tensor]:
+    """One full repartition: bounds -> streams -> exchange -> local tables.  Returns (tables, inner bounds)."""
+    own = t.owned
+    bounds = slab_bounds(t.state[own, coord_axis].contiguous(), world, group)
+    (P, Pd), (B, Bd), (Cs, Cd) = make_streams(t, coord_axis, bounds, r_ghost, world)
+    P_in, P_src = all_to_all_rows(P, Pd, world, group)
+    B_in, _ = all_to_all_rows(B, Bd, world, group)
+    C_in, _ = all_to_all_rows(Cs, Cd, world, group)
+    return relocalize(P_in, P_src, B_in, C_in, t.S), bounds
+
+
+@dataclass
+class HaloPlan:
+    """Per peer rank: what I send after every step and where what I receive goes (all local indices, int32)."""
+
+    peers: List[int]
+    send_idx: Dict[int, torch.Tensor]
+    send_rec: Dict[int, torch.Tensor]
+    recv_idx: Dict[int, torch.Tensor]
+    recv_rec: Dict[int, torch.Tensor]
+
+    def send_doubles(self, r: int) -> int:
+        return 9 * len(self.send_idx[r]) + 15 * len(self.send_rec[r])
+
+    def recv_doubles(self, r: int) -> int:
+        return 9 * len(self.recv_idx[r]) + 15 * len(self.recv_rec[r])
+
+
+def build_halo_plan(t: LocalTables, rank: int, world: int, group=None) -> HaloPlan:
+    """Request-based: every rank tells the owners which ghosts (by global id) and which of their bond records (by
+    (gid_i, gid_j)) it holds; the owners translate the requests into their local indices."""
+    dev = t.gid.device
+    n = t.n
+    ghost = torch.nonzero(~t.owned, as_tuple=True)[0]
+    g_src = t.src[ghost]
+    # particle requests, grouped by owner rank (stable -> ascending local index inside a group)
+    req_p = _i2f(t.gid[ghost])[:, None]
+    got_p, got_p_src = all_to_all_rows(req_p, g_src, world, group)
+    # bond-record requests: records whose first particle is a ghost
+    bptr = t.bptr.to(torch.int64)
+    rec_owner = torch.repeat_interleave(torch.arange(n, device=dev), bptr[1:] - bptr[:-1])
+    grec = torch.nonzero(~t.owned[rec_owner], as_tuple=True)[0] if t.n_bonds else torch.zeros(0, dtype=torch.int64, device=dev)
+    r_src = t.src[rec_owner[grec]]
+    req_b = torch.stack([_i2f(t.gid[rec_owner[grec]]), _i2f(t.gid[t.bj[grec].to(torch.int64)])], dim=1) if len(grec) else \
+        torch.zeros((0, 2), dtype=torch.float64, device=dev)
+    got_b, got_b_src = all_to_all_rows(req_b, r_src, world, group)
+    # translate what others asked of me
+    want_gid = _f2i(got_p[:, 0].contiguous())
+    s_idx, ok = lookup_sorted(t.gid, want_gid)
+    if len(s_idx) and not bool((ok & t.owned[s_idx]).all()):
+        raise RuntimeError("halo plan: a rank requested a particle this rank does not own")
+    my_key = rec_owner * max(n, 1) + t.bj.to(torch.int64) if t.n_bonds else torch.zeros(0, dtype=torch.int64, device=dev)
+    if len(got_b):
+        wi, ok_i = lookup_sorted(t.gid, _f2i(got_b[:, 0].contiguous()))
+        wj, ok_j = lookup_sorted(t.gid, _f2i(got_b[:, 1].contiguous()))
+        s_rec, ok_r = lookup_sorted(my_key, wi * max(n, 1) + wj)
+        if not bool((ok_i & ok_j & ok_r).all()):
+            raise RuntimeError("halo plan: a rank requested a bond record this rank does not hold")
+    else:
+        s_rec = torch.zeros(0, dtype=torch.int64, device=dev)
+    peers = sorted(set(g_src.tolist()) | set(got_p_src.tolist()) | set(r_src.tolist()) | set(got_b_src.tolist()))
+    peers = [p for p in peers if p != rank]
+    order_p = torch.argsort(g_src, stable=True)
+    order_b = torch.argsort(r_src, stable=True)
+    plan = HaloPlan(peers, {}, {}, {}, {})
+    for r in peers:
+        plan.send_idx[r] = s_idx[got_p_src == r].to(torch.int32).contiguous()
+        plan.send_rec[r] = s_rec[got_b_src == r].to(torch.int32).contiguous()
+        gp = ghost[order_p]
+        plan.recv_idx[r] = gp[g_src[order_p] == r].to(torch.int32).contiguous()
+        gb = grec[order_b]
+        plan.recv_rec[r] = gb[r_src[order_b] == r].to(torch.int32).contiguous()
+    return plan
+
+
+def block_tables(rank: int, world: int, x, v, theta, omega, S: int, bond_ij=None, bond_conn=None, bond_len=None,
+                 device="cpu") -> LocalTables:
+    """Initial, arbitrary distribution before the first repartition: rank r 'owns' the contiguous block of global
+    ids [r n / W, (r + 1) n / W) of the caller's arrays, without ghosts.  Bond records (global ids, both
+    orientations) are taken for the block's particles; partners outside the block are dropped here and come back
+    with the first repartition, which ships every record with its particle."""
+    n = len(x)
+    lo, hi = (rank * n) // world, ((rank + 1) * n) // world
+    st = np.concatenate([np.asarray(a, dtype=np.float64)[lo:hi] for a in (x, v, theta, omega)] +
+                        [np.zeros((hi - lo, 6))], axis=1)
+    gid = torch.arange(lo, hi, dtype=torch.int64, device=device)
+    m = hi - lo
+    state = torch.from_numpy(st).to(device)
+    if bond_ij is not None and len(bond_ij):
+        ij = np.asarray(bond_ij, dtype=np.int64)
+        sel = (ij[:, 0] >= lo) & (ij[:, 0] < hi)
+        B = np.concatenate([ij[sel].view(np.float64), np.asarray(bond_conn)[sel].reshape(-1, 15),
+                            np.asarray(bond_len)[sel].reshape(-1, 5)], axis=1)
+        B = torch.from_numpy(np.ascontiguousarray(B)).to(device)
+    else:
+        B = torch.zeros((0, B_INT + B_DBL), dtype=torch.float64, device=device)
+    return _InitialTables(gid, state, S, B, m)
+
+
+class _InitialTables(LocalTables):
+    """Block distribution whose bond stream is already in global-id form (partners need not be local)."""
+
+    def __init__(self, gid, state, S, B, m):
+        dev = gid.device
+        super().__init__(gid=gid, owned=torch.ones(m, dtype=torch.bool, device=dev),
+                         src=torch.zeros(m, dtype=torch.int64, device=dev), state=state, S=S,
+                         sgid=torch.full((m, S), -1, dtype=torch.int32, device=dev),
+                         spr=torch.zeros((m, S, 9), dtype=torch.float64, device=dev),
+                         bptr=torch.zeros(m + 1, dtype=torch.int32, device=dev), bj=torch.zeros(0, dtype=torch.int32, device=dev),
+                         brev=torch.zeros(0, dtype=torch.int32, device=dev), bconn=torch.zeros((0, 15), dtype=torch.float64, device=dev),
+                         blen=torch.zeros((0, 5), dtype=torch.float64, device=dev))
+        self.global_bonds = B

@@ -373,3 +373,40 @@ def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1
     if cfg.model_mask & MODEL_FACET:
         sysm.add_facet(cfg.facet_vertices, cfg.facet_v, cfg.surf_contact, (cfg.surf_A, cfg.surf_h0))
     return sysm
+
+
+def host_bond_table(x, r_part: float, critical_separation: float, unit_vectors):
+    """sinter_functor's constructor scan (LG/sinter_bridge/sinter_bridge.h:148-211) through lg_bond_table_create:
+    pure host code, no GPU needed.  Returns (ij int64 [2b, 2], connectors [2b, 15], rest lengths [2b, 5]) --
+    both orientations of every bond, in the layout lg_set_bonds takes."""
+    lib = load_library()
+    x = _c3(x)
+    if callable(unit_vectors):
+        def cb(_user, out):
+            vec = unit_vectors()
+            out[0], out[1], out[2] = float(vec[0]), float(vec[1]), float(vec[2])
+    else:
+        arr = _c3(unit_vectors)
+        state = {"k": 0}
+
+        def cb(_user, out):
+            k = state["k"]
+            out[0], out[1], out[2] = arr[k, 0], arr[k, 1], arr[k, 2]
+            state["k"] = k + 1
+    cfn = UNIT_VECTOR_FN(cb)
+    tbl = C.c_void_p()
+    rc = lib.lg_bond_table_create(len(x), x.ctypes.data, float(r_part), float(critical_separation), cfn, None, C.byref(tbl))
+    if rc != LG_OK:
+        raise LgError(rc, lib.lg_last_error().decode(errors="replace"))
+    try:
+        nb = C.c_int64(0)
+        lib.lg_bond_table_count(tbl, C.byref(nb))
+        m = 2 * nb.value
+        ij = np.zeros((m, 2), dtype=np.int64)
+        conn = np.zeros((m, 15), dtype=np.float64)
+        ln = np.zeros((m, 5), dtype=np.float64)
+        if m:
+            lib.lg_bond_table_records(tbl, ij.ctypes.data, conn.ctypes.data, ln.ctypes.data)
+    finally:
+        lib.lg_bond_table_destroy(tbl)
+    return ij, conn, ln
