@@ -378,3 +378,254 @@ class _InitialTables(LocalTables):
                          brev=torch.zeros(0, dtype=torch.int32, device=dev), bconn=torch.zeros((0, 15), dtype=torch.float64, device=dev),
                          blen=torch.zeros((0, 5), dtype=torch.float64, device=dev))
         self.global_bonds = B
+
+
+# =================================================================================================
+# the GPU driver
+# =================================================================================================
+class _DevView:
+    """Zero-copy torch view of device memory owned by the C library (``__cuda_array_interface__``)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def _view(ptr, shape, dtype: torch.dtype, device) -> torch.Tensor:
+    typestr = {torch.float64: "<f8", torch.int32: "<i4", torch.uint8: "|u1"}[dtype]
+    if int(np.prod(shape)) == 0 or not ptr:
+        return torch.zeros(tuple(shape), dtype=dtype, device=device)
+    return torch.as_tensor(_DevView(ptr, shape, typestr), device=device)
+
+
+class SlabSystem:
+    """A granular system slab-decomposed over the ranks of a ``torch.distributed`` process group (one GPU each).
+
+    Mirrors the driver-facing surface of ``GranularSystem`` (do_step, update_neighbor_list, run, get, diagnostics).
+    Every rank constructs it with the same full initial state (the driver program's x0, v0, theta0, omega0)."""
+
+    def __init__(self, cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = 0, group=None, skin: Optional[float] = None,
+                 axis: int = 0, max_contacts: int = 16):
+        from . import system as _sys
+        from .scenarios import MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
+
+        if not cfg.use_neighbor_list:
+            raise ValueError("slab decomposition needs the neighbor-list system (granular_system_neighbor_list)")
+        if cfg.model_mask & MODEL_FACET:
+            raise ValueError("facets are not supported in slab-decomposed runs yet")
+        self._sys = _sys
+        self.lib = _sys.load_library()
+        self.cfg = cfg
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.device = torch.device("cuda", device)
+        self.dev_index = device
+        self.axis = axis
+        self.skin = float(skin) if skin is not None else 1.0 * cfg.r_part
+        self.r_ghost = cfg.r_verlet + self.skin
+        self.S = max_contacts
+        self.n_global = len(x0)
+        self.h = C.c_void_p()
+        self.steps = 0
+        self.repartitions = 0
+        self.kicked = False
+        self._models = (bool(cfg.model_mask & MODEL_CONTACT), bool(cfg.model_mask & MODEL_SINTER), bool(cfg.model_mask & MODEL_HAMAKER))
+        bonds = (None, None, None)
+        if cfg.model_mask & MODEL_SINTER:
+            if unit_vectors is None:
+                raise ValueError("the sinter model needs unit_vectors")
+            bonds = _sys.host_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors)
+        torch.cuda.set_device(self.device)
+        t0 = block_tables(self.rank, self.world, x0, v0, theta0, omega0, self.S, *bonds, device=self.device)
+        self._install(t0)
+
+    # -- plumbing ------------------------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != 0:
+            raise self._sys.LgError(rc, self.lib.lg_last_error().decode(errors="replace"))
+
+    def close(self):
+        if getattr(self, "h", None) and self.h.value:
+            self.lib.lg_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _install(self, t_old: LocalTables):
+        """Repartition `t_old` and build this rank's lg_system from what arrives."""
+        t, self.bounds = repartition_tables(t_old, self.axis, self.r_ghost, self.world, self.group)
+        torch.cuda.current_stream(self.device).synchronize()  # the library copies from these tensors on its own stream
+        self.close()
+        lib, cfg = self.lib, self.cfg
+        n = t.n
+        if n == 0:
+            raise RuntimeError("slab decomposition left a rank without particles")
+        self._check(lib.lg_create(n, cfg.r_part, cfg.mass, cfg.inertia, self.dev_index, C.byref(self.h)))
+        self._check(lib.lg_set_max_contacts(self.h, self.S))
+        st = t.state
+        cols = [st[:, 3 * k:3 * k + 3].contiguous() for k in range(6)]  # x v theta omega a alpha
+        self._check(lib.lg_import_state_device(self.h, *[c.data_ptr() for c in cols], int(self.kicked)))
+        owned_u8 = t.owned.to(torch.uint8).contiguous()
+        self._check(lib.lg_set_owned_device(self.h, owned_u8.data_ptr()))
+        contact, sinter, hamaker = self._models
+        cp = self._sys.ContactParamsStruct.from_seq(cfg.contact)
+        if contact:
+            self._check(lib.lg_set_contact(self.h, C.byref(cp)))
+        if sinter:
+            self._check(lib.lg_import_bonds_device(self.h, C.byref(cp), cfg.k_d, cfg.gamma_d, t.n_bonds, t.bptr.data_ptr(),
+                                                   t.bj.data_ptr(), t.brev.data_ptr(), t.bconn.data_ptr(), t.blen.data_ptr()))
+        if hamaker:
+            self._check(lib.lg_set_hamaker(self.h, cfg.hamaker_A, cfg.hamaker_h0))
+        self._check(lib.lg_import_slots_device(self.h, t.sgid.contiguous().data_ptr(), t.spr.contiguous().data_ptr()))
+        self._check(lib.lg_enable_neighbor_list(self.h, cfg.r_verlet))
+        sp = C.c_void_p()
+        self._check(lib.lg_get_stream(self.h, C.byref(sp)))
+        self.stream = torch.cuda.ExternalStream(sp.value, device=self.device)
+        # what stays on the Python side: identity, ownership, halo lists, reference positions for the skin check
+        self.n_local = n
+        self.gid, self.owned, self.src = t.gid, t.owned, t.src
+        self.own_idx = torch.nonzero(t.owned, as_tuple=True)[0]
+        self.x_ref = cols[0][self.own_idx].clone()
+        self.n_bonds_local = t.n_bonds
+        self.plan = build_halo_plan(t, self.rank, self.world, self.group)
+        self.send_buf = {r: torch.empty(max(self.plan.send_doubles(r), 1), dtype=torch.float64, device=self.device) for r in self.plan.peers}
+        self.recv_buf = {r: torch.empty(max(self.plan.recv_doubles(r), 1), dtype=torch.float64, device=self.device) for r in self.plan.peers}
+        self.halo_bytes_per_step = 8 * sum(self.plan.send_doubles(r) for r in self.plan.peers)
+        self.repartitions += 1
+
+    def _field_view(self, name: str) -> torch.Tensor:
+        p = C.c_void_p()
+        self._check(self.lib.lg_device_field(self.h, self._sys.FIELDS[name], C.byref(p)))
+        return _view(p.value, (self.n_local, 3), torch.float64, self.device)
+
+    def _export(self) -> LocalTables:
+        """Snapshot of this rank's tables (copies: the system they live in is about to be replaced)."""
+        lib = self.lib
+        self._check(lib.lg_flush(self.h))
+        S, p_sgid, p_spr = C.c_int(), C.c_void_p(), C.c_void_p()
+        self._check(lib.lg_export_slots(self.h, C.byref(S), C.byref(p_sgid), C.byref(p_spr)))
+        nb, p_bptr, p_bj, p_bconn, p_blen = C.c_int64(), C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
+        self._check(lib.lg_export_bonds(self.h, C.byref(nb), C.byref(p_bptr), C.byref(p_bj), C.byref(p_bconn), C.byref(p_blen)))
+        self._check(lib.lg_synchronize(self.h))
+        n, dev = self.n_local, self.device
+        state = torch.cat([self._field_view(f) for f in ("x", "v", "theta", "omega", "a", "alpha")], dim=1)
+        nbv = int(nb.value)
+        return LocalTables(
+            gid=self.gid, owned=self.owned, src=self.src, state=state, S=S.value,
+            sgid=_view(p_sgid.value, (n, S.value), torch.int32, dev).clone(),
+            spr=_view(p_spr.value, (n, S.value, 9), torch.float64, dev).clone(),
+            bptr=_view(p_bptr.value, (n + 1,), torch.int32, dev).clone(), bj=_view(p_bj.value, (nbv,), torch.int32, dev).clone(),
+            brev=torch.zeros(nbv, dtype=torch.int32, device=dev),
+            bconn=_view(p_bconn.value, (nbv, 15), torch.float64, dev).clone(),
+            blen=_view(p_blen.value, (nbv, 5), torch.float64, dev).clone())
+
+    # -- halo ----------------------------------------------------------------------------------------------
+    def halo_exchange(self):
+        """Owners' x, v, omega and bond connectors -> the ghost copies on the neighbouring ranks."""
+        plan, lib = self.plan, self.lib
+        if not plan.peers:
+            return
+        with torch.cuda.stream(self.stream):
+            ops = []
+            for r in plan.peers:
+                self._check(lib.lg_halo_pack(self.h, len(plan.send_idx[r]), plan.send_idx[r].data_ptr(), len(plan.send_rec[r]),
+                                             plan.send_rec[r].data_ptr(), self.send_buf[r].data_ptr()))
+                if plan.send_doubles(r):
+                    ops.append(dist.P2POp(dist.isend, self.send_buf[r][:plan.send_doubles(r)], r, group=self.group))
+                if plan.recv_doubles(r):
+                    ops.append(dist.P2POp(dist.irecv, self.recv_buf[r][:plan.recv_doubles(r)], r, group=self.group))
+            for q in dist.batch_isend_irecv(ops) if ops else []:
+                q.wait()
+            for r in plan.peers:
+                self._check(lib.lg_halo_unpack(self.h, len(plan.recv_idx[r]), plan.recv_idx[r].data_ptr(), len(plan.recv_rec[r]),
+                                               plan.recv_rec[r].data_ptr(), self.recv_buf[r].data_ptr()))
+
+    # -- the driver-facing surface ---------------------------------------------------------------------
+    def do_step(self, dt: float):
+        if not self.kicked:
+            # first call: evaluate, half kick back | refresh the ghosts' kicked v, omega | evaluate again, integrate
+            self._check(self.lib.lg_first_half_kick(self.h, float(dt)))
+            self.halo_exchange()
+            self.kicked = True
+        self._check(self.lib.lg_do_step(self.h, float(dt)))
+        self.halo_exchange()
+        self.steps += 1
+
+    def needs_repartition(self) -> bool:
+        """True on every rank when some owned particle has moved more than skin / 2 since the last partition."""
+        with torch.cuda.stream(self.stream):
+            x = self._field_view("x")[self.own_idx]
+            d2 = ((x - self.x_ref) ** 2).sum(dim=1).max().reshape(1)
+            if self.world > 1:
+                dist.all_reduce(d2, op=dist.ReduceOp.MAX, group=self.group)
+        return float(d2) > (0.5 * self.skin) ** 2
+
+    def repartition(self):
+        with torch.cuda.stream(self.stream):
+            t = self._export()
+        self.stream.synchronize()
+        self._install(t)  # on torch's current stream: the system (and its stream) is replaced inside
+
+    def update_neighbor_list(self):
+        if self.world > 1 and self.needs_repartition():
+            self.repartition()
+        self._check(self.lib.lg_update_neighbor_list(self.h))
+
+    def run(self, dt: float, n_steps: int, rebuild_every: int = 0):
+        for _ in range(n_steps):
+            if rebuild_every > 0 and self.steps % rebuild_every == 0:
+                self.update_neighbor_list()
+            self.do_step(dt)
+
+    def synchronize(self):
+        self._check(self.lib.lg_synchronize(self.h))
+
+    def get(self, name: str) -> np.ndarray:
+        """Field in the caller's original particle order, assembled on every rank."""
+        if name in ("a", "alpha"):
+            self._check(self.lib.lg_flush(self.h))
+        with torch.cuda.stream(self.stream):
+            mine = torch.cat([_i2f(self.gid[self.own_idx])[:, None], self._field_view(name)[self.own_idx]], dim=1)
+            if self.world == 1:
+                rows = mine
+            else:
+                dest = torch.arange(self.world, device=self.device).repeat_interleave(len(mine))
+                rows, _ = all_to_all_rows(mine.repeat(self.world, 1), dest, self.world, self.group)
+            out = torch.empty((self.n_global, 3), dtype=torch.float64, device=self.device)
+            out[_f2i(rows[:, 0].contiguous())] = rows[:, 1:]
+        self.synchronize()
+        torch.cuda.synchronize(self.device)
+        return out.cpu().numpy()
+
+    def counters(self) -> dict:
+        out = (C.c_int64 * 8)()
+        self._check(self.lib.lg_get_counters(self.h, out))
+        loc = torch.tensor([out[0], out[1], int(self.owned.sum()), self.n_local - int(self.owned.sum())], dtype=torch.int64,
+                           device=self.device)
+        tot = loc.clone()
+        if self.world > 1:
+            dist.all_reduce(tot, group=self.group)
+        return {"pairs": int(tot[0]), "contacts": int(tot[1]), "owned_local": int(loc[2]), "ghosts_local": int(loc[3]),
+                "ghosts_total": int(tot[3]), "launches": int(out[5]), "repartitions": self.repartitions,
+                "halo_bytes_per_step": self.halo_bytes_per_step}
+
+    def diagnostics(self) -> dict:
+        """test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26 over the owned particles of all ranks."""
+        cfg = self.cfg
+        with torch.cuda.stream(self.stream):
+            x, v, w = (self._field_view(f)[self.own_idx] for f in ("x", "v", "omega"))
+            s = torch.cat([(cfg.mass * (v * v).sum(1) / 2.0).sum().reshape(1), (cfg.inertia * (w * w).sum(1) / 2.0).sum().reshape(1),
+                           v.sum(0), (cfg.inertia * w + torch.linalg.cross(x, cfg.mass * v)).sum(0), x.sum(0)])
+            if self.world > 1:
+                dist.all_reduce(s, group=self.group)
+            com = s[8:11] / self.n_global
+            rg2 = ((x - com) ** 2).sum().reshape(1)
+            if self.world > 1:
+                dist.all_reduce(rg2, group=self.group)
+        s, rg2, com = s.cpu().numpy(), float(rg2), com.cpu().numpy()
+        return {"ke": s[0] + s[1], "ke_trs": s[0], "ke_rot": s[1], "linear_momentum": cfg.mass * float(np.linalg.norm(s[2:5])),
+                "angular_momentum": float(np.linalg.norm(s[5:8])), "com": com, "rg": float(np.sqrt(rg2 / self.n_global))}

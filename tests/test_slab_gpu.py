@@ -1,0 +1,105 @@
+"""Slab-decomposed runs (libgran_b200/slab.py, one rank per GPU over NCCL) against the single-GPU system:
+bit-identical fields at every compared step, for bonded + Hamaker aggregates and for a contact + Hamaker packing
+whose particles cross slab boundaries (forced repartitions with migrating contact springs).
+
+Needs >= 2 GPUs (gpurun --gpus 2); skipped otherwise.  world_size 1 is covered on any GPU box."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+
+from libgran_b200 import scenarios as S
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _uv(n, seed=7):
+    rng = np.random.Generator(np.random.MT19937(seed))
+    v = rng.normal(size=(n, 3))
+    return v / np.linalg.norm(v, axis=1)[:, None]
+
+
+def _scenario(name):
+    if name == "aggregates":
+        return S.multi_aggregate_collision(24), 90, None
+    if name == "packing":
+        # fast particles: several repartitions within the run, contacts form and break across the boundary
+        return S.random_packing(6000, volume_fraction=0.3, v_scale=400.0), 120, 0.1 * S.R_PART
+    if name == "fractal":
+        return S.fractal_aggregate(4000, models=S.MODEL_SINTER | S.MODEL_HAMAKER), 60, None
+    raise KeyError(name)
+
+
+def _worker(rank, world, port, name, out_dir):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from libgran_b200.slab import SlabSystem
+
+        scn, steps, skin = _scenario(name)
+        cfg = scn.cfg
+        uv = _uv(4 * cfg.n) if cfg.model_mask & S.MODEL_SINTER else None
+        sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=rank, skin=skin)
+        res = {}
+        done = 0
+        for cp in (1, steps // 2, steps):
+            sysm.run(cfg.dt, cp - done, cfg.rebuild_every)
+            done = cp
+            for f in ("x", "v", "theta", "omega", "a", "alpha"):
+                res[f"{f}_{cp}"] = sysm.get(f)
+        cnt = sysm.counters()
+        diag = sysm.diagnostics()
+        if rank == 0:
+            np.savez(os.path.join(out_dir, "slab.npz"), repartitions=cnt["repartitions"], pairs=cnt["pairs"],
+                     contacts=cnt["contacts"], ghosts=cnt["ghosts_total"], ke=diag["ke"], rg=diag["rg"], **res)
+        sysm.close()
+    finally:
+        dist.destroy_process_group()
+
+
+def _single(name):
+    from libgran_b200.system import from_config
+
+    scn, steps, _ = _scenario(name)
+    cfg = scn.cfg
+    uv = _uv(4 * cfg.n) if cfg.model_mask & S.MODEL_SINTER else None
+    g = from_config(cfg, *scn.state, unit_vectors=uv, device=0)
+    res, done = {}, 0
+    for cp in (1, steps // 2, steps):
+        g.run(cfg.dt, cp - done, cfg.rebuild_every)
+        done = cp
+        for f in ("x", "v", "theta", "omega", "a", "alpha"):
+            res[f"{f}_{cp}"] = g.get(f)
+    return res, g.counters(), g.diagnostics()
+
+
+@pytest.mark.parametrize("name", ["aggregates", "packing", "fractal"])
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_slab_equals_single_gpu(lib, tmp_path, name, world):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    import torch.multiprocessing as mp
+
+    mp.spawn(_worker, args=(world, _free_port(), name, str(tmp_path)), nprocs=world, join=True)
+    got = np.load(os.path.join(str(tmp_path), "slab.npz"))
+    want, cnt, diag = _single(name)
+    for key, val in want.items():
+        assert np.array_equal(got[key], val), f"{name} world {world}: {key} differs, max abs {np.abs(got[key] - val).max():.3e}"
+    assert int(got["pairs"]) == cnt["pairs"] and int(got["contacts"]) == cnt["contacts"]
+    assert abs(float(got["ke"]) - diag["ke"]) <= 1e-12 * abs(diag["ke"])
+    assert abs(float(got["rg"]) - diag["rg"]) <= 1e-12 * abs(diag["rg"])
+    if world > 1:
+        assert int(got["ghosts"]) > 0
+        if name == "packing":
+            assert int(got["repartitions"]) > 1, "the packing case is meant to force repartitions"
