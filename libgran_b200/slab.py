@@ -562,7 +562,8 @@ class SlabSystem:
             d2 = ((x - self.x_ref) ** 2).sum(dim=1).max().reshape(1)
             if self.world > 1:
                 dist.all_reduce(d2, op=dist.ReduceOp.MAX, group=self.group)
-        return float(d2) > (0.5 * self.skin) ** 2
+            moved2 = float(d2)  # read back on the system's stream (it is non-blocking: the default stream does not order with it)
+        return moved2 > (0.5 * self.skin) ** 2
 
     def repartition(self):
         with torch.cuda.stream(self.stream):
@@ -626,6 +627,6 @@ class SlabSystem:
             rg2 = ((x - com) ** 2).sum().reshape(1)
             if self.world > 1:
                 dist.all_reduce(rg2, group=self.group)
-        s, rg2, com = s.cpu().numpy(), float(rg2), com.cpu().numpy()
+            s, rg2, com = s.cpu().numpy(), float(rg2), com.cpu().numpy()  # inside the stream context, see needs_repartition
         return {"ke": s[0] + s[1], "ke_trs": s[0], "ke_rot": s[1], "linear_momentum": cfg.mass * float(np.linalg.norm(s[2:5])),
                 "angular_momentum": float(np.linalg.norm(s[5:8])), "com": com, "rg": float(np.sqrt(rg2 / self.n_global))}

@@ -100,6 +100,7 @@ def test_slab_equals_single_gpu(lib, tmp_path, name, world):
     assert abs(float(got["ke"]) - diag["ke"]) <= 1e-12 * abs(diag["ke"])
     assert abs(float(got["rg"]) - diag["rg"]) <= 1e-12 * abs(diag["rg"])
     if world > 1:
-        assert int(got["ghosts"]) > 0
+        if name != "aggregates":  # the aggregates are separated by more than the ghost margin: the cut may fall in a gap
+            assert int(got["ghosts"]) > 0
         if name == "packing":
             assert int(got["repartitions"]) > 1, "the packing case is meant to force repartitions"
