@@ -602,6 +602,27 @@ class SlabSystem:
         torch.cuda.synchronize(self.device)
         return out.cpu().numpy()
 
+    def set_state_host(self, x, v, theta, omega):
+        """lg_set_state for a decomposed system: every rank uploads (H2D, pinned) the rows of the caller's full arrays
+        that it holds (owned and ghost); re-arms the first-step half kick like the reference constructor."""
+        gid = self.gid.cpu().numpy()
+        bufs = [torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64)[gid])).pin_memory() for a in (x, v, theta, omega)]
+        dp = C.POINTER(C.c_double)
+        self._check(self.lib.lg_set_state(self.h, self.n_local, *[C.cast(b.data_ptr(), dp) for b in bufs]))
+        self.kicked = False
+        with torch.cuda.stream(self.stream):
+            self.x_ref = self._field_view("x")[self.own_idx].clone()
+
+    def get_owned_host(self, names) -> dict:
+        """D2H of this rank's owned rows (global ids + fields), without assembling the global arrays."""
+        out = {"gid": self.gid[self.own_idx].cpu().numpy()}
+        with torch.cuda.stream(self.stream):
+            for f in names:
+                if f in ("a", "alpha"):
+                    self._check(self.lib.lg_flush(self.h))
+                out[f] = self._field_view(f)[self.own_idx].cpu().numpy()
+        return out
+
     def counters(self) -> dict:
         out = (C.c_int64 * 8)()
         self._check(self.lib.lg_get_counters(self.h, out))
