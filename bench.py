@@ -143,7 +143,8 @@ def run_ours(args):
         return run_slab(args, scn, world, rank, local_rank)
 
     uv = numpy_unit_vectors(n + 1024)
-    sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant)
+    mode = 1 if (args.math == "fast" and args.variant in (None, 1)) else 0
+    sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)
     stream = torch.cuda.ExternalStream(sysm.stream_handle(), device=torch.device("cuda", local_rank))
 
     def timed_run(k):
@@ -192,7 +193,7 @@ def run_ours(args):
 
     if args.kernel_only:
         if rank == 0:
-            print(json.dumps({"value": round(value, 1), "ms_per_step": round(ms / args.steps, 5), "roofline": roofline,
+            print(json.dumps({"math": args.math, "value": round(value, 1), "ms_per_step": round(ms / args.steps, 5), "roofline": roofline,
                               "gpu_launches": int(launches), "clocks": clocks, "lib": os.environ.get("LGB200_LIB", "default")}))
         return
 
@@ -201,7 +202,7 @@ def run_ours(args):
     host_np = [t.numpy() for t in pinned]
     outs = [torch.empty((n, 3), dtype=torch.float64).pin_memory() for _ in range(4)]
     out_np = [t.numpy() for t in outs]
-    e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant)  # model tables built once (as a ctor would)
+    e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)  # model tables built once (as a ctor would)
     e2e_steps = args.steps
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -232,7 +233,7 @@ def run_ours(args):
         "config": {"workload": f"cfg4 multi-aggregate collision, {n} particles ({args.copies} x aggregate.h), sinter+contact+Hamaker, "
                                f"r_verlet=5r, rebuild every {REBUILD_EVERY} steps", "particles": n, "pairs": cnt["pairs"],
                    "bonds_ordered": cnt["bonds"], "contacts": cnt["contacts"], "l2_policy": "working set (>400 MB) larger than L2",
-                   "kernel_variant": args.variant},
+                   "kernel_variant": args.variant, "math_mode": "fast (<=1e-10 rel. forces, bit-exact sets)" if mode else "exact (bit-identical to the reference)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
     }
     if rank == 0 and not args.no_cpu_baseline:
@@ -253,7 +254,8 @@ def run_slab(args, scn, world, rank, local_rank):
     n = cfg.n
     dev = torch.device("cuda", local_rank)
     uv = numpy_unit_vectors(n + 1024)
-    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank)
+    mode = 1 if args.math == "fast" else 0
+    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode)
     warm = max(args.warmup, 3)
     sysm.run(cfg.dt, warm, REBUILD_EVERY)
     sysm.synchronize()
@@ -346,7 +348,7 @@ def run_slab(args, scn, world, rank, local_rank):
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"cfg4 multi-aggregate collision, {n} particles ({args.copies} x aggregate.h), sinter+contact+Hamaker, "
                                f"r_verlet=5r, rebuild every {REBUILD_EVERY} steps", "particles": n, "pairs": cnt["pairs"],
-                   "contacts": cnt["contacts"], "l2_policy": "per-rank working set larger than L2 up to 4 GPUs; at 8 GPUs "
+                   "contacts": cnt["contacts"], "math_mode": "fast" if mode else "exact", "l2_policy": "per-rank working set larger than L2 up to 4 GPUs; at 8 GPUs "
                    "(~100 MB/step/rank) the step streams through L2 once per step, no reuse across steps is possible "
                    "because every byte is rewritten each step",
                    "decomposition": f"{world} slabs along x, ghosts {cnt['ghosts_total']}, halo {cnt['halo_bytes_per_step']} B/step "
@@ -416,6 +418,9 @@ def main():
     ap.add_argument("--copies", type=int, default=6667, help="aggregates in the workload (6667 -> 1 000 050 particles)")
     ap.add_argument("--sample", type=int, default=34, help="aggregates in the CPU-reference sample (34 -> 5100 particles)")
     ap.add_argument("--variant", type=int, default=None, help="force kernel variant (0 simple, 1 tiled)")
+    ap.add_argument("--math", default="fast", choices=["fast", "exact"],
+                    help="arithmetic of the step kernel: fast = LG_MATH_FAST (forces within 1e-10 of the reference, sets "
+                         "bit-exact; tests/test_gpu_fast_math.py), exact = bit-identical to the reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel-only", action="store_true", help="tuning runs: device-resident throughput + roofline only")
     args = ap.parse_args()

@@ -199,6 +199,18 @@ int lg_get_counters(lg_system* s, int64_t out_8[8]);
  *   out[5..7] centre of mass      out[8] radius of gyration */
 int lg_diagnostics(lg_system* s, double out_9[9]);
 
+/* Arithmetic of the force laws in the tiled kernel.
+ *   LG_MATH_EXACT (default): the reference's operand order, IEEE division and square root, no FMA contraction --
+ *       x, v, theta, omega, a, alpha are bit-identical to the reference built with -ffp-contract=off.
+ *   LG_MATH_FAST: reciprocal square roots shared between the components of a normalisation, fused multiply-adds,
+ *       the four Hamaker fractions (hamaker_force.h:36-40) combined into one (-64 r^6 / (h^2 (2r+h)^3 (4r+h)^2)),
+ *       multiplication by 1/mass, 1/inertia.  Per-step forces and torques stay within 1e-10 relative of the
+ *       reference (the tolerance BASELINE.json states; measured ~1e-13), neighbor and contact SETS stay bit-exact
+ *       (overlap decisions inside a rounding band are re-taken on the exact expression), and pairs that are in
+ *       contact run the exact Luding law so their history springs evolve as in the reference. */
+enum { LG_MATH_EXACT = 0, LG_MATH_FAST = 1 };
+int lg_set_math_mode(lg_system* s, int mode);
+
 /* ---- slab decomposition (no reference counterpart -- the reference is single-process) ----
  * One lg_system per rank holds that rank's owned particles and its ghosts, ordered by global particle id.  The
  * functions below move device-resident tables in and out of a system (d_* = device pointers on its device) so that

@@ -98,6 +98,7 @@ struct lg_system {
     ModelParams mp{};
     int mask = 0;  // binary models
     int variant = 1;
+    int math_mode = 0;  // 0 = bit-exact (reference operand order, IEEE division), 1 = relaxed (lg_set_math_mode)
 
     PingPong x, v, w;         // read by other particles' pair evaluations -> double-buffered
     DevBuf<double> a, th, al;  // private to their particle -> single
@@ -261,6 +262,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     }
     A.err = s->err.p;
     A.rows_per_block = rows_per_block(s);
+    A.fast = s->math_mode;
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;
     A.x_next = s->x.next; A.v_next = s->v.next; A.w_next = s->w.next; A.th = s->th.p; A.bconn_next = s->bconn.next;
@@ -1241,10 +1243,20 @@ int lg_get_profile(lg_system* s, double* ms, int64_t* count) {
     return LG_OK;
 }
 
+int lg_set_math_mode(lg_system* s, int mode) {
+    LG_ENTER(s);
+    if (mode != 0 && mode != 1) return fail(LG_EINVAL, "math mode must be LG_MATH_EXACT (0) or LG_MATH_FAST (1)");
+    if (mode == 1 && s->variant != 1) return fail(LG_EINVAL, "the relaxed math mode exists for the tiled kernel variant only");
+    LG_TRY(flush(s));
+    s->math_mode = mode;
+    return LG_OK;
+}
+
 int lg_set_kernel_variant(lg_system* s, int variant) {
     LG_ENTER(s);
     if (variant != 0 && variant != 1) return fail(LG_EINVAL, "variant must be 0 or 1");
     LG_TRY(flush(s));
+    if (variant != 1 && s->math_mode != 0) return fail(LG_EINVAL, "the validation variant is bit-exact only; reset the math mode first");
     s->variant = variant;
     return LG_OK;
 }

@@ -124,7 +124,7 @@ __device__ __forceinline__ Accel unary_forces(const ForceArgs& A, int i, d3 xi, 
     return total;
 }
 
-template <int MASK, int MODE, bool FACETS>
+template <int MASK, int MODE, bool FACETS, bool FAST>
 __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
@@ -138,6 +138,11 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
     const int i0 = blockIdx.x * R;
     const int nrows = min(R, A.n - i0);
     const bool have_bonds = kSinter && A.bptr != nullptr;
+    // relaxed arithmetic: constants hoisted out of the pair loops; contact decisions inside a rounding band of
+    // zero overlap are re-taken on the reference's exact expression (sets stay bit-exact)
+    const HamakerFast hf = hamaker_fast_setup(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass);
+    const double two_r = 2.0 * A.mp.r, overlap_band = 1e-12 * A.mp.r;
+    const double inv_mass = 1.0 / A.mp.mass, inv_inertia = 1.0 / A.mp.inertia;
 
     // ---- stage the CTA's particles (coalesced: 3 * nrows consecutive doubles per field) ----------------
     for (int idx = tid; idx < 3 * nrows; idx += TB) {
@@ -194,13 +199,19 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                 const int j = j_cur;
                 const d3 xi = particle(r, 0);
                 const d3 xj = neighbour(j, 0, A.x);
-                const PairGeom g = pair_geometry(xi, xj);
+                const PairGeom g = FAST ? pair_geometry_fast(xi, xj) : pair_geometry(xi, xj);
                 if constexpr (kContact) {
                     const int t = t_cur;
                     if (kSinter && t >= kTagBond && t != kTagNone) {
                         kind = KIND_BOND;
                     } else {
-                        const double overlap = contact_overlap(g, 2.0 * A.mp.r);
+                        double overlap;
+                        if constexpr (FAST) {
+                            overlap = two_r - g.len;
+                            if (fabs(overlap) < overlap_band) overlap = contact_overlap(pair_geometry(xi, xj), two_r);
+                        } else {
+                            overlap = contact_overlap(g, 2.0 * A.mp.r);
+                        }
                         if (overlap <= 0) {
                             if (t != kTagNone) {  // reset_springs (contact_force.h:68-71)
                                 A.sgid[(size_t)(i0 + r) * A.S + t] = -1;
@@ -212,7 +223,10 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                     }
                 }
                 d3 h = zero3();
-                if constexpr (kHamaker) h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
+                if constexpr (kHamaker) {
+                    if constexpr (FAST) h = hamaker_accel_fast(hf, g);
+                    else h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
+                }
                 sm.tile[0 * TS + q] = h.x;
                 sm.tile[1 * TS + q] = h.y;
                 sm.tile[2 * TS + q] = h.z;
@@ -261,11 +275,19 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                     const double* cj = A.bconn + (size_t)A.brev[b] * 15;
                     const double* len = A.blen + (size_t)b * 5;
                     d3 force = zero3(), torque = zero3();
+                    if constexpr (FAST) {
+#pragma unroll
+                        for (int k = 0; k < 5; k++)
+                            bonded_spring_fast(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi,
+                                               vj, wi, wj, force, torque);
+                        c = Accel{force * inv_mass, torque * inv_inertia};
+                    } else {
 #pragma unroll 1
-                    for (int k = 0; k < 5; k++)
-                        bonded_spring(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi, vj,
-                                      wi, wj, force, torque);
-                    c = Accel{force / A.mp.mass, torque / A.mp.inertia};
+                        for (int k = 0; k < 5; k++)
+                            bonded_spring(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi, vj,
+                                          wi, wj, force, torque);
+                        c = Accel{force / A.mp.mass, torque / A.mp.inertia};
+                    }
                 } else {
                     const PairGeom g = pair_geometry(xi, xj);
                     const double overlap = contact_overlap(g, 2.0 * A.mp.r);
@@ -387,26 +409,27 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
     }
 }
 
-template <int MASK, int MODE, bool FACETS>
+template <int MASK, int MODE, bool FACETS, bool FAST>
 void launch_one(const ForceArgs& args, cudaStream_t st) {
     static bool configured = false;  // per instantiation
     if (!configured) {
-        cudaFuncSetAttribute(step_tiled_kernel<MASK, MODE, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        cudaFuncSetAttribute(step_tiled_kernel<MASK, MODE, FACETS, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)sizeof(Smem));
         configured = true;
     }
     const int R = args.rows_per_block;
     const int blocks = (args.n + R - 1) / R;
-    step_tiled_kernel<MASK, MODE, FACETS><<<blocks, TB, sizeof(Smem), st>>>(args);
+    step_tiled_kernel<MASK, MODE, FACETS, FAST><<<blocks, TB, sizeof(Smem), st>>>(args);
     g_launch_count++;
 }
 
 template <int MASK, int MODE>
 void launch_facets(const ForceArgs& args, cudaStream_t st) {
-    if (args.n_facets > 0)
-        launch_one<MASK, MODE, true>(args, st);
-    else
-        launch_one<MASK, MODE, false>(args, st);
+    if (args.n_facets > 0) {
+        if (args.fast) launch_one<MASK, MODE, true, true>(args, st); else launch_one<MASK, MODE, true, false>(args, st);
+    } else {
+        if (args.fast) launch_one<MASK, MODE, false, true>(args, st); else launch_one<MASK, MODE, false, false>(args, st);
+    }
 }
 
 template <int MODE>

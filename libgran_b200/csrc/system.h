@@ -72,6 +72,7 @@ struct ForceArgs {
     int* err;
     // tiled / fused kernel only
     int rows_per_block;
+    int fast;           // relaxed arithmetic (lg_set_math_mode)
     double dt;          // integration step of the fused update
     double* x_next;     // next-step buffers (double-buffered state)
     double* v_next;

@@ -404,7 +404,7 @@ class SlabSystem:
     Every rank constructs it with the same full initial state (the driver program's x0, v0, theta0, omega0)."""
 
     def __init__(self, cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = 0, group=None, skin: Optional[float] = None,
-                 axis: int = 0, max_contacts: int = 16):
+                 axis: int = 0, max_contacts: int = 16, math_mode: int = 0):
         from . import system as _sys
         from .scenarios import MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
 
@@ -424,6 +424,7 @@ class SlabSystem:
         self.skin = float(skin) if skin is not None else 1.0 * cfg.r_part
         self.r_ghost = cfg.r_verlet + self.skin
         self.S = max_contacts
+        self.math_mode = int(math_mode)
         self.n_global = len(x0)
         self.h = C.c_void_p()
         self.steps = 0
@@ -466,6 +467,8 @@ class SlabSystem:
             raise RuntimeError("slab decomposition left a rank without particles")
         self._check(lib.lg_create(n, cfg.r_part, cfg.mass, cfg.inertia, self.dev_index, C.byref(self.h)))
         self._check(lib.lg_set_max_contacts(self.h, self.S))
+        if self.math_mode:
+            self._check(lib.lg_set_math_mode(self.h, self.math_mode))
         st = t.state
         cols = [st[:, 3 * k:3 * k + 3].contiguous() for k in range(6)]  # x v theta omega a alpha
         self._check(lib.lg_import_state_device(self.h, *[c.data_ptr() for c in cols], int(self.kicked)))

@@ -30,7 +30,7 @@ ABI_SYMBOLS = (
     "lg_get_neighbor_count", "lg_get_neighbor_rows", "lg_get_contact_springs", "lg_get_bond", "lg_get_counters",
     "lg_diagnostics", "lg_set_kernel_variant", "lg_get_stream", "lg_set_profiling", "lg_get_profile",
     "lg_bond_table_create", "lg_bond_table_count", "lg_bond_table_records", "lg_bond_table_destroy", "lg_set_bond_table",
-    "lg_facet_set_vertices",
+    "lg_facet_set_vertices", "lg_set_math_mode",
     # slab decomposition support
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
@@ -116,6 +116,7 @@ def load_library(path: Optional[str] = None):
     lib.lg_bond_table_destroy.argtypes = [vp]
     lib.lg_set_bond_table.argtypes = [vp, cpp, C.c_double, C.c_double, vp]
     lib.lg_facet_set_vertices.argtypes = [vp, C.c_int, dp]
+    lib.lg_set_math_mode.argtypes = [vp, C.c_int]
     # slab decomposition support: device pointers travel as plain integers
     lib.lg_flush.argtypes = [vp]
     lib.lg_first_half_kick.argtypes = [vp, C.c_double]
@@ -271,6 +272,10 @@ class GranularSystem:
         self._check(self.lib.lg_set_kernel_variant(self.h, int(variant)))
 
     # -- the reference's driver-facing calls --------------------------------------------------------
+    def set_math_mode(self, mode: int):
+        """0 = bit-exact (default), 1 = relaxed arithmetic (see lg_set_math_mode)."""
+        self._check(self.lib.lg_set_math_mode(self.h, int(mode)))
+
     def update_neighbor_list(self):
         self._check(self.lib.lg_update_neighbor_list(self.h))
 
@@ -354,7 +359,8 @@ class GranularSystem:
                 "rg": out[8]}
 
 
-def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1, variant: Optional[int] = None) -> GranularSystem:
+def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1, variant: Optional[int] = None,
+                math_mode: int = 0) -> GranularSystem:
     """Build a GranularSystem from a ``scenarios.DemConfig`` (same meaning as oracle/dem_config.h)."""
     from .scenarios import MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
 
@@ -362,6 +368,8 @@ def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1
                           r_verlet=cfg.r_verlet if cfg.use_neighbor_list else None)
     if variant is not None:
         sysm.set_kernel_variant(variant)
+    if math_mode:
+        sysm.set_math_mode(math_mode)
     if cfg.model_mask & MODEL_CONTACT:
         sysm.set_contact(cfg.contact)
     if cfg.model_mask & MODEL_SINTER:
