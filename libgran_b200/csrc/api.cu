@@ -263,6 +263,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.err = s->err.p;
     A.rows_per_block = rows_per_block(s);
     A.fast = s->math_mode;
+    A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia);
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;
     A.x_next = s->x.next; A.v_next = s->v.next; A.w_next = s->w.next; A.th = s->th.p; A.bconn_next = s->bconn.next;

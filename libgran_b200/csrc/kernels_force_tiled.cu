@@ -46,8 +46,10 @@ namespace {
 constexpr int TB = LG_TB;      // threads per CTA
 constexpr int TILE = LG_TILE;  // pairs per tile
 constexpr int RMAX = LG_RMAX;  // max particles per CTA (<= TB)
+constexpr int BCAP = 4 * RMAX; // bond records per CTA with a precomputed owner row (beyond: binary search)
 constexpr int TS = TILE + 1;   // padded component stride of the tile (bank spread for phase C)
-static_assert(RMAX <= TB, "one staging pass per CTA");
+static_assert(RMAX <= TB && RMAX <= 256, "one staging pass per CTA; local rows are stored in a byte");
+static_assert(TILE % TB == 0, "phase A handles TILE / TB pairs per thread");
 static_assert(15 * RMAX <= 6 * TS, "the output staging area reuses the tile");
 
 enum : int { MODE_FORCE = 0, MODE_FUSED = 1 };
@@ -62,6 +64,7 @@ struct Smem {
     uint32_t sbptr[RMAX + 1];
     uint16_t heavy[TILE];
     uint8_t srow[TILE];     // local row of every pair of the tile (written by the row owners, replaces a search)
+    uint8_t brow[BCAP];     // local row of the CTA's first BCAP bond records (connector stage)
     int cnt[2];
 };
 
@@ -124,11 +127,42 @@ __device__ __forceinline__ Accel unary_forces(const ForceArgs& A, int i, d3 xi, 
     return total;
 }
 
+// The Luding contact law with its history springs for ONE overlapping ordered pair (phase B).  Kept out of line
+// on purpose: it needs ~110 registers and runs for a small minority of pairs, so the kernel's register budget
+// (and with it the number of resident warps) is set by the Hamaker / bridge paths instead; everything it needs
+// is re-read from global memory (L1/L2 hits).  Always the reference's exact arithmetic, in both math modes.
+__device__ __noinline__ void contact_heavy(const ForceArgs& A, int i, int j, uint32_t p, double* out6) {
+    const d3 xi = load3(A.x + 3 * (size_t)i), vi = load3(A.v + 3 * (size_t)i), wi = load3(A.w + 3 * (size_t)i);
+    const d3 xj = load3(A.x + 3 * (size_t)j), vj = load3(A.v + 3 * (size_t)j), wj = load3(A.w + 3 * (size_t)j);
+    const int t = A.tag[p];
+    const PairGeom g = pair_geometry(xi, xj);
+    const double overlap = contact_overlap(g, 2.0 * A.mp.r);
+    int slot = t;
+    Springs s;
+    if (t == kTagNone) {  // first overlapping evaluation: claim a free slot of particle i
+        slot = -1;
+        for (int k = 0; k < A.S; k++)
+            if (atomicCAS(&A.sgid[(size_t)i * A.S + k], -1, j) == -1) {  // bookkeeping only
+                slot = k;
+                break;
+            }
+        s.xi[0] = s.xi[1] = s.xi[2] = zero3();
+        if (slot >= 0) A.tag[p] = (uint8_t)slot; else atomicOr(A.err, ERR_SLOT_OVERFLOW);
+    } else {
+        s = ld_springs(A.spr + ((size_t)i * A.S + slot) * 9);
+    }
+    const Accel c = contact_force(A.mp.cp, A.mp.r, A.mp.mass, A.mp.inertia, g, overlap, vi, vj, wi, wj, s);
+    if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
+    store3(out6, c.a);
+    store3(out6 + 3, c.alpha);
+}
+
 template <int MASK, int MODE, bool FACETS, bool FAST>
 __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
     constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
+    constexpr int PPT = TILE / TB;  // pairs per thread and tile in phase A
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     Smem& sm = *reinterpret_cast<Smem*>(smem_raw);
@@ -138,11 +172,6 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
     const int i0 = blockIdx.x * R;
     const int nrows = min(R, A.n - i0);
     const bool have_bonds = kSinter && A.bptr != nullptr;
-    // relaxed arithmetic: constants hoisted out of the pair loops; contact decisions inside a rounding band of
-    // zero overlap are re-taken on the reference's exact expression (sets stay bit-exact)
-    const HamakerFast hf = hamaker_fast_setup(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass);
-    const double two_r = 2.0 * A.mp.r, overlap_band = 1e-12 * A.mp.r;
-    const double inv_mass = 1.0 / A.mp.mass, inv_inertia = 1.0 / A.mp.inertia;
 
     // ---- stage the CTA's particles (coalesced: 3 * nrows consecutive doubles per field) ----------------
     for (int idx = tid; idx < 3 * nrows; idx += TB) {
@@ -158,10 +187,16 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
     if (tid <= nrows) {
         const uint32_t rp = A.row_ptr[i0 + tid];
         sm.sptr[tid] = rp;
-        sm.sbptr[tid] = have_bonds ? A.bptr[i0 + tid] : 0u;
-        if (tid < nrows) {  // local-row map of the first tile
+        const uint32_t bp = have_bonds ? A.bptr[i0 + tid] : 0u;
+        sm.sbptr[tid] = bp;
+        if (tid < nrows) {
+            // local-row map of the first tile, and of this particle's bond records (connector stage)
             const uint32_t lo = rp - p_begin, hi = min(A.row_ptr[i0 + tid + 1] - p_begin, (uint32_t)TILE);
             for (uint32_t q = lo; q < hi; q++) sm.srow[q] = (uint8_t)tid;
+            if (MODE == MODE_FUSED && have_bonds) {
+                const uint32_t b0 = A.bptr[i0], b1 = A.bptr[i0 + tid + 1];
+                for (uint32_t b = bp; b < b1 && b - b0 < (uint32_t)BCAP; b++) sm.brow[b - b0] = (uint8_t)tid;
+            }
         }
     }
     if (tid == 0) sm.cnt[0] = sm.cnt[1] = 0;
@@ -179,57 +214,69 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
         const int cntp = (int)min((uint32_t)TILE, p_end - tile_start);
 
         // ---- phase A: light work for every pair, classify ------------------------------------------------
-        // columns / tags of the next pass are requested before the current pass computes (latency hiding)
-        int j_cur = 0, t_cur = kTagNone;
-        if (tid < cntp) {
-            j_cur = A.cols[tile_start + tid];
-            if constexpr (kContact) t_cur = A.tag[tile_start + tid];
-        }
-        for (int qb = 0; qb < cntp; qb += TB) {
-            const int q = qb + tid;
-            int j_nxt = 0, t_nxt = kTagNone;
-            if (q + TB < cntp) {
-                j_nxt = A.cols[tile_start + q + TB];
-                if constexpr (kContact) t_nxt = A.tag[tile_start + q + TB];
+        // All of a thread's PPT pairs are loaded before any is computed (PPT gathers in flight per thread), and
+        // the straight-line geometry + Hamaker arithmetic of the PPT pairs is independent (instruction-level
+        // parallelism for the FP64 pipe); classification, which branches, comes last.
+        int jv[PPT], tv[PPT];
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int q = tid + k * TB;
+            jv[k] = -1;
+            tv[k] = kTagNone;
+            if (q < cntp) {
+                jv[k] = A.cols[tile_start + q];
+                if constexpr (kContact) tv[k] = A.tag[tile_start + q];
             }
+        }
+        d3 xjv[PPT];
+#pragma unroll
+        for (int k = 0; k < PPT; k++) xjv[k] = jv[k] >= 0 ? neighbour(jv[k], 0, A.x) : zero3();
+        d3 hv[PPT];
+        double ov[PPT];  // contact overlap (exact mode: the reference's value; fast mode: 2r - len, refined below)
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int q = tid + k * TB;
+            const int r = q < cntp ? sm.srow[q] : 0;
+            const d3 xi = particle(r, 0);
+            hv[k] = zero3();
+            if constexpr (FAST) {
+                const PairGeom g = pair_geometry_fast(xi, xjv[k]);
+                ov[k] = A.fc.two_r - g.len;
+                if constexpr (kHamaker) hv[k] = hamaker_accel_fast(A.fc, g);
+            } else {
+                const PairGeom g = pair_geometry(xi, xjv[k]);
+                ov[k] = contact_overlap(g, 2.0 * A.mp.r);
+                if constexpr (kHamaker) hv[k] = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < PPT; k++) {
+            const int q = tid + k * TB;
             int kind = KIND_LIGHT;
             if (q < cntp) {
-                const uint32_t p = tile_start + q;
-                const int r = sm.srow[q];
-                const int j = j_cur;
-                const d3 xi = particle(r, 0);
-                const d3 xj = neighbour(j, 0, A.x);
-                const PairGeom g = FAST ? pair_geometry_fast(xi, xj) : pair_geometry(xi, xj);
                 if constexpr (kContact) {
-                    const int t = t_cur;
+                    const int t = tv[k];
                     if (kSinter && t >= kTagBond && t != kTagNone) {
                         kind = KIND_BOND;
                     } else {
-                        double overlap;
-                        if constexpr (FAST) {
-                            overlap = two_r - g.len;
-                            if (fabs(overlap) < overlap_band) overlap = contact_overlap(pair_geometry(xi, xj), two_r);
-                        } else {
-                            overlap = contact_overlap(g, 2.0 * A.mp.r);
+                        double overlap = ov[k];
+                        if constexpr (FAST) {  // inside a rounding band of zero: decide on the exact expression
+                            if (fabs(overlap) < A.fc.band)
+                                overlap = contact_overlap(pair_geometry(particle(sm.srow[q], 0), xjv[k]), A.fc.two_r);
                         }
                         if (overlap <= 0) {
                             if (t != kTagNone) {  // reset_springs (contact_force.h:68-71)
-                                A.sgid[(size_t)(i0 + r) * A.S + t] = -1;
-                                A.tag[p] = (uint8_t)kTagNone;
+                                A.sgid[(size_t)(i0 + sm.srow[q]) * A.S + t] = -1;
+                                A.tag[tile_start + q] = (uint8_t)kTagNone;
                             }
                         } else {
                             kind = KIND_CONTACT;
                         }
                     }
                 }
-                d3 h = zero3();
-                if constexpr (kHamaker) {
-                    if constexpr (FAST) h = hamaker_accel_fast(hf, g);
-                    else h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
-                }
-                sm.tile[0 * TS + q] = h.x;
-                sm.tile[1 * TS + q] = h.y;
-                sm.tile[2 * TS + q] = h.z;
+                sm.tile[0 * TS + q] = hv[k].x;
+                sm.tile[1 * TS + q] = hv[k].y;
+                sm.tile[2 * TS + q] = hv[k].z;
                 sm.tile[3 * TS + q] = 0.0;
                 sm.tile[4 * TS + q] = 0.0;
                 sm.tile[5 * TS + q] = 0.0;
@@ -250,8 +297,6 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                     if (kind == KIND_CONTACT) sm.heavy[TILE - 1 - (base_c + __popc(mc & lt))] = (uint16_t)q;
                 }
             }
-            j_cur = j_nxt;
-            t_cur = t_nxt;
         }
         __syncthreads();
 
@@ -263,25 +308,34 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                 const int q = is_bond ? sm.heavy[e] : sm.heavy[TILE - 1 - (e - nB)];
                 const uint32_t p = tile_start + q;
                 const int r = sm.srow[q];
-                const int i = i0 + r;
                 const int j = A.cols[p];
-                const d3 xi = particle(r, 0), vi = particle(r, 1), wi = particle(r, 2);
-                const d3 xj = neighbour(j, 0, A.x), vj = neighbour(j, 1, A.v), wj = neighbour(j, 2, A.w);
-                const int t = A.tag[p];
                 Accel c;
                 if (kSinter && is_bond) {
+                    const int t = A.tag[p];
                     const uint32_t b = sm.sbptr[r] + (uint32_t)(t - kTagBond);
                     const double* ci = A.bconn + (size_t)b * 15;
                     const double* cj = A.bconn + (size_t)A.brev[b] * 15;
                     const double* len = A.blen + (size_t)b * 5;
+                    const d3 xi = particle(r, 0), xj = neighbour(j, 0, A.x);
                     d3 force = zero3(), torque = zero3();
                     if constexpr (FAST) {
+                        if (A.mp.gamma_d != 0.0) {
+                            const d3 vi = particle(r, 1), wi = particle(r, 2);
+                            const d3 vj = neighbour(j, 1, A.v), wj = neighbour(j, 2, A.w);
 #pragma unroll
-                        for (int k = 0; k < 5; k++)
-                            bonded_spring_fast(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi,
-                                               vj, wi, wj, force, torque);
-                        c = Accel{force * inv_mass, torque * inv_inertia};
+                            for (int k = 0; k < 5; k++)
+                                bonded_spring_fast<true>(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi,
+                                                         xj, vi, vj, wi, wj, force, torque);
+                        } else {  // undamped bridges (the reference's tests): velocities are not needed at all
+#pragma unroll
+                            for (int k = 0; k < 5; k++)
+                                bonded_spring_fast<false>(A.mp.k_d, 0.0, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj,
+                                                          zero3(), zero3(), zero3(), zero3(), force, torque);
+                        }
+                        c = Accel{force * A.fc.inv_mass, torque * A.fc.inv_inertia};
                     } else {
+                        const d3 vi = particle(r, 1), wi = particle(r, 2);
+                        const d3 vj = neighbour(j, 1, A.v), wj = neighbour(j, 2, A.w);
 #pragma unroll 1
                         for (int k = 0; k < 5; k++)
                             bonded_spring(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi, vj,
@@ -289,24 +343,9 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                         c = Accel{force / A.mp.mass, torque / A.mp.inertia};
                     }
                 } else {
-                    const PairGeom g = pair_geometry(xi, xj);
-                    const double overlap = contact_overlap(g, 2.0 * A.mp.r);
-                    int slot = t;
-                    Springs s;
-                    if (t == kTagNone) {  // first overlapping evaluation: claim a free slot of particle i
-                        slot = -1;
-                        for (int k = 0; k < A.S; k++)
-                            if (atomicCAS(&A.sgid[(size_t)i * A.S + k], -1, j) == -1) {  // bookkeeping only
-                                slot = k;
-                                break;
-                            }
-                        s.xi[0] = s.xi[1] = s.xi[2] = zero3();
-                        if (slot >= 0) A.tag[p] = (uint8_t)slot; else atomicOr(A.err, ERR_SLOT_OVERFLOW);
-                    } else {
-                        s = ld_springs(A.spr + ((size_t)i * A.S + slot) * 9);
-                    }
-                    c = contact_force(A.mp.cp, A.mp.r, A.mp.mass, A.mp.inertia, g, overlap, vi, vj, wi, wj, s);
-                    if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
+                    double out6[6];
+                    contact_heavy(A, i0 + r, j, p, out6);
+                    c = Accel{load3(out6), load3(out6 + 3)};
                 }
                 if constexpr (kHamaker) {  // pair value = (contact | sinter)(i,j) + hamaker(i,j)
                     sm.tile[0 * TS + q] = c.a.x + sm.tile[0 * TS + q];
@@ -397,8 +436,8 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
             const uint32_t b0 = sm.sbptr[0];
             const int ncon = (int)(sm.sbptr[nrows] - b0) * 5;
             for (int cq = tid; cq < ncon; cq += TB) {
-                const uint32_t b = b0 + (uint32_t)(cq / 5);
-                const int r = find_row(sm.sbptr, nrows, b);
+                const int bl = cq / 5;
+                const int r = bl < BCAP ? (int)sm.brow[bl] : find_row(sm.sbptr, nrows, b0 + (uint32_t)bl);
                 const size_t off = (size_t)b0 * 15 + 3 * (size_t)cq;
                 d3 ck = load3(A.bconn + off) + load3(out + 4 * OB + 3 * r);
                 const d3 sv = ck - load3(out + 0 * OB + 3 * r);

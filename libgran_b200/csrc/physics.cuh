@@ -187,15 +187,20 @@ __device__ __forceinline__ PairGeom pair_geometry_fast(d3 xi, d3 xj) {
     return g;
 }
 
-// constants of the combined Hamaker term, hoisted out of the pair loop
-struct HamakerFast {
+#endif
+// constants of the relaxed laws, computed once on the host (api.cu: evaluate)
+struct FastConsts {
     double c0m;  // (A / 6) * 64 r^6 / mass
     double r2, r4, h0;
+    double two_r, band;  // contact decision: |2r - len| < band is re-taken on the exact expression
+    double inv_mass, inv_inertia;
 };
-__device__ __forceinline__ HamakerFast hamaker_fast_setup(double A, double h0, double r, double mass) {
+inline FastConsts fast_consts(double A, double h0, double r, double mass, double inertia) {
     const double r3 = r * r * r;
-    return HamakerFast{A / 6.0 * 64.0 * r3 * r3 / mass, 2.0 * r, 4.0 * r, h0};
+    return FastConsts{A / 6.0 * 64.0 * r3 * r3 / mass, 2.0 * r, 4.0 * r, h0, 2.0 * r, 1e-12 * r, 1.0 / mass, 1.0 / inertia};
 }
+typedef FastConsts HamakerFast;
+#if defined(__CUDACC__)
 // (4r+2h)/((4r+h)h) - 2/(2r+h) - 4r^2/(2r+h)^3 - 2r^2(4r+2h)/((4r+h)^2 h^2)  ==  -64 r^6 / (h^2 (2r+h)^3 (4r+h)^2)
 __device__ __forceinline__ d3 hamaker_accel_fast(const HamakerFast& hf, const PairGeom& g) {
     double h = g.len - hf.r2;
@@ -207,6 +212,7 @@ __device__ __forceinline__ d3 hamaker_accel_fast(const HamakerFast& hf, const Pa
     return (-coef) * g.n;
 }
 
+template <bool DAMPED>
 __device__ __forceinline__ void bonded_spring_fast(double k_d, double gamma_d, double eq, d3 ci, d3 cj, d3 xi, d3 xj, d3 vi,
                                                    d3 vj, d3 wi, d3 wj, d3& force, d3& torque) {
     // The stretch (length - eq) cancels to ~1e-5 of the length near equilibrium, so the length keeps the
@@ -217,7 +223,7 @@ __device__ __forceinline__ void bonded_spring_fast(double k_d, double gamma_d, d
     const double inv = z > 0.0 ? 1.0 / spring_length : 0.0;
     const d3 arm = ci - xi;
     d3 dforce = (((-(eq - spring_length)) * k_d) * inv) * spring;
-    if (gamma_d != 0.0) {
+    if constexpr (DAMPED) {
         const d3 ci_v = vi + cross_fma(wi, arm);
         const d3 cj_v = vj + cross_fma(wj, cj - xj);
         const d3 rel_v = cj_v - ci_v;

@@ -1,7 +1,11 @@
 set -x; mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q 2>&1 | tail -3 > gpurun_out/tune_tests.log
 : > gpurun_out/tune.jsonl
-python bench.py --steps 200 --warmup 20 --kernel-only >> gpurun_out/tune.jsonl 2>> gpurun_out/tune.err
+python bench.py --steps 100 --warmup 10 --kernel-only >> gpurun_out/tune.jsonl 2>> gpurun_out/tune.err
 for v in libgran_b200/variants/*.so; do
-  LGB200_LIB=$PWD/$v python bench.py --steps 200 --warmup 20 --kernel-only >> gpurun_out/tune.jsonl 2>> gpurun_out/tune.err
+  LGB200_LIB=$PWD/$v python bench.py --steps 100 --warmup 10 --kernel-only >> gpurun_out/tune.jsonl 2>> gpurun_out/tune.err
 done
+python - <<'PY'
+import json
+for l in open('gpurun_out/tune.jsonl'):
+    d=json.loads(l); print(d['lib'].split('/')[-1], d['math'], d['ms_per_step'], d['roofline']['avg_launch_ms'])
+PY
