@@ -37,6 +37,9 @@ sys.path.insert(0, ROOT)
 from libgran_b200 import scenarios as S  # noqa: E402
 
 METRIC = "particle-timesteps/s"
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused step kernel on this workload, from the committed
+# `ncu --set full` captures (profiles/r01d_step_tiled_ncu_raw.csv: 482.0 MB + 301.7 MB; exact mode r01b: 482 + 301 MB)
+TRAFFIC_NCU = {"fast": 783.8e6, "exact": 783.0e6}
 REBUILD_EVERY = 20
 
 
@@ -180,10 +183,15 @@ def run_ours(args):
     step_bytes, force_bytes = algorithmic_bytes(n, cnt["pairs"], cnt["contacts"], cnt["bonds"])
     peak, peak_src = measured_peaks()
     force_avg_ms = force_ms / max(force_launches, 1)
-    achieved = force_bytes / (force_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "pair_force", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": None, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": int(force_bytes), "avg_launch_ms": round(force_avg_ms, 5),
+    # the production launch is the FUSED step kernel (force + Verlet + connector update): it moves the whole B_step;
+    # the validation variant's force-only kernel moves force_bytes
+    fused = args.variant in (None, 1)
+    launch_bytes = step_bytes if fused else force_bytes
+    achieved = launch_bytes / (force_avg_ms * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": "step_tiled_kernel (fused pair force + Verlet + connectors)" if fused else "pair_force",
+                "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                "frac": round(achieved / peak, 4), "traffic": TRAFFIC_NCU.get(args.math if fused else "variant0"), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": int(launch_bytes), "avg_launch_ms": round(force_avg_ms, 5),
                 "launches_timed": int(force_launches),
                 "share_of_step": round(force_avg_ms / (ms / args.steps), 3),
                 "whole_step": {"algorithmic_bytes_per_step": int(step_bytes),
@@ -237,7 +245,7 @@ def run_ours(args):
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
     }
     if rank == 0 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = run_reference_sample(args, steps=40, warmup=5)
+        line["cpu_baseline"] = run_reference_sample(args, steps=args.cpu_steps, warmup=5)
     if rank == 0:
         print(json.dumps(line))
 
@@ -421,6 +429,7 @@ def main():
     ap.add_argument("--math", default="fast", choices=["fast", "exact"],
                     help="arithmetic of the step kernel: fast = LG_MATH_FAST (forces within 1e-10 of the reference, sets "
                          "bit-exact; tests/test_gpu_fast_math.py), exact = bit-identical to the reference")
+    ap.add_argument("--cpu-steps", type=int, default=10000, help="time steps of the CPU-reference sample (about 10 s of CPU work)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel-only", action="store_true", help="tuning runs: device-resident throughput + roofline only")
     args = ap.parse_args()
