@@ -202,7 +202,7 @@ def run_ours(args):
     if args.kernel_only:
         if rank == 0:
             print(json.dumps({"math": args.math, "value": round(value, 1), "ms_per_step": round(ms / args.steps, 5), "roofline": roofline,
-                              "gpu_launches": int(launches), "clocks": clocks, "lib": os.environ.get("LGB200_LIB", "default")}))
+                              "gpu_launches": int(launches), "clocks": clocks, "lib": os.environ.get("LGB200_LIB", "default"), "tag": os.environ.get("LGB200_TAG")}))
         return
 
     # ---- end to end through the host-facing API with host buffers ---------------------------------
@@ -360,7 +360,7 @@ def run_slab(args, scn, world, rank, local_rank):
                    "(~100 MB/step/rank) the step streams through L2 once per step, no reuse across steps is possible "
                    "because every byte is rewritten each step",
                    "decomposition": f"{world} slabs along x, ghosts {cnt['ghosts_total']}, halo {cnt['halo_bytes_per_step']} B/step "
-                                    f"sent by rank 0, repartitions {cnt['repartitions']}"},
+                                    f"sent by rank 0, repartitions {cnt['repartitions']}, halo transport {cnt['transport']}"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
     }
     if rank == 0:

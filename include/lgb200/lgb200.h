@@ -246,6 +246,27 @@ int lg_halo_pack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, cons
 int lg_halo_unpack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec,
                    const double* d_in);
 
+/* Peer-to-peer halo exchange over NVLink, without a host transport in the time loop.  Each rank allocates ONE
+ * receive buffer (two parity halves, a flag per peer and half) and exports it with cudaIpcGetMemHandle; a neighbour
+ * maps it (lg_halo_connect) and its pack kernel stores x, v, omega and connector blocks straight into it, then
+ * publishes a sequence number with a system-scope release store.  lg_halo_exchange queues, on the system's stream,
+ * the push to every peer and a pull that waits for the peers' sequence numbers (bounded: ERR -> LG_ECUDA at the next
+ * synchronisation) and scatters into the ghost slots.  The launcher exchanges the 64-byte handles and offsets between
+ * ranks (libgran_b200/slab.py does it over torch.distributed).  Message layout as lg_halo_pack.
+ * Order of teardown across ranks: every rank lg_halo_disconnect, barrier, then lg_halo_destroy. */
+typedef struct lg_halo lg_halo;
+int lg_halo_create(lg_system* s, int n_peers, const int64_t* recv_doubles, lg_halo** out);
+int lg_halo_set_lists(lg_halo* h, int peer, int n_send_part, const int32_t* d_send_idx, int n_send_rec,
+                      const int32_t* d_send_rec, int n_recv_part, const int32_t* d_recv_idx, int n_recv_rec,
+                      const int32_t* d_recv_rec);
+int lg_halo_export(lg_halo* h, int peer, unsigned char handle[64], int64_t offs[4]);
+int lg_halo_connect(lg_halo* h, int peer, const unsigned char handle[64], const int64_t offs[4]);
+int lg_halo_exchange(lg_system* s, lg_halo* h);
+/* n_steps x (lg_do_step, lg_halo_exchange) without returning to the caller (no neighbor rebuild inside). */
+int lg_run_slab(lg_system* s, lg_halo* h, double dt, int64_t n_steps);
+int lg_halo_disconnect(lg_halo* h);
+int lg_halo_destroy(lg_halo* h);
+
 /* The CUDA stream (cudaStream_t) all work of this system is queued on, so that callers can time it with
  * events or order their own copies against it. */
 int lg_get_stream(lg_system* s, void** stream);

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <memory>
@@ -122,6 +123,14 @@ struct lg_system {
     DevBuf<int32_t> cols;
     DevBuf<uint8_t> tag;
     int64_t n_pairs = 0;
+    // Rows rebuilt while a closing evaluation was still pending: that evaluation belongs to the OLD rows, so the new
+    // ones wait here and are installed (swap + retag) right after it has run -- the step after a rebuild then stays
+    // ONE fused launch instead of force-only + integrate (rebuild(), evaluate()).
+    DevBuf<uint32_t> row_ptr_new;
+    DevBuf<int32_t> cols_new;
+    DevBuf<uint8_t> tag_new;
+    int64_t n_pairs_new = 0;
+    bool rows_staged = false;
 
     // contact slots
     int S = 16;
@@ -176,6 +185,7 @@ int check_async(lg_system* s) {
     if (h & ERR_SLOT_OVERFLOW)
         return fail(LG_ECAPACITY, "a particle has more simultaneous contacts than lg_set_max_contacts allows");
     if (h & ERR_BOND_LOOKUP) return fail(LG_ECAPACITY, "bond table lookup failed");
+    if (h & ERR_HALO_TIMEOUT) return fail(LG_ECUDA, "halo exchange: a neighbouring rank did not publish its message in time");
     return LG_OK;
 }
 
@@ -203,6 +213,21 @@ int retag(lg_system* s) {
                  s->n_bonds > 0 ? s->bptr.p : nullptr, s->bj.p, s->err.p, s->stream);
     LG_CUDA(cudaGetLastError());
     return LG_OK;
+}
+
+template <typename T>
+void swap_buf(DevBuf<T>& a, DevBuf<T>& b) {
+    std::swap(a.p, b.p);
+    std::swap(a.cap, b.cap);
+}
+
+int install_staged_rows(lg_system* s) {
+    swap_buf(s->row_ptr, s->row_ptr_new);
+    swap_buf(s->cols, s->cols_new);
+    swap_buf(s->tag, s->tag_new);
+    s->n_pairs = s->n_pairs_new;
+    s->rows_staged = false;
+    return retag(s);
 }
 
 int build_allpairs(lg_system* s) {
@@ -236,7 +261,12 @@ int drain_profile(lg_system* s) {
 int rows_per_block(const lg_system* s) {
     // aim at one (almost full) tile of pairs per CTA
     const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 1.0;
-    int r = (int)std::lround(0.977 * tiled_tile_pairs() / std::max(k_mean, 1.0));
+    static const double fill = [] {  // tuning knob: fraction of the tile the average CTA fills
+        const char* e = std::getenv("LGB200_TILE_FILL");
+        const double f = e ? std::atof(e) : 0.0;
+        return (f > 0.05 && f <= 1.0) ? f : 0.977;
+    }();
+    int r = (int)std::lround(fill * tiled_tile_pairs() / std::max(k_mean, 1.0));
     r = std::max(8, std::min(r, tiled_max_rows_per_block()));
     return r;
 }
@@ -291,6 +321,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         s->w.swap();
         if (s->n_bonds > 0) s->bconn.swap();
     }
+    if (s->rows_staged) LG_TRY(install_staged_rows(s));  // this was the evaluation the old rows were kept for
     return LG_OK;
 }
 
@@ -359,8 +390,16 @@ int rebuild(lg_system* s) {
     if (!s->use_nl) return LG_OK;  // granular_system (all pairs) has no update_neighbor_list
     if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
     LG_TRY(ensure_slots(s));
-    LG_TRY(flush(s));  // the pending evaluation belongs to the OLD rows (it closed the previous do_step)
+    // The pending evaluation belongs to the OLD rows (it closed the previous do_step).  In the steady state of the
+    // fused variant it stays pending: the new rows are built next to the old ones (they depend on x only, which
+    // the evaluation does not change) and are installed by evaluate() once the evaluation has run.
+    const bool defer = s->pending && s->variant == 1 && s->rebuilds > 0 && s->n_pairs > 0;
+    if (!defer) LG_TRY(flush(s));
     const int n = (int)s->n;
+    if (defer) LG_CUDA(s->row_ptr_new.reserve((size_t)n + 1));
+    DevBuf<uint32_t>& row_ptr = defer ? s->row_ptr_new : s->row_ptr;
+    DevBuf<int32_t>& cols = defer ? s->cols_new : s->cols;
+    DevBuf<uint8_t>& tag = defer ? s->tag_new : s->tag;
     cudaStream_t st = s->stream;
     // 1. bounding box -> grid
     launch_bbox(n, s->x.p, s->bbox_scratch.p, s->bbox_out.p, st);
@@ -400,18 +439,26 @@ int rebuild(lg_system* s) {
     launch_cell_fill(n, s->cell_of.p, s->cell_start.p, s->cell_cursor.p, s->order.p, st);
     // 3. rows: count, scan, fill + sort
     const uint8_t* owned = s->has_owned ? s->owned.p : nullptr;
-    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, owned, st);
-    LG_CUDA(cudaMemsetAsync(s->row_ptr.p + n, 0, sizeof(uint32_t), st));
-    launch_exclusive_scan_u32(s->row_ptr.p, (size_t)n + 1, s->scan_scratch.p, st);
+    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, owned, st);
+    LG_CUDA(cudaMemsetAsync(row_ptr.p + n, 0, sizeof(uint32_t), st));
+    launch_exclusive_scan_u32(row_ptr.p, (size_t)n + 1, s->scan_scratch.p, st);
     LG_CUDA(cudaGetLastError());
     uint32_t total_pairs = 0;
-    LG_CUDA(cudaMemcpyAsync(&total_pairs, s->row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaMemcpyAsync(&total_pairs, row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     LG_CUDA(cudaStreamSynchronize(st));
-    s->n_pairs = (int64_t)total_pairs;
-    LG_TRY(ensure_pair_capacity(s, s->n_pairs));
-    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, s->row_ptr.p, s->cols.p, owned, st);
+    if ((size_t)total_pairs > cols.cap) {
+        LG_CUDA(cols.reserve((size_t)total_pairs, 1.25));
+        LG_CUDA(tag.reserve(cols.cap));
+    }
+    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, cols.p, owned, st);
     LG_CUDA(cudaGetLastError());
     s->rebuilds++;
+    if (defer) {
+        s->n_pairs_new = (int64_t)total_pairs;
+        s->rows_staged = true;
+        return LG_OK;
+    }
+    s->n_pairs = (int64_t)total_pairs;
     return retag(s);
 }
 
@@ -477,6 +524,7 @@ int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
     s->h_bptr = std::move(bptr);
     s->h_bj = std::move(bj);
     // existing rows (if any) need their tags refreshed
+    LG_TRY(flush(s));  // installs rows that were rebuilt behind a pending evaluation
     if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
     return LG_OK;
 }
@@ -713,6 +761,7 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     s->state_set = true;
     s->kicked = false;
     s->half_kicked = false;
+    if (s->rows_staged) LG_TRY(install_staged_rows(s));  // the discarded evaluation would have installed them
     s->pending = false;
     return LG_OK;
 }
@@ -916,6 +965,7 @@ int lg_enable_neighbor_list(lg_system* s, double r_verlet) {
     s->r_verlet = r_verlet;
     s->allpairs_built = false;
     s->n_pairs = 0;
+    s->rows_staged = false;
     LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, ((size_t)s->n + 1) * sizeof(uint32_t), s->stream));
     return LG_OK;
 }
@@ -965,6 +1015,7 @@ int lg_get_neighbor_count(lg_system* s, int64_t* n_pairs) {
         *n_pairs = s->n * (s->n - 1);
         return LG_OK;
     }
+    LG_TRY(flush(s));  // rows rebuilt behind a pending evaluation are installed by it
     *n_pairs = s->n_pairs;
     return LG_OK;
 }
@@ -976,6 +1027,7 @@ int lg_get_neighbor_rows(lg_system* s, int64_t* row_ptr, int64_t* cols) {
         LG_TRY(ensure_slots(s));
         LG_TRY(build_allpairs(s));
     }
+    LG_TRY(flush(s));  // rows rebuilt behind a pending evaluation are installed by it
     const size_t n = (size_t)s->n, p = (size_t)s->n_pairs;
     std::vector<uint32_t> hp(n + 1);
     std::vector<int32_t> hc(p);
@@ -1110,6 +1162,7 @@ int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, c
     s->state_set = true;
     s->kicked = kicked != 0;
     s->half_kicked = false;
+    if (s->rows_staged) LG_TRY(install_staged_rows(s));  // the discarded evaluation would have installed them
     s->pending = false;
     return LG_OK;
 }
@@ -1147,6 +1200,7 @@ int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_
     LG_CUDA(cudaMemcpyAsync(s->sgid.p, d_sgid, cells * sizeof(int32_t), cudaMemcpyDeviceToDevice, s->stream));
     LG_CUDA(cudaMemcpyAsync(s->spr.p, d_spr, cells * 9 * sizeof(double), cudaMemcpyDeviceToDevice, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
+    LG_TRY(flush(s));  // installs rows that were rebuilt behind a pending evaluation
     if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
     return LG_OK;
 }
@@ -1199,6 +1253,7 @@ int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, doubl
     s->n_bonds = nb;
     s->h_bptr = std::move(bptr);
     s->h_bj = std::move(bj);
+    LG_TRY(flush(s));  // installs rows that were rebuilt behind a pending evaluation
     if (s->n_pairs > 0 || s->allpairs_built) LG_TRY(retag(s));
     return LG_OK;
 }
@@ -1216,6 +1271,168 @@ int lg_halo_unpack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, co
     if (n_part < 0 || n_rec < 0 || (n_part > 0 && !d_idx) || (n_rec > 0 && !d_rec) || !d_in) return fail(LG_EINVAL, "bad halo arguments");
     launch_halo_unpack(n_part, d_idx, n_rec, d_rec, s->x.p, s->v.p, s->w.p, s->bconn.p, d_in, s->stream);
     LG_CUDA(cudaGetLastError());
+    return LG_OK;
+}
+
+// ---- peer-to-peer halo exchange (cudaIpc mappings of the neighbours' receive buffers) -------------------------
+struct lg_halo {
+    int device = 0;
+    int n_peers = 0;
+    int64_t recv_doubles[kMaxHaloPeers] = {};
+    int64_t recv_off[kMaxHaloPeers] = {};   // doubles, inside one parity half
+    int64_t half_doubles = 0;               // doubles per parity half
+    unsigned char* base = nullptr;          // [2 halves of recv data][flags: 2 x kMaxHaloPeers u64][counters: kMaxHaloPeers u32]
+    size_t flag_off = 0, counter_off = 0, bytes = 0;
+    HaloSendPeer send[kMaxHaloPeers] = {};
+    HaloRecvPeer recv[kMaxHaloPeers] = {};
+    void* peer_base[kMaxHaloPeers] = {};
+    double* remote_data[kMaxHaloPeers][2] = {};
+    unsigned long long* remote_flag[kMaxHaloPeers][2] = {};
+    unsigned long long seq = 0;
+};
+
+namespace {
+int halo_exchange(lg_system* s, lg_halo* hl) {
+    if (hl->n_peers == 0) return LG_OK;
+    hl->seq++;
+    const int par = (int)(hl->seq & 1ull);
+    HaloPushArgs P{};
+    HaloPullArgs Q{};
+    P.n_peers = Q.n_peers = hl->n_peers;
+    int pb = 0, qb = 0;
+    for (int k = 0; k < hl->n_peers; k++) {
+        P.block_begin[k] = pb;
+        Q.block_begin[k] = qb;
+        P.peer[k] = hl->send[k];
+        const long ts = 9L * hl->send[k].n_part + 15L * hl->send[k].n_rec;
+        if (ts > 0 && hl->remote_data[k][par] == nullptr) return fail(LG_EINVAL, "halo peer not connected");
+        P.peer[k].remote = hl->remote_data[k][par];
+        P.peer[k].remote_flag = hl->remote_flag[k][par];
+        P.peer[k].counter = (unsigned int*)(hl->base + hl->counter_off) + k;
+        pb += (int)((ts + 255) / 256);
+        Q.peer[k] = hl->recv[k];
+        const long tr = 9L * hl->recv[k].n_part + 15L * hl->recv[k].n_rec;
+        Q.peer[k].local = (const double*)hl->base + (size_t)par * hl->half_doubles + hl->recv_off[k];
+        Q.peer[k].flag = (const unsigned long long*)(hl->base + hl->flag_off) + (size_t)par * kMaxHaloPeers + k;
+        qb += (int)((tr + 255) / 256);
+    }
+    P.block_begin[hl->n_peers] = pb;
+    Q.block_begin[hl->n_peers] = qb;
+    P.x = s->x.p; P.v = s->v.p; P.w = s->w.p; P.bconn = s->bconn.p;
+    Q.x = s->x.p; Q.v = s->v.p; Q.w = s->w.p; Q.bconn = s->bconn.p;
+    P.seq = Q.seq = hl->seq;
+    Q.timeout_ns = 20ull * 1000000000ull;
+    Q.err = s->err.p;
+    launch_halo_push(P, s->stream);
+    launch_halo_pull(Q, s->stream);
+    LG_CUDA(cudaGetLastError());
+    return LG_OK;
+}
+}  // namespace
+
+int lg_halo_create(lg_system* s, int n_peers, const int64_t* recv_doubles, lg_halo** out) {
+    LG_ENTER(s);
+    if (!out || n_peers < 0 || n_peers > kMaxHaloPeers || (n_peers > 0 && !recv_doubles)) return fail(LG_EINVAL, "bad halo arguments");
+    std::unique_ptr<lg_halo> hl(new (std::nothrow) lg_halo());
+    if (!hl) return fail(LG_ENOMEM, "host allocation failed");
+    hl->device = s->device;
+    hl->n_peers = n_peers;
+    int64_t off = 0;
+    for (int k = 0; k < n_peers; k++) {
+        if (recv_doubles[k] < 0) return fail(LG_EINVAL, "negative halo size");
+        hl->recv_doubles[k] = recv_doubles[k];
+        hl->recv_off[k] = off;
+        off += (recv_doubles[k] + 1) & ~(int64_t)1;  // 16-byte granules
+    }
+    hl->half_doubles = off;
+    hl->flag_off = (size_t)(2 * off) * sizeof(double);
+    hl->counter_off = hl->flag_off + 2 * kMaxHaloPeers * sizeof(unsigned long long);
+    hl->bytes = hl->counter_off + kMaxHaloPeers * sizeof(unsigned int);
+    LG_CUDA(cudaMalloc(&hl->base, hl->bytes));   // cudaMalloc (not a pool): the allocation is exported with cudaIpc
+    LG_CUDA(cudaMemset(hl->base, 0, hl->bytes));
+    LG_CUDA(cudaDeviceSynchronize());
+    *out = hl.release();
+    return LG_OK;
+}
+
+int lg_halo_set_lists(lg_halo* hl, int k, int n_send_part, const int32_t* d_send_idx, int n_send_rec, const int32_t* d_send_rec,
+                      int n_recv_part, const int32_t* d_recv_idx, int n_recv_rec, const int32_t* d_recv_rec) {
+    if (!hl || k < 0 || k >= hl->n_peers) return fail(LG_EINVAL, "bad halo peer");
+    if (n_send_part < 0 || n_send_rec < 0 || n_recv_part < 0 || n_recv_rec < 0) return fail(LG_EINVAL, "negative halo list size");
+    if (9LL * n_recv_part + 15LL * n_recv_rec > hl->recv_doubles[k]) return fail(LG_ESIZE, "halo receive list exceeds the buffer");
+    hl->send[k].n_part = n_send_part; hl->send[k].idx = d_send_idx;
+    hl->send[k].n_rec = n_send_rec;   hl->send[k].rec = d_send_rec;
+    hl->recv[k].n_part = n_recv_part; hl->recv[k].idx = d_recv_idx;
+    hl->recv[k].n_rec = n_recv_rec;   hl->recv[k].rec = d_recv_rec;
+    return LG_OK;
+}
+
+int lg_halo_export(lg_halo* hl, int k, unsigned char handle[64], int64_t offs[4]) {
+    if (!hl || k < 0 || k >= hl->n_peers || !handle || !offs) return fail(LG_EINVAL, "bad halo peer");
+    DeviceGuard guard_(hl->device);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    cudaIpcMemHandle_t h;
+    LG_CUDA(cudaIpcGetMemHandle(&h, hl->base));
+    std::memcpy(handle, &h, 64);
+    for (int par = 0; par < 2; par++) {
+        offs[par] = (int64_t)(((size_t)par * hl->half_doubles + hl->recv_off[k]) * sizeof(double));
+        offs[2 + par] = (int64_t)(hl->flag_off + ((size_t)par * kMaxHaloPeers + k) * sizeof(unsigned long long));
+    }
+    return LG_OK;
+}
+
+int lg_halo_connect(lg_halo* hl, int k, const unsigned char handle[64], const int64_t offs[4]) {
+    if (!hl || k < 0 || k >= hl->n_peers || !handle || !offs) return fail(LG_EINVAL, "bad halo peer");
+    DeviceGuard guard_(hl->device);
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, 64);
+    void* p = nullptr;
+    LG_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    hl->peer_base[k] = p;
+    for (int par = 0; par < 2; par++) {
+        hl->remote_data[k][par] = (double*)((unsigned char*)p + offs[par]);
+        hl->remote_flag[k][par] = (unsigned long long*)((unsigned char*)p + offs[2 + par]);
+    }
+    return LG_OK;
+}
+
+int lg_halo_disconnect(lg_halo* hl) {
+    if (!hl) return LG_OK;
+    DeviceGuard guard_(hl->device);
+    for (int k = 0; k < hl->n_peers; k++)
+        if (hl->peer_base[k]) {
+            cudaIpcCloseMemHandle(hl->peer_base[k]);
+            hl->peer_base[k] = nullptr;
+            hl->remote_data[k][0] = hl->remote_data[k][1] = nullptr;
+        }
+    return LG_OK;
+}
+
+int lg_halo_destroy(lg_halo* hl) {
+    if (!hl) return LG_OK;
+    lg_halo_disconnect(hl);
+    {
+        DeviceGuard guard_(hl->device);
+        if (hl->base) cudaFree(hl->base);
+    }
+    delete hl;
+    return LG_OK;
+}
+
+int lg_halo_exchange(lg_system* s, lg_halo* hl) {
+    LG_ENTER(s);
+    if (!hl) return fail(LG_EINVAL, "null halo");
+    return halo_exchange(s, hl);
+}
+
+int lg_run_slab(lg_system* s, lg_halo* hl, double dt, int64_t n_steps) {
+    LG_ENTER(s);
+    if (!hl) return fail(LG_EINVAL, "null halo");
+    LG_TRY(prepare(s));
+    for (int64_t k = 0; k < n_steps; k++) {
+        LG_TRY(step(s, dt));
+        LG_TRY(halo_exchange(s, hl));
+    }
     return LG_OK;
 }
 

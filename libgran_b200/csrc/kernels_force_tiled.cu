@@ -9,15 +9,21 @@
 //   LT/rotational_integrator/rotational_velocity_verlet_half.h:63-73      (integrate, MODE_FUSED)
 //   LG/sinter_bridge/sinter_bridge.h:24-42,55-75                          (connector update, MODE_FUSED)
 //
-// Organisation (one CTA of 256 threads owns `rows_per_block` consecutive particles):
-//   stage   x, v, omega of the CTA's particles and its slice of the row / bond pointers -> shared memory
-//   per tile of up to 1024 consecutive neighbor pairs of those rows:
+// Organisation (one CTA of LG_TB threads owns `rows_per_block` consecutive particles):
+//   stage   Everything the CTA reads that is CONTIGUOUS in HBM -- x, v, omega, theta of its particles, its slice of
+//           the row / bond pointers, the columns and tags of its first tile of pairs, the connectors, rest lengths
+//           and mirror indices of its particles' bond records -- is brought into shared memory by bulk asynchronous
+//           copies (cp.async.bulk, the TMA engine) that ONE thread issues at kernel entry against two mbarriers.
+//           The dependent chain row pointer -> column -> tag -> mirror index -> partner connector, which used to be
+//           five serialized global round trips per CTA (profiles/README.md r01d), becomes two: the bulk stage and
+//           the gathers of x_j (and of the few partner connectors owned by another CTA).
+//   per tile of up to LG_TILE consecutive neighbor pairs of those rows:
 //     phase A  one thread per PAIR: geometry, Hamaker, contact test (the cheap, uniform work);
 //              pairs that need the expensive laws (bonded, overlapping) are compacted into a list with
 //              warp ballots so that phase B runs with full lanes instead of diverging inside phase A
 //     phase B  one thread per HEAVY pair: sinter-bridge springs or Luding contact with its history springs
-//     phase C  one thread per PARTICLE: adds its pairs' contributions from shared memory in ascending-j
-//              order -- the reference's accumulation order, so a / alpha are bit-identical to it; no
+//     phase C  one thread per (PARTICLE, component): adds its pairs' contributions from shared memory in
+//              ascending-j order -- the reference's accumulation order, so a / alpha are bit-identical to it; no
 //              atomics, deterministic
 //   finalize unary (facet) forces, then either write a, alpha (MODE_FORCE) or integrate v, x, omega, theta
 //            into the next-step buffers and move the particle's bridge connectors (MODE_FUSED), with
@@ -35,38 +41,92 @@ namespace {
 #define LG_TB 256
 #endif
 #ifndef LG_TILE
-#define LG_TILE 1024
+#define LG_TILE 512
 #endif
 #ifndef LG_RMAX
-#define LG_RMAX 128
+#define LG_RMAX 64
+#endif
+#ifndef LG_CCAP
+#define LG_CCAP 128
 #endif
 #ifndef LG_MINB
-#define LG_MINB 2
+#define LG_MINB 3
+#endif
+#ifndef LG_BU
+#define LG_BU 5  // unroll factor of the five bridge springs in the relaxed-arithmetic path
 #endif
 constexpr int TB = LG_TB;      // threads per CTA
 constexpr int TILE = LG_TILE;  // pairs per tile
 constexpr int RMAX = LG_RMAX;  // max particles per CTA (<= TB)
-constexpr int BCAP = 4 * RMAX; // bond records per CTA with a precomputed owner row (beyond: binary search)
+constexpr int CCAP = LG_CCAP;  // bond records per CTA staged in shared memory (more: the CTA reads them from global)
 constexpr int TS = TILE + 1;   // padded component stride of the tile (bank spread for phase C)
+constexpr int BU = LG_BU;     // unroll factor of the five bridge springs (relaxed-arithmetic path)
 static_assert(RMAX <= TB && RMAX <= 256, "one staging pass per CTA; local rows are stored in a byte");
 static_assert(TILE % TB == 0, "phase A handles TILE / TB pairs per thread");
 static_assert(15 * RMAX <= 6 * TS, "the output staging area reuses the tile");
+static_assert(RMAX % 4 == 0 && TILE % 16 == 0 && CCAP % 16 == 0, "staged windows are multiples of 16 bytes");
 
 enum : int { MODE_FORCE = 0, MODE_FUSED = 1 };
 enum : int { KIND_LIGHT = 0, KIND_BOND = 1, KIND_CONTACT = 2 };
 
-struct Smem {
-    double tile[6 * TS];    // a.x a.y a.z alpha.x alpha.y alpha.z, structure-of-arrays over the tile
-    double st[RMAX * 9];    // x, v, omega of the CTA's particles
-    double acc[RMAX * 6];   // running a, alpha of the CTA's particles ([row][component])
-    double sth[RMAX * 3];   // theta of the CTA's particles (MODE_FUSED)
-    uint32_t sptr[RMAX + 1];
-    uint32_t sbptr[RMAX + 1];
+// A staged array is a 16-byte aligned WINDOW around the bytes the CTA needs (cp.async.bulk wants 16-byte aligned
+// addresses and sizes): up to 15 bytes before and after are copied along; `lead` says where the payload starts.
+// Every device buffer ends with >= 16 bytes of slack (api.cu: DevBuf), so the window never leaves the allocation.
+struct alignas(16) Smem {
+    double tile[6 * TS];             // a.x a.y a.z alpha.x alpha.y alpha.z, structure-of-arrays over the tile
+    double wx[3 * RMAX + 4];         // windows: x, v, omega, theta of the CTA's particles
+    double wv[3 * RMAX + 4];
+    double ww[3 * RMAX + 4];
+    double wth[3 * RMAX + 4];
+    double wconn[15 * CCAP + 4];     // window: connectors of the CTA's bond records
+    double wlen[5 * CCAP + 4];       // window: their rest lengths
+    double acc[RMAX * 6];            // running a, alpha of the CTA's particles ([row][component])
+    uint32_t wrow[RMAX + 12];        // window: row_ptr[i0 .. i0 + nrows]
+    uint32_t wbond[RMAX + 12];       // window: bptr[i0 .. i0 + nrows]
+    int32_t wcols[TILE + 8];         // window: columns of the first tile
+    int32_t wrev[CCAP + 8];          // window: mirror record of every staged bond
     uint16_t heavy[TILE];
-    uint8_t srow[TILE];     // local row of every pair of the tile (written by the row owners, replaces a search)
-    uint8_t brow[BCAP];     // local row of the CTA's first BCAP bond records (connector stage)
+    uint8_t wtag[TILE + 32];         // window: tags of the first tile (snapshot at kernel entry)
+    uint8_t srow[TILE];              // local row of every pair of the tile (written by the row owners)
+    uint8_t brow[CCAP];              // local row of the CTA's staged bond records (connector stage)
+    unsigned long long bar[2];       // mbarriers: [0] state + pointers, [1] pair / bond data
     int cnt[2];
 };
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+            : "=r"(done)
+            : "r"(a), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+// 16-byte aligned window around [begin, begin + nbytes): returns the bytes to copy (0 for an empty range)
+__device__ __forceinline__ uint32_t window_bytes(const void* begin, uint32_t nbytes) {
+    if (nbytes == 0) return 0u;
+    const uint32_t lead = (uint32_t)((uintptr_t)begin & 15u);
+    return (lead + nbytes + 15u) & ~15u;
+}
+__device__ __forceinline__ uint32_t window_lead(const void* begin) { return (uint32_t)((uintptr_t)begin & 15u); }
+// one bulk copy global -> shared of the window around [begin, begin + nbytes), completion counted on `bar`
+__device__ __forceinline__ void bulk_load(void* dst, const void* begin, uint32_t nbytes, unsigned long long* bar) {
+    const uint32_t bytes = window_bytes(begin, nbytes);
+    if (bytes == 0) return;
+    const void* src = (const void*)((uintptr_t)begin & ~(uintptr_t)15u);
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 
 __device__ __forceinline__ Springs ld_springs(const double* p) {
     Springs s;
@@ -173,45 +233,92 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
     const int nrows = min(R, A.n - i0);
     const bool have_bonds = kSinter && A.bptr != nullptr;
 
-    // ---- stage the CTA's particles (coalesced: 3 * nrows consecutive doubles per field) ----------------
-    for (int idx = tid; idx < 3 * nrows; idx += TB) {
-        const int r = idx / 3, c = idx - 3 * r;
-        const size_t gidx = 3 * (size_t)i0 + idx;
-        sm.st[r * 9 + c] = A.x[gidx];
-        sm.st[r * 9 + 3 + c] = A.v[gidx];
-        sm.st[r * 9 + 6 + c] = A.w[gidx];
-        if constexpr (MODE == MODE_FUSED) sm.sth[idx] = A.th[gidx];
+    // ---- stage: bulk asynchronous copies of every contiguous range the CTA reads ---------------------------
+    const double* gx = A.x + 3 * (size_t)i0;
+    const double* gv = A.v + 3 * (size_t)i0;
+    const double* gw = A.w + 3 * (size_t)i0;
+    const double* gth = A.th + 3 * (size_t)i0;
+    const uint32_t* grow = A.row_ptr + i0;
+    const uint32_t* gbond = have_bonds ? A.bptr + i0 : nullptr;
+    if (tid == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint32_t nb3 = 24u * (uint32_t)nrows, nbp = 4u * (uint32_t)(nrows + 1);
+        uint32_t total = window_bytes(gx, nb3) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(grow, nbp);
+        if constexpr (MODE == MODE_FUSED) total += window_bytes(gth, nb3);
+        if (have_bonds) total += window_bytes(gbond, nbp);
+        mbar_expect_tx(&sm.bar[0], total);
+        bulk_load(sm.wx, gx, nb3, &sm.bar[0]);
+        bulk_load(sm.wv, gv, nb3, &sm.bar[0]);
+        bulk_load(sm.ww, gw, nb3, &sm.bar[0]);
+        if constexpr (MODE == MODE_FUSED) bulk_load(sm.wth, gth, nb3, &sm.bar[0]);
+        bulk_load(sm.wrow, grow, nbp, &sm.bar[0]);
+        if (have_bonds) bulk_load(sm.wbond, gbond, nbp, &sm.bar[0]);
+        // the ranges of pairs and bond records: four independent loads, one round trip, overlapped with the copies above
+        const uint32_t rp0 = grow[0], rp1 = grow[nrows];
+        const uint32_t bp0 = have_bonds ? gbond[0] : 0u, bp1 = have_bonds ? gbond[nrows] : 0u;
+        const uint32_t np0 = min(rp1 - rp0, (uint32_t)TILE);           // pairs of the first tile
+        const uint32_t nbr = (bp1 - bp0 <= (uint32_t)CCAP) ? bp1 - bp0 : 0u;  // staged bond records
+        const int32_t* gcols = A.cols + rp0;
+        const uint8_t* gtag = A.tag + rp0;
+        const double* gconn = A.bconn + 15 * (size_t)bp0;
+        const double* glen = A.blen + 5 * (size_t)bp0;
+        const int32_t* grev = A.brev + bp0;
+        uint32_t total1 = window_bytes(gcols, 4u * np0);
+        if constexpr (kContact) total1 += window_bytes(gtag, np0);
+        if (nbr) total1 += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(grev, 4u * nbr);
+        mbar_expect_tx(&sm.bar[1], total1);
+        bulk_load(sm.wcols, gcols, 4u * np0, &sm.bar[1]);
+        if constexpr (kContact) bulk_load(sm.wtag, gtag, np0, &sm.bar[1]);
+        if (nbr) {
+            bulk_load(sm.wconn, gconn, 120u * nbr, &sm.bar[1]);
+            bulk_load(sm.wlen, glen, 40u * nbr, &sm.bar[1]);
+            bulk_load(sm.wrev, grev, 4u * nbr, &sm.bar[1]);
+        }
+        sm.cnt[0] = sm.cnt[1] = 0;
     }
     for (int idx = tid; idx < 6 * nrows; idx += TB) sm.acc[idx] = 0.0;
-    const uint32_t p_begin = A.row_ptr[i0];
-    if (tid <= nrows) {
-        const uint32_t rp = A.row_ptr[i0 + tid];
-        sm.sptr[tid] = rp;
-        const uint32_t bp = have_bonds ? A.bptr[i0 + tid] : 0u;
-        sm.sbptr[tid] = bp;
-        if (tid < nrows) {
-            // local-row map of the first tile, and of this particle's bond records (connector stage)
-            const uint32_t lo = rp - p_begin, hi = min(A.row_ptr[i0 + tid + 1] - p_begin, (uint32_t)TILE);
-            for (uint32_t q = lo; q < hi; q++) sm.srow[q] = (uint8_t)tid;
-            if (MODE == MODE_FUSED && have_bonds) {
-                const uint32_t b0 = A.bptr[i0], b1 = A.bptr[i0 + tid + 1];
-                for (uint32_t b = bp; b < b1 && b - b0 < (uint32_t)BCAP; b++) sm.brow[b - b0] = (uint8_t)tid;
-            }
-        }
+    __syncthreads();  // the mbarriers are initialised
+    mbar_wait(&sm.bar[0], 0);
+
+    // payloads inside the windows
+    const double* sx = sm.wx + (window_lead(gx) >> 3);
+    const double* sv = sm.wv + (window_lead(gv) >> 3);
+    const double* sw = sm.ww + (window_lead(gw) >> 3);
+    const double* sth = sm.wth + (window_lead(gth) >> 3);
+    const uint32_t* sptr = sm.wrow + (window_lead(grow) >> 2);
+    const uint32_t* sbptr = sm.wbond + (window_lead(gbond) >> 2);  // valid only when have_bonds
+    const uint32_t p_begin = sptr[0], p_end = sptr[nrows];
+    const uint32_t b0 = have_bonds ? sbptr[0] : 0u;
+    const uint32_t nbond = have_bonds ? sbptr[nrows] - b0 : 0u;
+    const bool conn_staged = nbond > 0 && nbond <= (uint32_t)CCAP;
+    const int32_t* scols = sm.wcols + (window_lead(A.cols + p_begin) >> 2);
+    const uint8_t* stag = sm.wtag + window_lead(A.tag + p_begin);
+    const double* sconn = sm.wconn + (window_lead(A.bconn + 15 * (size_t)b0) >> 3);
+    const double* slen = sm.wlen + (window_lead(A.blen + 5 * (size_t)b0) >> 3);
+    const int32_t* srev = sm.wrev + (window_lead(A.brev + b0) >> 2);
+
+    if (tid < nrows) {
+        // local-row map of the first tile, and of this particle's staged bond records (connector stage)
+        const uint32_t lo = sptr[tid] - p_begin, hi = min(sptr[tid + 1] - p_begin, (uint32_t)TILE);
+        for (uint32_t q = lo; q < hi; q++) sm.srow[q] = (uint8_t)tid;
+        if (MODE == MODE_FUSED && conn_staged)
+            for (uint32_t b = sbptr[tid]; b < sbptr[tid + 1]; b++) sm.brow[b - b0] = (uint8_t)tid;
     }
-    if (tid == 0) sm.cnt[0] = sm.cnt[1] = 0;
-    __syncthreads();
+    mbar_wait(&sm.bar[1], 0);
+    __syncthreads();  // srow / brow
 
-    const uint32_t p_end = sm.sptr[nrows];
-
-    auto particle = [&](int r, int which) -> d3 { return load3(sm.st + r * 9 + 3 * which); };
+    auto particle = [&](int r, int which) -> d3 { return load3((which == 0 ? sx : which == 1 ? sv : sw) + 3 * r); };
     auto neighbour = [&](int j, int which, const double* gsrc) -> d3 {
         const unsigned rj = (unsigned)(j - i0);
-        return rj < (unsigned)nrows ? load3(sm.st + rj * 9 + 3 * which) : load3(gsrc + 3 * (size_t)j);
+        return rj < (unsigned)nrows ? load3((which == 0 ? sx : which == 1 ? sv : sw) + 3 * rj) : load3(gsrc + 3 * (size_t)j);
     };
 
     for (uint32_t tile_start = p_begin; tile_start < p_end; tile_start += TILE) {
         const int cntp = (int)min((uint32_t)TILE, p_end - tile_start);
+        const bool first = tile_start == p_begin;  // columns and tags of the first tile are staged
 
         // ---- phase A: light work for every pair, classify ------------------------------------------------
         // All of a thread's PPT pairs are loaded before any is computed (PPT gathers in flight per thread), and
@@ -224,8 +331,8 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
             jv[k] = -1;
             tv[k] = kTagNone;
             if (q < cntp) {
-                jv[k] = A.cols[tile_start + q];
-                if constexpr (kContact) tv[k] = A.tag[tile_start + q];
+                jv[k] = first ? scols[q] : A.cols[tile_start + q];
+                if constexpr (kContact) tv[k] = first ? stag[q] : A.tag[tile_start + q];
             }
         }
         d3 xjv[PPT];
@@ -308,26 +415,34 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
                 const int q = is_bond ? sm.heavy[e] : sm.heavy[TILE - 1 - (e - nB)];
                 const uint32_t p = tile_start + q;
                 const int r = sm.srow[q];
-                const int j = A.cols[p];
+                const int j = first ? scols[q] : A.cols[p];
                 Accel c;
                 if (kSinter && is_bond) {
-                    const int t = A.tag[p];
-                    const uint32_t b = sm.sbptr[r] + (uint32_t)(t - kTagBond);
-                    const double* ci = A.bconn + (size_t)b * 15;
-                    const double* cj = A.bconn + (size_t)A.brev[b] * 15;
-                    const double* len = A.blen + (size_t)b * 5;
+                    const int t = first ? stag[q] : A.tag[p];
+                    const uint32_t b = sbptr[r] + (uint32_t)(t - kTagBond);
+                    const double *ci, *cj, *len;
+                    if (conn_staged) {  // own record from shared memory; the mirror too when this CTA owns the partner
+                        const uint32_t bl = b - b0, ml = (uint32_t)srev[bl] - b0;
+                        ci = sconn + 15 * bl;
+                        len = slen + 5 * bl;
+                        cj = ml < nbond ? sconn + 15 * ml : A.bconn + (size_t)srev[bl] * 15;
+                    } else {
+                        ci = A.bconn + (size_t)b * 15;
+                        cj = A.bconn + (size_t)A.brev[b] * 15;
+                        len = A.blen + (size_t)b * 5;
+                    }
                     const d3 xi = particle(r, 0), xj = neighbour(j, 0, A.x);
                     d3 force = zero3(), torque = zero3();
                     if constexpr (FAST) {
                         if (A.mp.gamma_d != 0.0) {
                             const d3 vi = particle(r, 1), wi = particle(r, 2);
                             const d3 vj = neighbour(j, 1, A.v), wj = neighbour(j, 2, A.w);
-#pragma unroll
+#pragma unroll BU
                             for (int k = 0; k < 5; k++)
                                 bonded_spring_fast<true>(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi,
                                                          xj, vi, vj, wi, wj, force, torque);
                         } else {  // undamped bridges (the reference's tests): velocities are not needed at all
-#pragma unroll
+#pragma unroll BU
                             for (int k = 0; k < 5; k++)
                                 bonded_spring_fast<false>(A.mp.k_d, 0.0, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj,
                                                           zero3(), zero3(), zero3(), zero3(), force, torque);
@@ -366,9 +481,9 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
         // ---- phase C: ordered accumulation (ascending j), one thread per (particle, component) ----------------
         for (int wk = tid; wk < 6 * nrows; wk += TB) {
             const int r = wk / 6, c = wk - 6 * r;
-            const uint32_t lo = max(sm.sptr[r], tile_start) - tile_start;
-            const uint32_t hi = min(sm.sptr[r + 1], tile_start + (uint32_t)cntp) - tile_start;
-            if (lo < hi && sm.sptr[r + 1] > tile_start) {
+            const uint32_t lo = max(sptr[r], tile_start) - tile_start;
+            const uint32_t hi = min(sptr[r + 1], tile_start + (uint32_t)cntp) - tile_start;
+            if (lo < hi && sptr[r + 1] > tile_start) {
                 const double* t = sm.tile + c * TS;
                 double a = sm.acc[wk];
                 for (uint32_t q = lo; q < hi; q++) a += t[q];
@@ -378,7 +493,7 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
         if (tile_start + TILE < p_end) {  // local-row map of the next tile (srow is not read in phase C)
             const uint32_t nxt = tile_start + TILE;
             if (tid < nrows) {
-                const uint32_t r0 = sm.sptr[tid], r1 = sm.sptr[tid + 1];
+                const uint32_t r0 = sptr[tid], r1 = sptr[tid + 1];
                 if (r1 > nxt && r0 < nxt + TILE) {
                     const uint32_t lo = max(r0, nxt) - nxt, hi = min(r1 - nxt, (uint32_t)TILE);
                     for (uint32_t q = lo; q < hi; q++) sm.srow[q] = (uint8_t)tid;
@@ -427,21 +542,20 @@ __global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_co
             A.x_next[gidx] = out[0 * OB + idx];
             A.v_next[gidx] = out[1 * OB + idx];
             A.w_next[gidx] = out[2 * OB + idx];
-            A.th[gidx] = sm.sth[idx] + out[3 * OB + idx];
+            A.th[gidx] = sth[idx] + out[3 * OB + idx];
         }
     }
     if constexpr (MODE == MODE_FUSED && kSinter) {
         if (have_bonds) {
             // connectors of the CTA's particles: c += dx ; c += dtheta x (c - x_new)   (sinter_bridge.h:36-41,67-74)
-            const uint32_t b0 = sm.sbptr[0];
-            const int ncon = (int)(sm.sbptr[nrows] - b0) * 5;
+            const int ncon = (int)nbond * 5;
             for (int cq = tid; cq < ncon; cq += TB) {
                 const int bl = cq / 5;
-                const int r = bl < BCAP ? (int)sm.brow[bl] : find_row(sm.sbptr, nrows, b0 + (uint32_t)bl);
+                const int r = conn_staged ? (int)sm.brow[bl] : find_row(sbptr, nrows, b0 + (uint32_t)bl);
                 const size_t off = (size_t)b0 * 15 + 3 * (size_t)cq;
-                d3 ck = load3(A.bconn + off) + load3(out + 4 * OB + 3 * r);
-                const d3 sv = ck - load3(out + 0 * OB + 3 * r);
-                ck = ck + cross(load3(out + 3 * OB + 3 * r), sv);
+                d3 ck = (conn_staged ? load3(sconn + 3 * cq) : load3(A.bconn + off)) + load3(out + 4 * OB + 3 * r);
+                const d3 arm = ck - load3(out + 0 * OB + 3 * r);
+                ck = ck + cross(load3(out + 3 * OB + 3 * r), arm);
                 store3(A.bconn_next + off, ck);
             }
         }

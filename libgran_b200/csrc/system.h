@@ -37,7 +37,7 @@ constexpr int kMaxBondsPerParticle = 120;
 constexpr int kMaxSlots = 120;
 
 // asynchronous error flags raised by kernels (checked at synchronisation points)
-enum : int { ERR_SLOT_OVERFLOW = 1, ERR_BOND_LOOKUP = 2 };
+enum : int { ERR_SLOT_OVERFLOW = 1, ERR_BOND_LOOKUP = 2, ERR_HALO_TIMEOUT = 4 };
 
 struct ModelParams {
     double r, mass, inertia;
@@ -143,5 +143,45 @@ void launch_halo_pack(int n_part, const int32_t* idx, int n_rec, const int32_t* 
                       const double* w, const double* bconn, double* out, cudaStream_t st);
 void launch_halo_unpack(int n_part, const int32_t* idx, int n_rec, const int32_t* rec, double* x, double* v, double* w,
                         double* bconn, const double* in, cudaStream_t st);
+
+// ---- peer-to-peer halo exchange over NVLink (kernels_halo.cu) ------------------------------------------------
+// One rank's view of the exchange with up to kMaxHaloPeers neighbouring ranks.  The SEND side gathers the owners'
+// x, v, omega (9 doubles per particle) and the connector blocks of cross-slab bond records (15 doubles each) and
+// stores them straight into the receiving rank's buffer (a cudaIpc mapping of peer memory), then publishes a
+// sequence number there; the RECEIVE side polls its own flag and scatters the buffer into the ghost slots.
+constexpr int kMaxHaloPeers = 8;
+struct HaloSendPeer {
+    int n_part, n_rec;
+    const int32_t* idx;
+    const int32_t* rec;
+    double* remote;                    // peer memory (this step's parity)
+    unsigned long long* remote_flag;   // peer memory
+    unsigned int* counter;             // local: blocks of this peer that have finished storing
+};
+struct HaloRecvPeer {
+    int n_part, n_rec;
+    const int32_t* idx;
+    const int32_t* rec;
+    const double* local;               // this step's parity
+    const unsigned long long* flag;
+};
+struct HaloPushArgs {
+    int n_peers;
+    int block_begin[kMaxHaloPeers + 1];
+    HaloSendPeer peer[kMaxHaloPeers];
+    const double *x, *v, *w, *bconn;
+    unsigned long long seq;
+};
+struct HaloPullArgs {
+    int n_peers;
+    int block_begin[kMaxHaloPeers + 1];
+    HaloRecvPeer peer[kMaxHaloPeers];
+    double *x, *v, *w, *bconn;
+    unsigned long long seq;
+    unsigned long long timeout_ns;
+    int* err;
+};
+void launch_halo_push(const HaloPushArgs& args, cudaStream_t st);
+void launch_halo_pull(const HaloPullArgs& args, cudaStream_t st);
 
 }  // namespace lg

@@ -16,6 +16,7 @@ Layout of this module
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Dict, List, Optional, Tuple
 
@@ -427,6 +428,8 @@ class SlabSystem:
         self.math_mode = int(math_mode)
         self.n_global = len(x0)
         self.h = C.c_void_p()
+        self.halo = C.c_void_p()
+        self.transport = "none"
         self.steps = 0
         self.repartitions = 0
         self.kicked = False
@@ -445,14 +448,25 @@ class SlabSystem:
         if rc != 0:
             raise self._sys.LgError(rc, self.lib.lg_last_error().decode(errors="replace"))
 
-    def close(self):
+    def _release_halo(self, collective: bool):
+        """Teardown order across ranks: everyone unmaps its neighbours' buffers, barrier, then frees its own."""
+        if getattr(self, "halo", None) and self.halo.value:
+            self.lib.lg_synchronize(self.h)
+            self.lib.lg_halo_disconnect(self.halo)
+            if collective and self.world > 1 and dist.is_initialized():
+                dist.barrier(group=self.group)
+            self.lib.lg_halo_destroy(self.halo)
+            self.halo = C.c_void_p()
+
+    def close(self, collective: bool = True):
+        self._release_halo(collective)
         if getattr(self, "h", None) and self.h.value:
             self.lib.lg_destroy(self.h)
             self.h = C.c_void_p()
 
     def __del__(self):
         try:
-            self.close()
+            self.close(collective=False)
         except Exception:
             pass
 
@@ -499,6 +513,49 @@ class SlabSystem:
         self.recv_buf = {r: torch.empty(max(self.plan.recv_doubles(r), 1), dtype=torch.float64, device=self.device) for r in self.plan.peers}
         self.halo_bytes_per_step = 8 * sum(self.plan.send_doubles(r) for r in self.plan.peers)
         self.repartitions += 1
+        self.transport = "nccl" if self.world > 1 else "none"
+        if self.world > 1 and self.device.type == "cuda" and os.environ.get("LGB200_HALO", "p2p") == "p2p":
+            self._connect_p2p()
+
+    def _connect_p2p(self):
+        """Peer-to-peer transport (lgb200.h: lg_halo_*): every rank exports its receive buffer with cudaIpc, the
+        neighbours map it, and from then on the pack kernel stores over NVLink straight into the neighbour's memory.
+        Falls back to NCCL send/recv (on every rank together) when the mappings cannot be established."""
+        lib, plan, peers = self.lib, self.plan, self.plan.peers
+        halo = C.c_void_p()
+        exports = None
+        recv = (C.c_int64 * max(len(peers), 1))(*[plan.recv_doubles(r) for r in peers])
+        ok = len(peers) <= 8 and lib.lg_halo_create(self.h, len(peers), recv, C.byref(halo)) == 0
+        if ok:
+            exports = {}
+            for k, r in enumerate(peers):
+                ok = ok and lib.lg_halo_set_lists(halo, k, len(plan.send_idx[r]), plan.send_idx[r].data_ptr(), len(plan.send_rec[r]),
+                                                  plan.send_rec[r].data_ptr(), len(plan.recv_idx[r]), plan.recv_idx[r].data_ptr(),
+                                                  len(plan.recv_rec[r]), plan.recv_rec[r].data_ptr()) == 0
+                hb, offs = C.create_string_buffer(64), (C.c_int64 * 4)()
+                ok = ok and lib.lg_halo_export(halo, k, hb, offs) == 0
+                exports[r] = (hb.raw, list(offs))
+        gathered = [None] * self.world
+        dist.all_gather_object(gathered, exports if ok else None, group=self.group)
+        ok = ok and all(g is not None for g in gathered)
+        if ok:
+            for k, r in enumerate(peers):
+                handle, offs = gathered[r][self.rank]
+                ok = ok and lib.lg_halo_connect(halo, k, handle, (C.c_int64 * 4)(*offs)) == 0
+        agree = torch.tensor([int(ok)], dtype=torch.int32, device=self.device)
+        dist.all_reduce(agree, op=dist.ReduceOp.MIN, group=self.group)
+        self.halo = halo
+        if int(agree) == 1:
+            self.transport = "p2p"
+        else:
+            if self.rank == 0:
+                print("libgran_b200.slab: cudaIpc peer mappings unavailable (%s); halo exchange over NCCL send/recv"
+                      % self.lib.lg_last_error().decode(errors="replace"), flush=True)
+            if halo.value:
+                self._release_halo(collective=True)
+            else:
+                dist.barrier(group=self.group)
+            self.halo = C.c_void_p()
 
     def _field_view(self, name: str) -> torch.Tensor:
         p = C.c_void_p()
@@ -531,6 +588,9 @@ class SlabSystem:
         """Owners' x, v, omega and bond connectors -> the ghost copies on the neighbouring ranks."""
         plan, lib = self.plan, self.lib
         if not plan.peers:
+            return
+        if self.transport == "p2p":
+            self._check(lib.lg_halo_exchange(self.h, self.halo))
             return
         with torch.cuda.stream(self.stream):
             ops = []
@@ -580,10 +640,19 @@ class SlabSystem:
         self._check(self.lib.lg_update_neighbor_list(self.h))
 
     def run(self, dt: float, n_steps: int, rebuild_every: int = 0):
-        for _ in range(n_steps):
+        k = 0
+        while k < n_steps:
             if rebuild_every > 0 and self.steps % rebuild_every == 0:
                 self.update_neighbor_list()
-            self.do_step(dt)
+            if self.transport == "p2p" and self.kicked:
+                # the whole stretch up to the next rebuild is queued by ONE library call (step kernel, push, pull per step)
+                chunk = n_steps - k if rebuild_every <= 0 else min(n_steps - k, rebuild_every - self.steps % rebuild_every)
+                self._check(self.lib.lg_run_slab(self.h, self.halo, float(dt), chunk))
+                self.steps += chunk
+                k += chunk
+            else:
+                self.do_step(dt)
+                k += 1
 
     def synchronize(self):
         self._check(self.lib.lg_synchronize(self.h))
@@ -636,7 +705,7 @@ class SlabSystem:
             dist.all_reduce(tot, group=self.group)
         return {"pairs": int(tot[0]), "contacts": int(tot[1]), "owned_local": int(loc[2]), "ghosts_local": int(loc[3]),
                 "ghosts_total": int(tot[3]), "launches": int(out[5]), "repartitions": self.repartitions,
-                "halo_bytes_per_step": self.halo_bytes_per_step}
+                "halo_bytes_per_step": self.halo_bytes_per_step, "transport": self.transport}
 
     def diagnostics(self) -> dict:
         """test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26 over the owned particles of all ranks."""

@@ -34,6 +34,8 @@ ABI_SYMBOLS = (
     # slab decomposition support
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
+    "lg_halo_create", "lg_halo_set_lists", "lg_halo_export", "lg_halo_connect", "lg_halo_exchange", "lg_run_slab",
+    "lg_halo_disconnect", "lg_halo_destroy",
 )
 
 
@@ -128,6 +130,14 @@ def load_library(path: Optional[str] = None):
     lib.lg_import_bonds_device.argtypes = [vp, cpp, C.c_double, C.c_double, C.c_int64, vp, vp, vp, vp, vp]
     lib.lg_halo_pack.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp]
     lib.lg_halo_unpack.argtypes = [vp, C.c_int, vp, C.c_int, vp, vp]
+    lib.lg_halo_create.argtypes = [vp, C.c_int, C.POINTER(C.c_int64), C.POINTER(vp)]
+    lib.lg_halo_set_lists.argtypes = [vp, C.c_int, C.c_int, vp, C.c_int, vp, C.c_int, vp, C.c_int, vp]
+    lib.lg_halo_export.argtypes = [vp, C.c_int, C.c_char_p, C.POINTER(C.c_int64)]
+    lib.lg_halo_connect.argtypes = [vp, C.c_int, C.c_char_p, C.POINTER(C.c_int64)]
+    lib.lg_halo_exchange.argtypes = [vp, vp]
+    lib.lg_run_slab.argtypes = [vp, vp, C.c_double, C.c_int64]
+    lib.lg_halo_disconnect.argtypes = [vp]
+    lib.lg_halo_destroy.argtypes = [vp]
     for name in ABI_SYMBOLS:
         fn = getattr(lib, name)
         if name not in ("lg_last_error",):
