@@ -396,7 +396,13 @@ int rebuild(lg_system* s) {
     const bool defer = s->pending && s->variant == 1 && s->rebuilds > 0 && s->n_pairs > 0;
     if (!defer) LG_TRY(flush(s));
     const int n = (int)s->n;
-    if (defer) LG_CUDA(s->row_ptr_new.reserve((size_t)n + 1));
+    if (s->variant == 1) {  // the second set of row buffers is allocated up front: no cudaMalloc in the steady state
+        LG_CUDA(s->row_ptr_new.reserve((size_t)n + 1));
+        if (s->cols.cap > s->cols_new.cap) {
+            LG_CUDA(s->cols_new.reserve(s->cols.cap - 16));
+            LG_CUDA(s->tag_new.reserve(s->cols_new.cap));
+        }
+    }
     DevBuf<uint32_t>& row_ptr = defer ? s->row_ptr_new : s->row_ptr;
     DevBuf<int32_t>& cols = defer ? s->cols_new : s->cols;
     DevBuf<uint8_t>& tag = defer ? s->tag_new : s->tag;

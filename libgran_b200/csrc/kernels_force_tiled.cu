@@ -44,13 +44,16 @@ namespace {
 #define LG_TILE 512
 #endif
 #ifndef LG_RMAX
-#define LG_RMAX 64
+#define LG_RMAX 52
 #endif
 #ifndef LG_CCAP
-#define LG_CCAP 128
+#define LG_CCAP 112
 #endif
 #ifndef LG_MINB
-#define LG_MINB 3
+#define LG_MINB 4
+#endif
+#ifndef LG_MINB_EXACT
+#define LG_MINB_EXACT 3  // the reference-order arithmetic needs ~80 registers: 3 CTAs/SM measured faster than 4 with spills
 #endif
 #ifndef LG_BU
 #define LG_BU 5  // unroll factor of the five bridge springs in the relaxed-arithmetic path
@@ -218,7 +221,7 @@ __device__ __noinline__ void contact_heavy(const ForceArgs& A, int i, int j, uin
 }
 
 template <int MASK, int MODE, bool FACETS, bool FAST>
-__global__ void __launch_bounds__(TB, LG_MINB) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
+__global__ void __launch_bounds__(TB, FAST ? LG_MINB : LG_MINB_EXACT) step_tiled_kernel(const __grid_constant__ ForceArgs A) {
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
     constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
