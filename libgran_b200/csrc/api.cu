@@ -293,6 +293,11 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.err = s->err.p;
     A.rows_per_block = rows_per_block(s);
     A.fast = s->math_mode;
+    {   // short rows (aggregates) -> row kernel; long rows (packings) -> tile kernel.  LGB200_ROWS_KERNEL=0 disables it.
+        static const int rows_enabled = [] { const char* e = std::getenv("LGB200_ROWS_KERNEL"); return e ? std::atoi(e) : 1; }();
+        const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
+        A.use_rows = (rows_enabled && s->math_mode && k_mean <= 24.0) ? 1 : 0;
+    }
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia);
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;

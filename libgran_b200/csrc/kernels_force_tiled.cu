@@ -565,6 +565,357 @@ __global__ void __launch_bounds__(TB, FAST ? LG_MINB : LG_MINB_EXACT) step_tiled
     }
 }
 
+// ======================================================================================================================
+// step_rows_kernel -- the relaxed-arithmetic (LG_MATH_FAST) fused step for SHORT rows (aggregates: ~10 neighbors).
+//
+// Same inputs, same outputs and the same staging as step_tiled_kernel, but the work is cut the other way round:
+//   pass 1  one thread per BOND RECORD of the CTA's particles: the five bridge springs (full lanes, no compaction);
+//           the (force / m, torque / I) of record b waits in shared memory for the row pass
+//   pass 2  one thread per PARTICLE walks its row in ascending j with the accumulators in registers: geometry +
+//           Hamaker per pair, the bonded value looked up, Luding contact (rare for aggregates) evaluated in place
+//   pass 3  integrate, coalesced stores through the staged windows, connector update
+// There is no pair tile, no row map, no ballot compaction and no ordered shared-memory reduction: ~2.4x fewer
+// instructions per particle than the tile kernel (profiles/README.md r01f).  The accumulation order is still
+// ascending j with the pair value formed as (sinter | contact) + hamaker, i.e. the reference's order; only the
+// arithmetic inside the laws is the relaxed one.  Rows of a dense packing (~80 neighbors, several contacts per
+// particle) would serialise 80 iterations per thread and diverge on the contact law, so the host launches this kernel
+// only when the mean row length is small (launch_step_tiled: rows_kernel_suits).
+#ifndef LG_ROWS_TB
+#define LG_ROWS_TB 128
+#endif
+#ifndef LG_ROWS_MINB
+#define LG_ROWS_MINB 4
+#endif
+#ifndef LG_ROWS_BU
+#define LG_ROWS_BU 5
+#endif
+constexpr int RBU = LG_ROWS_BU;  // unroll factor of the five bridge springs in pass 1
+constexpr int RT = LG_ROWS_TB;   // threads = particles per CTA
+constexpr int RPC = 12 * RT;     // staged columns / tags per CTA (pairs beyond are read from global memory)
+constexpr int RBC = 2 * RT + 32; // bond records per CTA whose results are kept in shared memory
+constexpr int RH = RT;           // x is staged for RH particles before and after the CTA's own: neighbours of an
+                                 // aggregate are its own ~150 consecutive particles, so nearly every x_j is a shared-memory hit
+static_assert(RT % 32 == 0 && RPC % 16 == 0 && RBC % 16 == 0, "window sizes");
+
+struct alignas(16) RowsSmem {
+    double wx[3 * (RT + 2 * RH) + 4];  // window: x of the CTA's particles and of RH particles either side
+                              // windows: v, omega, theta of the CTA's particles; pass 3 reuses all four for the outputs
+    double wv[3 * RT + 4];
+    double ww[3 * RT + 4];
+    double wth[3 * RT + 4];
+    double res[6 * RBC];      // pass 1 results per bond record; pass 3: dx, dtheta of every particle
+    uint32_t wrow[RT + 12];   // window: row_ptr[i0 .. i0 + nrows]
+    uint32_t wbond[RT + 12];  // window: bptr[i0 .. i0 + nrows]
+    int32_t wcols[RPC + 8];   // window: columns of the CTA's first RPC pairs
+    uint8_t wtag[RPC + 32];   // window: their tags (snapshot at kernel entry)
+    uint8_t brow[RBC];        // local row of every staged bond record
+    unsigned long long bar[2];
+};
+
+template <bool DAMPED>
+__device__ __forceinline__ void bridge_fast(const ForceArgs& A, const double* ci, const double* cj, const double* len, d3 xi, d3 xj,
+                                            d3 vi, d3 vj, d3 wi, d3 wj, d3& fa, d3& ta) {
+    d3 force = zero3(), torque = zero3();
+#pragma unroll RBU
+    for (int k = 0; k < 5; k++)
+        bonded_spring_fast<DAMPED>(A.mp.k_d, A.mp.gamma_d, len[k], load3(ci + 3 * k), load3(cj + 3 * k), xi, xj, vi, vj, wi, wj,
+                                   force, torque);
+    fa = force * A.fc.inv_mass;
+    ta = torque * A.fc.inv_inertia;
+}
+
+// bonded value of record b (particle i = i0 + r) evaluated from global memory: used when the CTA holds more bond
+// records than fit in shared memory
+__device__ __noinline__ void bridge_from_global(const ForceArgs& A, int i, int j, uint32_t b, double* out6) {
+    const d3 xi = load3(A.x + 3 * (size_t)i), xj = load3(A.x + 3 * (size_t)j);
+    const double* ci = A.bconn + (size_t)b * 15;
+    const double* cj = A.bconn + (size_t)A.brev[b] * 15;
+    const double* len = A.blen + (size_t)b * 5;
+    d3 fa, ta;
+    if (A.mp.gamma_d != 0.0)
+        bridge_fast<true>(A, ci, cj, len, xi, xj, load3(A.v + 3 * (size_t)i), load3(A.v + 3 * (size_t)j),
+                          load3(A.w + 3 * (size_t)i), load3(A.w + 3 * (size_t)j), fa, ta);
+    else
+        bridge_fast<false>(A, ci, cj, len, xi, xj, zero3(), zero3(), zero3(), zero3(), fa, ta);
+    store3(out6, fa);
+    store3(out6 + 3, ta);
+}
+
+// The pairs of particle i0 + r that the hot loop of step_rows_kernel only marked (bit k of `slow`: pair pb + k), and,
+// for rows longer than 64, every later pair that it skipped: bridges whose record is not staged, overlapping pairs
+// (Luding contact) and pairs inside the rounding band of zero overlap (decided on the reference's exact expression).
+// Returns the sum of their pair values (law + Hamaker) in ascending j.
+template <bool kSinter, bool kHamaker>
+__device__ __noinline__ void rows_slow_pairs(const ForceArgs& A, const double* sx, int i0, int nrows, int r, uint32_t pb, uint32_t pe,  // sx: staged x of particles i0 .. i0 + nrows; r: this particle's index in it
+
+                                             unsigned long long slow, bool bonds_staged, uint32_t bond_base, double* out6) {
+    const d3 xi = load3(sx + 3 * r);
+    d3 acc_a = zero3(), acc_al = zero3();
+    for (uint32_t p = pb; p < pe; p++) {
+        const uint32_t k = p - pb;
+        if (k < 64u && !((slow >> k) & 1ull)) continue;
+        const int j = A.cols[p];
+        const int t = A.tag[p];
+        const unsigned rj = (unsigned)(j - i0);
+        const d3 xj = rj < (unsigned)nrows ? load3(sx + 3 * rj) : load3(A.x + 3 * (size_t)j);
+        const bool bond = kSinter && t >= kTagBond && t != kTagNone;
+        if (k >= 64u && bond && bonds_staged) continue;  // the hot loop has added it
+        const PairGeom gf = pair_geometry_fast(xi, xj);
+        d3 ha = zero3();
+        if constexpr (kHamaker) ha = hamaker_accel_fast(A.fc, gf);
+        double v6[6];
+        if (bond) {
+            bridge_from_global(A, i0 + r, j, bond_base + (uint32_t)(t - kTagBond), v6);
+        } else {
+            double overlap = A.fc.two_r - gf.len;
+            if (k >= 64u && overlap <= -A.fc.band) continue;  // the hot loop has handled it
+            if (fabs(overlap) < A.fc.band) overlap = contact_overlap(pair_geometry(xi, xj), A.fc.two_r);
+            if (overlap <= 0) {  // inside the band but not overlapping: Hamaker only, springs reset
+                if (t != kTagNone) {
+                    A.sgid[(size_t)(i0 + r) * A.S + t] = -1;
+                    A.tag[p] = (uint8_t)kTagNone;
+                }
+                acc_a += ha;
+                continue;
+            }
+            contact_heavy(A, i0 + r, j, p, v6);
+        }
+        acc_a += kHamaker ? load3(v6) + ha : load3(v6);
+        acc_al += load3(v6 + 3);
+    }
+    store3(out6, acc_a);
+    store3(out6 + 3, acc_al);
+}
+
+template <int MASK, bool FACETS>
+__global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __grid_constant__ ForceArgs A) {
+    constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
+    constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
+    constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    RowsSmem& sm = *reinterpret_cast<RowsSmem*>(smem_raw);
+
+    const int tid = threadIdx.x;
+    const int i0 = blockIdx.x * RT;
+    const int nrows = min(RT, A.n - i0);
+    const bool have_bonds = kSinter && A.bptr != nullptr;
+
+    // ---- stage (as step_tiled_kernel): state, pointer slices | columns and tags of the CTA's rows ------------
+    const int xlo = max(i0 - RH, 0), xcnt = min(A.n, i0 + RT + RH) - xlo;  // staged x range
+    const double* gx = A.x + 3 * (size_t)xlo;
+    const double* gv = A.v + 3 * (size_t)i0;
+    const double* gw = A.w + 3 * (size_t)i0;
+    const double* gth = A.th + 3 * (size_t)i0;
+    const uint32_t* grow = A.row_ptr + i0;
+    const uint32_t* gbond = have_bonds ? A.bptr + i0 : nullptr;
+    if (tid == 0) {
+        mbar_init(&sm.bar[0], 1);
+        mbar_init(&sm.bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const uint32_t nb3 = 24u * (uint32_t)nrows, nbp = 4u * (uint32_t)(nrows + 1), nbx = 24u * (uint32_t)xcnt;
+        uint32_t total = window_bytes(gx, nbx) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(gth, nb3) +
+                         window_bytes(grow, nbp);
+        if (have_bonds) total += window_bytes(gbond, nbp);
+        mbar_expect_tx(&sm.bar[0], total);
+        bulk_load(sm.wx, gx, nbx, &sm.bar[0]);
+        bulk_load(sm.wv, gv, nb3, &sm.bar[0]);
+        bulk_load(sm.ww, gw, nb3, &sm.bar[0]);
+        bulk_load(sm.wth, gth, nb3, &sm.bar[0]);
+        bulk_load(sm.wrow, grow, nbp, &sm.bar[0]);
+        if (have_bonds) bulk_load(sm.wbond, gbond, nbp, &sm.bar[0]);
+        const uint32_t rp0 = grow[0], rp1 = grow[nrows];
+        const uint32_t np0 = min(rp1 - rp0, (uint32_t)RPC);
+        const int32_t* gcols = A.cols + rp0;
+        const uint8_t* gtag = A.tag + rp0;
+        uint32_t total1 = window_bytes(gcols, 4u * np0);
+        if constexpr (kContact) total1 += window_bytes(gtag, np0);
+        mbar_expect_tx(&sm.bar[1], total1);
+        bulk_load(sm.wcols, gcols, 4u * np0, &sm.bar[1]);
+        if constexpr (kContact) bulk_load(sm.wtag, gtag, np0, &sm.bar[1]);
+    }
+    __syncthreads();  // the mbarriers are initialised
+    mbar_wait(&sm.bar[0], 0);
+
+    double* sxw = sm.wx + (window_lead(gx) >> 3);  // x of particle xlo + k at sxw[3 k]
+    double* sx = sxw + 3 * (i0 - xlo);             // the CTA's own particles
+    double* sv = sm.wv + (window_lead(gv) >> 3);
+    double* sw = sm.ww + (window_lead(gw) >> 3);
+    double* sth = sm.wth + (window_lead(gth) >> 3);
+    const uint32_t* sptr = sm.wrow + (window_lead(grow) >> 2);
+    const uint32_t* sbptr = sm.wbond + (window_lead(gbond) >> 2);  // valid only when have_bonds
+    const uint32_t p_begin = sptr[0];
+    const uint32_t b0 = have_bonds ? sbptr[0] : 0u;
+    const uint32_t nbond = have_bonds ? sbptr[nrows] - b0 : 0u;
+    const bool bonds_staged = nbond > 0 && nbond <= (uint32_t)RBC;
+    const int32_t* scols = sm.wcols + (window_lead(A.cols + p_begin) >> 2);
+    const uint8_t* stag = sm.wtag + window_lead(A.tag + p_begin);
+
+    auto neighbour = [&](int j, const double* s, const double* gsrc) -> d3 {  // v, omega: own particles staged
+        const unsigned rj = (unsigned)(j - i0);
+        return rj < (unsigned)nrows ? load3(s + 3 * rj) : load3(gsrc + 3 * (size_t)j);
+    };
+    auto neighbour_x = [&](int j) -> d3 {
+        const unsigned rj = (unsigned)(j - xlo);
+        return rj < (unsigned)xcnt ? load3(sxw + 3 * rj) : load3(A.x + 3 * (size_t)j);
+    };
+
+    // ---- pass 1: one thread per bond record ---------------------------------------------------------------
+    if constexpr (kSinter) {
+        if (bonds_staged) {
+            if (tid < nrows)
+                for (uint32_t b = sbptr[tid]; b < sbptr[tid + 1]; b++) sm.brow[b - b0] = (uint8_t)tid;
+            __syncthreads();
+            for (uint32_t bl = tid; bl < nbond; bl += RT) {
+                const uint32_t b = b0 + bl;
+                const int r = sm.brow[bl];
+                const int j = A.bj[b];
+                const double* ci = A.bconn + (size_t)b * 15;
+                const double* cj = A.bconn + (size_t)A.brev[b] * 15;
+                const double* len = A.blen + (size_t)b * 5;
+                const d3 xi = load3(sx + 3 * r), xj = neighbour_x(j);
+                d3 fa, ta;
+                if (A.mp.gamma_d != 0.0)
+                    bridge_fast<true>(A, ci, cj, len, xi, xj, load3(sv + 3 * r), neighbour(j, sv, A.v), load3(sw + 3 * r),
+                                      neighbour(j, sw, A.w), fa, ta);
+                else
+                    bridge_fast<false>(A, ci, cj, len, xi, xj, zero3(), zero3(), zero3(), zero3(), fa, ta);
+                store3(sm.res + 6 * bl, fa);
+                store3(sm.res + 6 * bl + 3, ta);
+            }
+        }
+    }
+    mbar_wait(&sm.bar[1], 0);
+    __syncthreads();  // pass 1 results
+
+    // ---- pass 2: one thread per particle, its row in ascending j ---------------------------------------------
+    d3 xn = zero3(), vn = zero3(), wn = zero3(), dth = zero3(), dxv = zero3();
+    if (tid < nrows) {
+        const d3 xi = load3(sx + 3 * tid), vi = load3(sv + 3 * tid), wi = load3(sw + 3 * tid);
+        d3 acc_a = zero3(), acc_al = zero3();
+        const uint32_t pb = sptr[tid], pe = sptr[tid + 1];
+        // Pairs that need an out-of-line law (Luding contact; a bridge whose record is not staged) are only MARKED in
+        // the hot loop and evaluated afterwards: a call inside the loop would force its live values into local memory.
+        unsigned long long slow = 0ull;  // bit k: pair pb + k (k < 64) is evaluated by the second loop
+        for (uint32_t p = pb; p < pe; p++) {
+            const uint32_t ps = p - p_begin;
+            const int j = ps < (uint32_t)RPC ? scols[ps] : A.cols[p];
+            const d3 xj = neighbour_x(j);
+            const PairGeom g = pair_geometry_fast(xi, xj);
+            d3 pa = zero3();
+            if constexpr (kHamaker) pa = hamaker_accel_fast(A.fc, g);
+            if constexpr (kContact) {
+                const int t = ps < (uint32_t)RPC ? stag[ps] : A.tag[p];
+                if (kSinter && t >= kTagBond && t != kTagNone) {
+                    if (bonds_staged) {
+                        const uint32_t bl = sbptr[tid] + (uint32_t)(t - kTagBond) - b0;
+                        const d3 sa = load3(sm.res + 6 * bl);
+                        pa = kHamaker ? sa + pa : sa;  // pair value = sinter(i,j) + hamaker(i,j)
+                        acc_al += load3(sm.res + 6 * bl + 3);
+                    } else {
+                        if (p - pb < 64u) slow |= 1ull << (p - pb);
+                        continue;
+                    }
+                } else {
+                    const double overlap = A.fc.two_r - g.len;
+                    if (overlap <= -A.fc.band) {  // clearly apart
+                        if (t != kTagNone) {  // reset_springs (contact_force.h:68-71)
+                            A.sgid[(size_t)(i0 + tid) * A.S + t] = -1;
+                            A.tag[p] = (uint8_t)kTagNone;
+                        }
+                    } else {  // overlapping, or inside the rounding band of zero (decided on the exact expression below)
+                        if (p - pb < 64u) slow |= 1ull << (p - pb);
+                        continue;
+                    }
+                }
+            }
+            acc_a += pa;
+        }
+        if constexpr (kContact) {
+            if (slow != 0ull || pe - pb > 64u) {  // rare: out of line, so that the hot loop keeps its registers
+                double out6[6];
+                rows_slow_pairs<kSinter, kHamaker>(A, sxw, xlo, xcnt, tid + (i0 - xlo), pb, pe, slow, bonds_staged, have_bonds ? sbptr[tid] : 0u, out6);
+                acc_a += load3(out6);
+                acc_al += load3(out6 + 3);
+            }
+        }
+        if constexpr (FACETS) {
+            const Accel u = unary_forces(A, i0 + tid, xi, vi, wi);
+            acc_a += u.a;
+            acc_al += u.alpha;
+        }
+        const double dt = A.dt;
+        vn = vi + acc_a * dt;   // increment_v(n, a * dt)
+        dxv = vn * dt;          // increment_x(n, v * dt), v already updated
+        xn = xi + dxv;
+        wn = wi + acc_al * dt;  // increment_omega
+        dth = wn * dt;          // increment_theta, omega already updated
+    }
+    __syncthreads();  // every read of the staged state and of the pass-1 results is done
+
+    // ---- pass 3: outputs through the windows (coalesced stores), connector update -----------------------------
+    if (tid < nrows) {
+        const d3 thn = load3(sth + 3 * tid) + dth;
+        store3(sx + 3 * tid, xn);
+        store3(sv + 3 * tid, vn);
+        store3(sw + 3 * tid, wn);
+        store3(sth + 3 * tid, thn);
+        store3(sm.res + 6 * tid, dxv);
+        store3(sm.res + 6 * tid + 3, dth);
+    }
+    __syncthreads();
+    for (int idx = tid; idx < 3 * nrows; idx += RT) {
+        const size_t gidx = 3 * (size_t)i0 + idx;
+        A.x_next[gidx] = sx[idx];
+        A.v_next[gidx] = sv[idx];
+        A.w_next[gidx] = sw[idx];
+        A.th[gidx] = sth[idx];
+    }
+    if constexpr (kSinter) {
+        if (have_bonds) {
+            // connectors of the CTA's particles: c += dx ; c += dtheta x (c - x_new)   (sinter_bridge.h:36-41,67-74)
+            const int ncon = (int)nbond * 5;
+            for (int cq = tid; cq < ncon; cq += RT) {
+                const int bl = cq / 5;
+                const int r = bonds_staged ? (int)sm.brow[bl] : find_row(sbptr, nrows, b0 + (uint32_t)bl);
+                const size_t off = (size_t)b0 * 15 + 3 * (size_t)cq;
+                d3 ck = load3(A.bconn + off) + load3(sm.res + 6 * r);
+                const d3 arm = ck - load3(sx + 3 * r);
+                ck = ck + cross(load3(sm.res + 6 * r + 3), arm);
+                store3(A.bconn_next + off, ck);
+            }
+        }
+    }
+}
+
+template <int MASK, bool FACETS>
+void launch_rows_one(const ForceArgs& args, cudaStream_t st) {
+    static bool configured = false;  // per instantiation
+    if (!configured) {
+        cudaFuncSetAttribute(step_rows_kernel<MASK, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowsSmem));
+        configured = true;
+    }
+    step_rows_kernel<MASK, FACETS><<<(args.n + RT - 1) / RT, RT, sizeof(RowsSmem), st>>>(args);
+    g_launch_count++;
+}
+
+template <int MASK>
+void launch_rows_facets(const ForceArgs& args, cudaStream_t st) {
+    if (args.n_facets > 0) launch_rows_one<MASK, true>(args, st); else launch_rows_one<MASK, false>(args, st);
+}
+
+void launch_rows(const ForceArgs& args, int mask, cudaStream_t st) {
+    switch (mask & (MODEL_CONTACT | MODEL_HAMAKER | MODEL_SINTER)) {
+        case MODEL_CONTACT: launch_rows_facets<MODEL_CONTACT>(args, st); break;
+        case MODEL_CONTACT | MODEL_HAMAKER: launch_rows_facets<MODEL_CONTACT | MODEL_HAMAKER>(args, st); break;
+        case MODEL_SINTER: launch_rows_facets<MODEL_SINTER>(args, st); break;
+        case MODEL_SINTER | MODEL_HAMAKER: launch_rows_facets<MODEL_SINTER | MODEL_HAMAKER>(args, st); break;
+        case MODEL_HAMAKER: launch_rows_facets<MODEL_HAMAKER>(args, st); break;
+        default: launch_rows_facets<0>(args, st); break;
+    }
+}
+
 template <int MASK, int MODE, bool FACETS, bool FAST>
 void launch_one(const ForceArgs& args, cudaStream_t st) {
     static bool configured = false;  // per instantiation
@@ -609,7 +960,9 @@ int tiled_tile_pairs() { return TILE; }
 // fused == true : additionally integrates into x_next, v_next, w_next, th, bconn_next  [MODE_FUSED]
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {
     if (args.n <= 0) return;
-    if (fused)
+    if (fused && args.fast && args.use_rows)
+        launch_rows(args, mask, st);
+    else if (fused)
         launch_mode<MODE_FUSED>(args, mask, st);
     else
         launch_mode<MODE_FORCE>(args, mask, st);

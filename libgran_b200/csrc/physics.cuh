@@ -177,11 +177,37 @@ __device__ __forceinline__ d3 cross_fma(d3 a, d3 b) {
     return d3{fma(a.y, b.z, -(a.z * b.y)), fma(a.z, b.x, -(a.x * b.z)), fma(a.x, b.y, -(a.y * b.x))};
 }
 
+// Reciprocal and reciprocal square root for NORMAL, positive operands (squared distances, products of gaps): the
+// hardware seed (MUFU.RCP64H / MUFU.RSQ64H, >= 20 bits) refined by Newton steps to ~1 ulp.  Unlike 1.0 / x and rsqrt(x)
+// there is no special-case slow path, hence no CALL in the instruction stream: a call inside the pair loop makes the
+// compiler park the loop's accumulators in local memory (profiles/README.md r01f).
+__device__ __forceinline__ double rcp_nr(double x) {
+    double y;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    double e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    y = fma(y, e, y);
+    e = fma(-x, y, 1.0);
+    return fma(y, e, y);
+}
+__device__ __forceinline__ double rsqrt_nr(double x) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
+    const double hx = 0.5 * x;
+    double e = fma(-hx * y, y, 0.5);   // 0.5 (1 - x y^2)
+    y = fma(y, e, y);
+    e = fma(-hx * y, y, 0.5);
+    y = fma(y, e, y);
+    e = fma(-hx * y, y, 0.5);
+    return fma(y, e, y);
+}
+
 __device__ __forceinline__ PairGeom pair_geometry_fast(d3 xi, d3 xj) {
     PairGeom g;
     g.dx = xi - xj;
     const double z = dot_fma(g.dx, g.dx);
-    const double inv = z > 0.0 ? rsqrt(z) : 0.0;
+    const double inv = z > 0.0 ? rsqrt_nr(z) : 0.0;
     g.len = z * inv;
     g.n = g.dx * inv;
     return g;
@@ -208,7 +234,7 @@ __device__ __forceinline__ d3 hamaker_accel_fast(const HamakerFast& hf, const Pa
     const double s = hf.r2 + h, q = hf.r4 + h;
     const double hq = h * q;
     const double den = (hq * hq) * (s * s * s);
-    const double coef = hf.c0m / den;   // > 0: attraction, along -n (towards j)
+    const double coef = hf.c0m * rcp_nr(den);   // > 0: attraction, along -n (towards j)
     return (-coef) * g.n;
 }
 

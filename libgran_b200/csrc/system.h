@@ -73,6 +73,7 @@ struct ForceArgs {
     // tiled / fused kernel only
     int rows_per_block;
     int fast;           // relaxed arithmetic (lg_set_math_mode)
+    int use_rows;       // fast + fused only: short rows -> step_rows_kernel (one thread per particle) instead of the tile kernel
     FastConsts fc;      // its host-computed constants
     double dt;          // integration step of the fused update
     double* x_next;     // next-step buffers (double-buffered state)

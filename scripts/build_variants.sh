@@ -15,5 +15,5 @@ while [ $# -ge 2 ]; do
     else cp build/$f.o $d/$f.o; fi
   done; wait
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -shared -o ../variants/liblgb200_$name.so $d/*.o
-  grep -A2 "ILi6ELi1ELb0ELb1" $d/kernels_force_tiled.ptxas.log | grep -E "spill|Used" | tr '\n' ' '; echo " <- $name"
+  grep -A2 "step_rows_kernelILi6ELb0\|ILi6ELi1ELb0ELb1" $d/kernels_force_tiled.ptxas.log | grep -E "spill|Used" | tr '\n' ' '; echo " <- $name"
 done
