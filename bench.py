@@ -39,7 +39,7 @@ from libgran_b200 import scenarios as S  # noqa: E402
 METRIC = "particle-timesteps/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused step kernel on this workload, from the committed
 # `ncu --set full` captures (profiles/r01d_step_tiled_ncu_raw.csv: 482.0 MB + 301.7 MB; exact mode r01b: 482 + 301 MB)
-TRAFFIC_NCU = {"fast": 783.8e6, "exact": 783.0e6}
+TRAFFIC_NCU = {"fast": 806.3e6, "exact": 783.0e6}  # fast: step_rows_kernel, profiles/r01f_step_rows_ncu_raw.csv (491.9 + 314.4 MB)
 REBUILD_EVERY = 20
 
 
@@ -194,7 +194,9 @@ def run_ours(args):
     fused = args.variant in (None, 1)
     launch_bytes = step_bytes if fused else force_bytes
     achieved = launch_bytes / (force_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "step_tiled_kernel (fused pair force + Verlet + connectors)" if fused else "pair_force",
+    rows_kernel = fused and mode == 1 and cnt["pairs"] <= 24 * n and os.environ.get("LGB200_ROWS_KERNEL", "1") != "0"
+    kname = ("step_rows_kernel" if rows_kernel else "step_tiled_kernel") + " (fused pair force + Verlet + connectors)"
+    roofline = {"bound": "hbm", "kernel": kname if fused else "pair_force",
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                 "frac": round(achieved / peak, 4), "traffic": TRAFFIC_NCU.get(args.math if fused else "variant0"), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(launch_bytes), "avg_launch_ms": round(force_avg_ms, 5),
@@ -218,9 +220,11 @@ def run_ours(args):
     out_np = [t.numpy() for t in outs]
     e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)  # model tables built once (as a ctor would)
     e2e_steps = args.steps
+    e2e_sys.run(cfg.dt, effective_warmup(args), REBUILD_EVERY)  # untimed: sizes the neighbor / scratch buffers once
+    e2e_sys.synchronize()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    e2e_sys.set_state(*host_np)  # H2D of x0, v0, theta0, omega0
+    e2e_sys.set_state(*host_np)  # H2D of x0, v0, theta0, omega0 (re-arms the first-step half kick)
     ke = 0.0
     for k in range(e2e_steps):
         if k % REBUILD_EVERY == 0:
@@ -321,7 +325,7 @@ def run_slab(args, scn, world, rank, local_rank):
     slow = float(worst[0])
     peak, peak_src = measured_peaks()
     ach = step_bytes_local / (force_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": "step_tiled_kernel (fused pair force + Verlet), this rank", "achieved": round(ach, 1),
+    roofline = {"bound": "hbm", "kernel": ("step_rows_kernel" if mode else "step_tiled_kernel") + " (fused pair force + Verlet + connectors), this rank", "achieved": round(ach, 1),
                 "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(step_bytes_local), "avg_launch_ms": round(force_avg_ms, 5),
                 "slowest_rank_launch_ms": round(slow, 5), "launches_timed": int(fl.value),
@@ -334,12 +338,13 @@ def run_slab(args, scn, world, rank, local_rank):
     t0 = time.perf_counter()
     sysm.set_state_host(*scn.state)  # H2D of this rank's owned + ghost particles from pinned memory
     ke = 0.0
-    for k in range(e2e_steps):
-        if k % REBUILD_EVERY == 0:
-            sysm.update_neighbor_list()
-        sysm.do_step(cfg.dt)
-        if (k + 1) % 10 == 0:
-            ke = sysm.diagnostics()["ke"]  # all-reduce + D2H
+    sysm.steps = 0  # new positions: the first run() call below rebuilds the neighbor rows
+    done = 0
+    while done < e2e_steps:
+        chunk = min(10, e2e_steps - done)
+        sysm.run(cfg.dt, chunk, REBUILD_EVERY)  # the driver-facing loop call (rebuild every 20 steps inside)
+        done += chunk
+        ke = sysm.kinetic_energy()  # all-reduce + D2H of the step's metric
     outs = sysm.get_owned_host(("x", "v", "omega", "theta"))  # D2H of the owned particles
     sysm.synchronize()
     torch.cuda.synchronize()
@@ -353,8 +358,8 @@ def run_slab(args, scn, world, rank, local_rank):
            "h2d_bytes_per_step": round(4 * 24 * int(nloc[0]) / e2e_steps, 1),
            "d2h_bytes_per_step": round((4 * 24 * int(nloc[1]) + (e2e_steps // 10) * 12 * 8 * world) / e2e_steps, 1),
            "steps": e2e_steps, "final_ke": ke,
-           "what": "per rank: set_state_host (H2D, pinned) + K x do_step with halo exchange (+ rebuild/20, KE all-reduce + "
-                   "read-back/10) + owned x,v,omega,theta (D2H)"}
+           "what": "per rank: set_state_host (H2D, pinned) + K/10 x [run(10 steps: step + halo exchange, rebuild/20) + KE "
+                   "all-reduce + read-back] + owned x,v,omega,theta (D2H)"}
     del outs
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": warm,

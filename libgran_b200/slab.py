@@ -707,6 +707,16 @@ class SlabSystem:
                 "ghosts_total": int(tot[3]), "launches": int(out[5]), "repartitions": self.repartitions,
                 "halo_bytes_per_step": self.halo_bytes_per_step, "transport": self.transport}
 
+    def kinetic_energy(self) -> float:
+        """compute_total_kinetic_energy (test/compute_energy.cpp:7-17) over the owned particles of all ranks."""
+        cfg = self.cfg
+        with torch.cuda.stream(self.stream):
+            v, w = (self._field_view(f)[self.own_idx] for f in ("v", "omega"))
+            s = (cfg.mass * (v * v).sum() / 2.0 + cfg.inertia * (w * w).sum() / 2.0).reshape(1)
+            if self.world > 1:
+                dist.all_reduce(s, group=self.group)
+            return float(s)  # inside the stream context, see needs_repartition
+
     def diagnostics(self) -> dict:
         """test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26 over the owned particles of all ranks."""
         cfg = self.cfg
