@@ -51,6 +51,18 @@ def test_bad_arguments(lib):
     assert lib.lg_destroy(None) == 0
 
 
+def test_halo_bad_arguments(lib):
+    """lg_halo_*: argument errors are reported without touching a device."""
+    hl = C.c_void_p()
+    assert lib.lg_halo_create(None, 1, (C.c_int64 * 1)(8), C.byref(hl)) == -1
+    assert lib.lg_halo_exchange(None, None) == -1
+    assert lib.lg_run_slab(None, None, 1e-13, 1) == -1
+    assert lib.lg_halo_set_lists(None, 0, 0, None, 0, None, 0, None, 0, None) == -1
+    assert lib.lg_halo_export(None, 0, C.create_string_buffer(64), (C.c_int64 * 4)()) == -1
+    assert lib.lg_halo_connect(None, 0, C.create_string_buffer(64), (C.c_int64 * 4)()) == -1
+    assert lib.lg_halo_disconnect(None) == 0 and lib.lg_halo_destroy(None) == 0
+
+
 def test_size_mismatch_exception(lib):
     """rotational_system.h:69-70: differing x0 / v0 / theta0 / omega0 sizes throw SizeMismatchException."""
     from libgran_b200.system import GranularSystem, SizeMismatchException

@@ -38,10 +38,10 @@ def _scenario(name):
     raise KeyError(name)
 
 
-def _worker(rank, world, port, name, out_dir):
+def _worker(rank, world, port, name, out_dir, transport="p2p"):
     import torch.distributed as dist
 
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), LGB200_HALO=transport)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
@@ -60,6 +60,8 @@ def _worker(rank, world, port, name, out_dir):
                 res[f"{f}_{cp}"] = sysm.get(f)
         cnt = sysm.counters()
         diag = sysm.diagnostics()
+        if world > 1 and cnt["transport"] != transport:
+            raise RuntimeError(f"halo transport {cnt['transport']} in use, {transport} requested")
         if rank == 0:
             np.savez(os.path.join(out_dir, "slab.npz"), repartitions=cnt["repartitions"], pairs=cnt["pairs"],
                      contacts=cnt["contacts"], ghosts=cnt["ghosts_total"], ke=diag["ke"], rg=diag["rg"], **res)
@@ -104,3 +106,18 @@ def test_slab_equals_single_gpu(lib, tmp_path, name, world):
             assert int(got["ghosts"]) > 0
         if name == "packing":
             assert int(got["repartitions"]) > 1, "the packing case is meant to force repartitions"
+
+
+def test_slab_nccl_transport_equals_single_gpu(lib, tmp_path):
+    """The NCCL isend/irecv halo path (LGB200_HALO=nccl, also the fallback when cudaIpc mappings are unavailable)
+    gives the same bits as the peer-to-peer path and as one GPU."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import torch.multiprocessing as mp
+
+    mp.spawn(_worker, args=(2, _free_port(), "fractal", str(tmp_path), "nccl"), nprocs=2, join=True)
+    got = np.load(os.path.join(str(tmp_path), "slab.npz"))
+    want, cnt, _ = _single("fractal")
+    for key, val in want.items():
+        assert np.array_equal(got[key], val), f"nccl transport: {key} differs"
+    assert int(got["pairs"]) == cnt["pairs"]
