@@ -157,6 +157,12 @@ struct lg_system {
     DevBuf<int32_t> cell_of, order;
     DevBuf<uint32_t> cell_start, cell_cursor, scan_scratch;
     int64_t last_cells = 0;
+    // The cell grid of the previous rebuild is reused for kGridReuse rebuilds: cell_coords clamps, so a grid that no
+    // longer covers every particle still yields the exact rows (the cell list is only a candidate filter, cell edge
+    // >= r_verlet), and the bounding-box kernels plus their host read-back drop out of most rebuilds.
+    NeighborGrid grid{};
+    bool grid_valid = false;
+    int grid_age = 0;
 
     // diagnostics scratch
     DevBuf<double> diag_partials, diag_out;
@@ -412,31 +418,41 @@ int rebuild(lg_system* s) {
     DevBuf<int32_t>& cols = defer ? s->cols_new : s->cols;
     DevBuf<uint8_t>& tag = defer ? s->tag_new : s->tag;
     cudaStream_t st = s->stream;
-    // 1. bounding box -> grid
-    launch_bbox(n, s->x.p, s->bbox_scratch.p, s->bbox_out.p, st);
-    LG_CUDA(cudaGetLastError());
-    LG_CUDA(cudaMemcpyAsync(s->h_pinned, s->bbox_out.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
-    LG_CUDA(cudaStreamSynchronize(st));
+    // 1. bounding box -> grid (reused from the previous rebuild most of the time)
+    constexpr int kGridReuse = 15;
     NeighborGrid g{};
-    double cell = s->r_verlet * (1.0 + 1e-6);
-    const double max_cells = 16.0 * (double)n + 65536.0;
-    for (;;) {
-        double total = 1.0;
-        for (int k = 0; k < 3; k++) {
-            double ext = s->h_pinned[3 + k] - s->h_pinned[k];
-            if (!(ext >= 0.0) || !std::isfinite(ext)) return fail(LG_EINVAL, "non-finite particle positions");
-            double d = std::floor(ext / cell) + 1.0;
-            g.dim[k] = d > 2.0e9 ? 2000000000 : (int)d;
-            total *= d;
+    if (s->grid_valid && s->grid_age < kGridReuse) {
+        g = s->grid;
+        s->grid_age++;
+    } else {
+        launch_bbox(n, s->x.p, s->bbox_scratch.p, s->bbox_out.p, st);
+        LG_CUDA(cudaGetLastError());
+        LG_CUDA(cudaMemcpyAsync(s->h_pinned, s->bbox_out.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaStreamSynchronize(st));
+        double cell = s->r_verlet * (1.0 + 1e-6);
+        const double max_cells = 16.0 * (double)n + 65536.0;
+        for (;;) {
+            double total = 1.0;
+            for (int k = 0; k < 3; k++) {
+                double ext = s->h_pinned[3 + k] - s->h_pinned[k];
+                if (!(ext >= 0.0) || !std::isfinite(ext)) return fail(LG_EINVAL, "non-finite particle positions");
+                double d = std::floor(ext / cell) + 1.0;
+                g.dim[k] = d > 2.0e9 ? 2000000000 : (int)d;
+                total *= d;
+            }
+            if (total <= max_cells) {
+                g.n_cells = (int64_t)g.dim[0] * g.dim[1] * g.dim[2];
+                break;
+            }
+            cell *= 1.26;
         }
-        if (total <= max_cells) {
-            g.n_cells = (int64_t)g.dim[0] * g.dim[1] * g.dim[2];
-            break;
-        }
-        cell *= 1.26;
+        g.cell = cell;
+        for (int k = 0; k < 3; k++) g.lo[k] = s->h_pinned[k];
+        s->last_cells = g.n_cells;
+        s->grid = g;
+        s->grid_valid = true;
+        s->grid_age = 0;
     }
-    g.cell = cell;
-    for (int k = 0; k < 3; k++) g.lo[k] = s->h_pinned[k];
     s->last_cells = g.n_cells;
     // 2. histogram, scan, scatter
     const size_t nc1 = (size_t)g.n_cells + 1;
@@ -773,6 +789,7 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     s->kicked = false;
     s->half_kicked = false;
     if (s->rows_staged) LG_TRY(install_staged_rows(s));  // the discarded evaluation would have installed them
+    s->grid_valid = false;  // new positions: the next rebuild measures the bounding box again
     s->pending = false;
     return LG_OK;
 }
@@ -977,6 +994,7 @@ int lg_enable_neighbor_list(lg_system* s, double r_verlet) {
     s->allpairs_built = false;
     s->n_pairs = 0;
     s->rows_staged = false;
+    s->grid_valid = false;
     LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, ((size_t)s->n + 1) * sizeof(uint32_t), s->stream));
     return LG_OK;
 }
@@ -1174,6 +1192,7 @@ int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, c
     s->kicked = kicked != 0;
     s->half_kicked = false;
     if (s->rows_staged) LG_TRY(install_staged_rows(s));  // the discarded evaluation would have installed them
+    s->grid_valid = false;  // new positions: the next rebuild measures the bounding box again
     s->pending = false;
     return LG_OK;
 }

@@ -675,24 +675,37 @@ class SlabSystem:
         return out.cpu().numpy()
 
     def set_state_host(self, x, v, theta, omega):
-        """lg_set_state for a decomposed system: every rank uploads (H2D, pinned) the rows of the caller's full arrays
-        that it holds (owned and ghost); re-arms the first-step half kick like the reference constructor."""
-        gid = self.gid.cpu().numpy()
-        bufs = [torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64)[gid])).pin_memory() for a in (x, v, theta, omega)]
-        dp = C.POINTER(C.c_double)
-        self._check(self.lib.lg_set_state(self.h, self.n_local, *[C.cast(b.data_ptr(), dp) for b in bufs]))
+        """lg_set_state for a decomposed system.  Every rank copies the caller's full arrays host -> device (asynchronous
+        when they are pinned; numpy arrays or tensors) and gathers the rows it holds (owned and ghost) on the device;
+        re-arms the first-step half kick like the reference constructor.  The copies run on torch's current stream, not
+        on the library's: pinned host blocks remember the streams that used them, and the library's stream dies with
+        the system."""
+        cur = torch.cuda.current_stream(self.device)
+        loc = []
+        for a in (x, v, theta, omega):
+            t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64)))
+            loc.append(t.to(self.device, non_blocking=True).index_select(0, self.gid).contiguous())
+        x_ref = loc[0][self.own_idx].clone()
+        cur.synchronize()
+        self._check(self.lib.lg_import_state_device(self.h, *[c.data_ptr() for c in loc], None, None, 0))  # synchronises
         self.kicked = False
-        with torch.cuda.stream(self.stream):
-            self.x_ref = self._field_view("x")[self.own_idx].clone()
+        self.x_ref = x_ref
 
     def get_owned_host(self, names) -> dict:
-        """D2H of this rank's owned rows (global ids + fields), without assembling the global arrays."""
+        """D2H of this rank's owned rows (global ids + fields) into pinned buffers, without assembling the global arrays."""
         out = {"gid": self.gid[self.own_idx].cpu().numpy()}
+        src = {}
         with torch.cuda.stream(self.stream):
             for f in names:
                 if f in ("a", "alpha"):
                     self._check(self.lib.lg_flush(self.h))
-                out[f] = self._field_view(f)[self.own_idx].cpu().numpy()
+                src[f] = self._field_view(f)[self.own_idx]
+        self.stream.synchronize()
+        for f in names:  # on torch's current stream (see set_state_host)
+            buf = torch.empty(src[f].shape, dtype=torch.float64, pin_memory=True)
+            buf.copy_(src[f], non_blocking=True)
+            out[f] = buf.numpy()
+        torch.cuda.current_stream(self.device).synchronize()
         return out
 
     def counters(self) -> dict:

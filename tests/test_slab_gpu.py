@@ -65,6 +65,14 @@ def _worker(rank, world, port, name, out_dir, transport="p2p"):
         if rank == 0:
             np.savez(os.path.join(out_dir, "slab.npz"), repartitions=cnt["repartitions"], pairs=cnt["pairs"],
                      contacts=cnt["contacts"], ghosts=cnt["ghosts_total"], ke=diag["ke"], rg=diag["rg"], **res)
+        # host upload / download of a decomposed system: the caller's arrays in, this rank's owned rows out
+        sysm.set_state_host(*scn.state)
+        if not np.array_equal(sysm.get("x"), np.asarray(scn.state[0])):
+            raise RuntimeError("set_state_host: positions do not round-trip")
+        own = sysm.get_owned_host(("x", "omega"))
+        if not (np.array_equal(own["x"], np.asarray(scn.state[0])[own["gid"]])
+                and np.array_equal(own["omega"], np.asarray(scn.state[3])[own["gid"]])):
+            raise RuntimeError("get_owned_host: owned rows differ from the uploaded state")
         sysm.close()
     finally:
         dist.destroy_process_group()
