@@ -219,7 +219,9 @@ def run_ours(args):
     out_np = [t.numpy() for t in outs]
     e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)  # model tables built once (as a ctor would)
     e2e_steps = args.steps
-    e2e_sys.run(cfg.dt, effective_warmup(args), REBUILD_EVERY)  # untimed: sizes the neighbor / scratch buffers once
+    # untimed priming with dt = 0: sizes the neighbor / scratch buffers for exactly this state and leaves positions,
+    # velocities and bridge connectors where the constructor put them (x += v * 0, c += 0)
+    e2e_sys.run(0.0, effective_warmup(args), REBUILD_EVERY)
     e2e_sys.synchronize()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -331,6 +333,11 @@ def run_slab(args, scn, world, rank, local_rank):
                 "share_of_step": round(force_avg_ms / (ms / args.steps), 3)}
 
     # end to end: host buffers in, host buffers out, through the slab driver
+    # (a fresh system, primed with dt = 0 like the single-GPU arm: same buffers, untouched state and connectors)
+    sysm.close()
+    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode)
+    sysm.run(0.0, warm, REBUILD_EVERY)
+    own = sysm.counters()["owned_local"]
     pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in scn.state]
     sysm.get_owned_host(("x", "v", "omega", "theta"))  # untimed: allocates the pinned download buffers once
     e2e_steps = args.steps
