@@ -40,7 +40,7 @@ METRIC = "particle-timesteps/s"
 # dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused step kernel on this workload, from the committed
 # `ncu --set full` captures (profiles/r01d_step_tiled_ncu_raw.csv: 482.0 MB + 301.7 MB; exact mode r01b: 482 + 301 MB)
 TRAFFIC_NCU = {"fast": 806.3e6, "exact": 783.0e6}  # fast: step_rows_kernel, profiles/r01f_step_rows_ncu_raw.csv (491.9 + 314.4 MB)
-REBUILD_EVERY = 20
+REBUILD_EVERY = int(os.environ.get("LGB200_BENCH_REBUILD_EVERY", "20"))  # 20 = the reference drivers' period; the override is for diagnostics only
 
 
 def measured_peaks():
@@ -55,7 +55,7 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """Samples SM clocks and throttle reasons of one GPU during the timed region: NVML polled every 5 ms from a
+    """Samples SM clocks and throttle reasons of one GPU during the timed region: NVML polled every 2 ms from a
     thread (the timed region lasts tens of milliseconds, far less than nvidia-smi's shortest loop period)."""
 
     def __init__(self, gpu_index: int = 0):
@@ -93,7 +93,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            if self._stop.wait(0.005):
+            if self._stop.wait(0.002):
                 break
 
     def stop(self):
