@@ -309,6 +309,8 @@ def build_halo_plan(t: LocalTables, rank: int, world: int, group=None) -> HaloPl
     bptr = t.bptr.to(torch.int64)
     rec_owner = torch.repeat_interleave(torch.arange(n, device=dev), bptr[1:] - bptr[:-1])
     grec = torch.nonzero(~t.owned[rec_owner], as_tuple=True)[0] if t.n_bonds else torch.zeros(0, dtype=torch.int64, device=dev)
+    if len(grec):  # only the records an owned particle's bridge reads as its mirror: ghost (j, i) with i owned here
+        grec = grec[t.owned[t.bj[grec].to(torch.int64)]]
     r_src = t.src[rec_owner[grec]]
     req_b = torch.stack([_i2f(t.gid[rec_owner[grec]]), _i2f(t.gid[t.bj[grec].to(torch.int64)])], dim=1) if len(grec) else \
         torch.zeros((0, 2), dtype=torch.float64, device=dev)
