@@ -735,6 +735,32 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
         bulk_load(sm.wcols, gcols, 4u * np0, &sm.bar[1]);
         if constexpr (kContact) bulk_load(sm.wtag, gtag, np0, &sm.bar[1]);
     }
+    // The first bond record of this thread (record b0 + tid) does not depend on anything staged: its indices, both
+    // connector sets and the rest lengths are requested NOW, so that their L2 round trips (indices, then connectors)
+    // run underneath the bulk copies instead of after them.
+    double e_ci[15], e_cj[15], e_len[5];
+    int e_j = 0;
+    bool e_have = false;
+    if constexpr (kSinter) {
+        if (have_bonds) {
+            const uint32_t eb0 = gbond[0], enb = gbond[nrows] - eb0;
+            if (enb <= (uint32_t)RBC && (uint32_t)tid < enb) {
+                e_have = true;
+                const uint32_t b = eb0 + (uint32_t)tid;
+                e_j = A.bj[b];
+                const double* ci = A.bconn + (size_t)b * 15;
+                const double* cj = A.bconn + (size_t)A.brev[b] * 15;
+                const double* len = A.blen + (size_t)b * 5;
+#pragma unroll
+                for (int k = 0; k < 15; k++) {
+                    e_ci[k] = ci[k];
+                    e_cj[k] = cj[k];
+                }
+#pragma unroll
+                for (int k = 0; k < 5; k++) e_len[k] = len[k];
+            }
+        }
+    }
     __syncthreads();  // the mbarriers are initialised
     mbar_wait(&sm.bar[0], 0);
 
@@ -767,7 +793,19 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
             if (tid < nrows)
                 for (uint32_t b = sbptr[tid]; b < sbptr[tid + 1]; b++) sm.brow[b - b0] = (uint8_t)tid;
             __syncthreads();
-            for (uint32_t bl = tid; bl < nbond; bl += RT) {
+            if (e_have) {  // record b0 + tid, loaded early (e_have implies bonds_staged and tid < nbond)
+                const int r = sm.brow[tid];
+                const d3 xi = load3(sx + 3 * r), xj = neighbour_x(e_j);
+                d3 fa, ta;
+                if (A.mp.gamma_d != 0.0)
+                    bridge_fast<true>(A, e_ci, e_cj, e_len, xi, xj, load3(sv + 3 * r), neighbour(e_j, sv, A.v), load3(sw + 3 * r),
+                                      neighbour(e_j, sw, A.w), fa, ta);
+                else
+                    bridge_fast<false>(A, e_ci, e_cj, e_len, xi, xj, zero3(), zero3(), zero3(), zero3(), fa, ta);
+                store3(sm.res + 6 * tid, fa);
+                store3(sm.res + 6 * tid + 3, ta);
+            }
+            for (uint32_t bl = tid + RT; bl < nbond; bl += RT) {
                 const uint32_t b = b0 + bl;
                 const int r = sm.brow[bl];
                 const int j = A.bj[b];
