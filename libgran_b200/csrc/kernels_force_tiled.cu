@@ -739,7 +739,7 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
     // connector sets and the rest lengths are requested NOW, so that their L2 round trips (indices, then connectors)
     // run underneath the bulk copies instead of after them.
     double e_ci[15], e_cj[15], e_len[5];
-    int e_j = 0;
+    int e_j = 0, e_j1 = 0, e_rev1 = -1;  // e_rev1 >= 0: the indices of the thread's second record (b0 + tid + RT) are loaded too
     bool e_have = false;
     if constexpr (kSinter) {
         if (have_bonds) {
@@ -758,6 +758,10 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
                 }
 #pragma unroll
                 for (int k = 0; k < 5; k++) e_len[k] = len[k];
+                if ((uint32_t)tid + (uint32_t)RT < enb) {
+                    e_j1 = A.bj[b + RT];
+                    e_rev1 = A.brev[b + RT];
+                }
             }
         }
     }
@@ -808,9 +812,10 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
             for (uint32_t bl = tid + RT; bl < nbond; bl += RT) {
                 const uint32_t b = b0 + bl;
                 const int r = sm.brow[bl];
-                const int j = A.bj[b];
+                const bool early = e_rev1 >= 0 && bl == (uint32_t)tid + (uint32_t)RT;
+                const int j = early ? e_j1 : A.bj[b];
                 const double* ci = A.bconn + (size_t)b * 15;
-                const double* cj = A.bconn + (size_t)A.brev[b] * 15;
+                const double* cj = A.bconn + (size_t)(early ? e_rev1 : A.brev[b]) * 15;
                 const double* len = A.blen + (size_t)b * 5;
                 const d3 xi = load3(sx + 3 * r), xj = neighbour_x(j);
                 d3 fa, ta;
