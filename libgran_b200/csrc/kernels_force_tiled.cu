@@ -1,7 +1,10 @@
-// kernels_force_tiled.cu -- the production step kernel (sm_100a): pair-parallel force evaluation with an
-// ordered per-particle reduction, optionally fused with the velocity-Verlet update.
+// kernels_force_tiled.cu -- the production step kernels (sm_100a).  Two organisations of the same fused step:
+//   step_tiled_kernel  pair-parallel force evaluation over a shared-memory tile with an ordered per-particle
+//                      reduction; every model mask, both math modes, force-only or fused.  Below.
+//   step_rows_kernel   one thread per bond record + one thread per particle, no tile; relaxed arithmetic, fused only,
+//                      launched for short rows (aggregates).  Further down, with its own header comment.
 //
-// Replaces, in ONE launch per time step,
+// Either one replaces, in ONE launch per time step,
 //   LT/rotational_system/rotational_binary_system_neighbors_omp.h:78-98   (pair loop, ascending j)
 //   LG/granular_system/binary_force_container.h:20-32                     (functor fold per pair)
 //   LG/contact_force/contact_force.h:57-147, LG/hamaker_force/hamaker_force.h:28-43,
