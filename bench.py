@@ -1,7 +1,17 @@
 #!/usr/bin/env python
-"""bench.py -- particle-timesteps/s of the DEM hot path on BASELINE.json config 4.
+"""bench.py -- particle-timesteps/s of the DEM hot path on BASELINE.json's configs (default: config 4, the headline).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--copies C]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config 2|3|4|4c|5|5d]
+
+  --config 4   (default, configs[3], the one `metric` is quoted on) 1 000 050-particle multi-aggregate collision
+  --config 4c  config 4 at the moment of impact: rows of aggregates slid into first contact (Luding contacts > 0)
+  --config 2   (configs[1]) 10 000-particle fractal aggregate, contact + Hamaker; the reference arm runs the
+               UNMODIFIED reference at full size (7.2 GB dense spring table) -- the one same-config comparison
+  --config 3   (configs[2]) 100 000-particle sintered fractal aggregate on a moving facet (CPU leg: oracle port)
+  --config 5   (configs[4]) random packing, volume fraction 0.30, contact + Hamaker, 1.25 M particles PER GPU (weak
+               scaling sweep over --gpus)
+  --config 5d  dense jittered lattice (rows of ~80 neighbors, ~4 contacts per particle), 1.25 M particles per GPU:
+               the pair-tile kernel's regime
 
 Workload (config.workload): ~1M-particle multi-aggregate collision -- 6667 randomly rotated copies of the
 150-particle soot aggregate (resources/aggregate.h), left half moving +x, right half -x; sinter bridges with
@@ -29,7 +39,7 @@ import threading
 import time
 
 import numpy as np
-from ctypes import byref, c_double as C_double, c_int64 as C_int64
+from ctypes import byref, c_double as C_double, c_int64 as C_int64, create_string_buffer
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -37,9 +47,10 @@ sys.path.insert(0, ROOT)
 from libgran_b200 import scenarios as S  # noqa: E402
 
 METRIC = "particle-timesteps/s"
-# dram__bytes_read.sum + dram__bytes_write.sum per launch of the fused step kernel on this workload, from the committed
-# `ncu --set full` captures (profiles/r01d_step_tiled_ncu_raw.csv: 482.0 MB + 301.7 MB; exact mode r01b: 482 + 301 MB)
-TRAFFIC_NCU = {"fast": 806.3e6, "exact": 783.0e6}  # fast: step_rows_kernel, profiles/r01f_step_rows_ncu_raw.csv (491.9 + 314.4 MB)
+# dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, read at bench time from the summary of
+# the most recent `ncu --set full` capture of the same command (scripts/ncu_traffic.py writes profiles/traffic_ncu.json:
+# {"<config>:<math>": {"kernel": ..., "bytes": ..., "source": "<raw csv>"}}); None when no capture of this workload exists
+TRAFFIC_FILE = os.path.join(ROOT, "profiles", "traffic_ncu.json")
 REBUILD_EVERY = int(os.environ.get("LGB200_BENCH_REBUILD_EVERY", "20"))  # 20 = the reference drivers' period; the override is for diagnostics only
 
 
@@ -111,9 +122,53 @@ def numpy_unit_vectors(count: int, seed: int = 99) -> np.ndarray:
     return v / np.linalg.norm(v, axis=1)[:, None]
 
 
-def build_workload(copies: int):
-    scn = S.multi_aggregate_collision(copies)
-    return scn
+def ncu_traffic(config: str, math: str, kernel: str):
+    try:
+        with open(TRAFFIC_FILE) as f:
+            rec = json.load(f).get(f"{config}:{math}")
+        if rec and kernel.startswith(rec["kernel"]):
+            return float(rec["bytes"])
+    except Exception:
+        pass
+    return None
+
+
+# ---- workloads -----------------------------------------------------------------------------------------
+PER_GPU_5 = 1_250_000
+
+
+def build_workload(args, world: int = 1, sample: bool = False):
+    """(scenario, description, move_facets) of --config; `sample` = the bounded CPU-reference sample of the same workload."""
+    c = args.config
+    if c == "2":
+        n = 10_000
+        return S.fractal_aggregate(n), f"cfg2 fractal aggregate, {n} particles, contact+Hamaker", False
+    if c == "3":
+        n = 100_000
+        return (S.sintered_aggregate_on_facet(n),
+                f"cfg3 sintered fractal aggregate on a facet moving +z at 0.5 m/s, {n} particles, sinter+contact+Hamaker+wall contact+wall Hamaker", True)
+    if c in ("4", "4c"):
+        copies = args.sample if sample else args.copies
+        if c == "4":
+            scn = S.multi_aggregate_collision(copies)
+            return scn, f"cfg4 multi-aggregate collision, {scn.cfg.n} particles ({copies} x aggregate.h), sinter+contact+Hamaker", False
+        scn = S.multi_aggregate_in_contact(copies)
+        return scn, (f"cfg4c multi-aggregate collision at impact (rows of aggregates slid into first contact, overlap 0.02 r), "
+                     f"{scn.cfg.n} particles ({copies} x aggregate.h), sinter+contact+Hamaker"), False
+    if c == "5":
+        n = 125_000 if sample else PER_GPU_5 * world
+        scn = S.random_packing(n, volume_fraction=0.30)
+        return scn, f"cfg5 random packing (RSA, volume fraction 0.30), {n} particles, contact+Hamaker", False
+    if c == "5d":
+        n1 = 50 if sample else 108
+        nx = n1 * (1 if sample else world)
+        scn = S.lattice_block(nx, n1, n1, spacing=1.98, jitter=0.02, v_scale=0.05)
+        return scn, f"cfg5d dense jittered lattice {nx}x{n1}x{n1} (spacing 1.98 r), {scn.cfg.n} particles, contact+Hamaker", False
+    raise SystemExit(f"unknown --config {c}")
+
+
+def workload_line(desc: str) -> str:
+    return f"{desc}, r_verlet=5r, rebuild every {REBUILD_EVERY} steps"
 
 
 def effective_warmup(args) -> int:
@@ -144,14 +199,14 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    scn = build_workload(args.copies)
+    scn, desc, moves = build_workload(args, world)
     cfg = scn.cfg
     n = cfg.n
     if world > 1:
-        return run_slab(args, scn, world, rank, local_rank)
+        return run_slab(args, scn, desc, moves, world, rank, local_rank)
 
-    uv = numpy_unit_vectors(n + 1024)
-    mode = 1 if (args.math == "fast" and args.variant in (None, 1)) else 0
+    uv = numpy_unit_vectors(n + 1024) if cfg.model_mask & S.MODEL_SINTER else None
+    mode = 1 if (args.math == "fast" and args.variant in (None, 1, 2)) else 0
     sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)
     stream = torch.cuda.ExternalStream(sysm.stream_handle(), device=torch.device("cuda", local_rank))
 
@@ -160,14 +215,14 @@ def run_ours(args):
         torch.cuda.synchronize()
         with torch.cuda.stream(stream):
             e0.record()
-            sysm.run(cfg.dt, k, REBUILD_EVERY)
+            sysm.run(cfg.dt, k, REBUILD_EVERY, moves)
             e1.record()
         sysm.synchronize()
         torch.cuda.synchronize()
         return e0.elapsed_time(e1)
 
     # ---- device-resident throughput ------------------------------------------------------------
-    sysm.run(cfg.dt, effective_warmup(args), REBUILD_EVERY)
+    sysm.run(cfg.dt, effective_warmup(args), REBUILD_EVERY, moves)
     sysm.synchronize()
     c0 = sysm.counters()
     sampler = ClockSampler(local_rank)
@@ -178,26 +233,26 @@ def run_ours(args):
     value = n * args.steps / (ms * 1e-3)
     launches = c1["launches"] - c0["launches"]
 
-    # ---- roofline of the dominant kernel (pair force), measured live with events ----------------
+    # ---- roofline of the dominant kernel (the step kernel), measured live with events ----------------
     sysm.set_profiling(True)
     prof_steps = min(args.steps, 40)
-    sysm.run(cfg.dt, prof_steps, REBUILD_EVERY)
+    sysm.run(cfg.dt, prof_steps, REBUILD_EVERY, moves)
     force_ms, force_launches = sysm.get_profile()
     sysm.set_profiling(False)
+    kernel = sysm.last_step_kernel()
     cnt = sysm.counters()
     step_bytes, force_bytes = algorithmic_bytes(n, cnt["pairs"], cnt["contacts"], cnt["bonds"])
     peak, peak_src = measured_peaks()
     force_avg_ms = force_ms / max(force_launches, 1)
     # the production launch is the FUSED step kernel (force + Verlet + connector update): it moves the whole B_step;
     # the validation variant's force-only kernel moves force_bytes
-    fused = args.variant in (None, 1)
+    fused = args.variant in (None, 1, 2)
     launch_bytes = step_bytes if fused else force_bytes
     achieved = launch_bytes / (force_avg_ms * 1e-3) / 1e9
-    rows_kernel = fused and mode == 1 and cnt["pairs"] <= 24 * n and os.environ.get("LGB200_ROWS_KERNEL", "1") != "0"
-    kname = ("step_rows_kernel" if rows_kernel else "step_tiled_kernel") + " (fused pair force + Verlet + connectors)"
-    roofline = {"bound": "hbm", "kernel": kname if fused else "pair_force",
+    kname = kernel + (" (fused pair force + Verlet + connectors)" if fused else " (pair force)")
+    roofline = {"bound": "hbm", "kernel": kname,
                 "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                "frac": round(achieved / peak, 4), "traffic": TRAFFIC_NCU.get(args.math if fused else "variant0"), "peak_source": peak_src,
+                "frac": round(achieved / peak, 4), "traffic": ncu_traffic(args.config, args.math, kernel), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(launch_bytes), "avg_launch_ms": round(force_avg_ms, 5),
                 "launches_timed": int(force_launches),
                 "share_of_step": round(force_avg_ms / (ms / args.steps), 3),
@@ -208,8 +263,10 @@ def run_ours(args):
 
     if args.kernel_only:
         if rank == 0:
-            print(json.dumps({"math": args.math, "value": round(value, 1), "ms_per_step": round(ms / args.steps, 5), "roofline": roofline,
-                              "gpu_launches": int(launches), "clocks": clocks, "lib": os.environ.get("LGB200_LIB", "default"), "tag": os.environ.get("LGB200_TAG")}))
+            print(json.dumps({"config": args.config, "math": args.math, "value": round(value, 1), "ms_per_step": round(ms / args.steps, 5),
+                              "particles": n, "pairs": cnt["pairs"], "contacts": cnt["contacts"], "bonds_ordered": cnt["bonds"],
+                              "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
+                              "lib": os.environ.get("LGB200_LIB", "default"), "tag": os.environ.get("LGB200_TAG")}))
         return
 
     # ---- end to end through the host-facing API with host buffers ---------------------------------
@@ -218,6 +275,7 @@ def run_ours(args):
     outs = [torch.empty((n, 3), dtype=torch.float64).pin_memory() for _ in range(4)]
     out_np = [t.numpy() for t in outs]
     e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)  # model tables built once (as a ctor would)
+    facet0 = e2e_sys.facet_vertices(0) if moves else None
     e2e_steps = args.steps
     # untimed priming with dt = 0: sizes the neighbor / scratch buffers for exactly this state and leaves positions,
     # velocities and bridge connectors where the constructor put them (x += v * 0, c += 0)
@@ -225,12 +283,14 @@ def run_ours(args):
     e2e_sys.synchronize()
     torch.cuda.synchronize()
     t0 = time.perf_counter()
-    e2e_sys.set_state(*host_np)  # H2D of x0, v0, theta0, omega0 (re-arms the first-step half kick)
+    e2e_sys.set_state(*host_np)  # H2D of x0, v0, theta0, omega0 (a new trajectory: history springs and rows reset)
     ke = 0.0
     for k in range(e2e_steps):
         if k % REBUILD_EVERY == 0:
             e2e_sys.update_neighbor_list()
         e2e_sys.do_step(cfg.dt)
+        if moves:
+            e2e_sys.facet_update_positions(cfg.dt)
         if (k + 1) % 10 == 0:
             ke = e2e_sys.diagnostics()["ke"]  # D2H of the step's metric (as main.cpp:152-159 dumps energies)
     for name, buf in zip(("x", "v", "omega", "theta"), out_np):
@@ -243,27 +303,31 @@ def run_ours(args):
     e2e = {"value": round(e2e_value, 1), "unit": METRIC, "h2d_bytes_per_step": round(h2d, 1),
            "d2h_bytes_per_step": round(d2h, 1), "steps": e2e_steps, "final_ke": ke,
            "what": "lg_set_state(H2D, pinned) + K x lg_do_step (+ rebuild/20, KE read-back/10) + get x,v,omega,theta (D2H)"}
+    del facet0
     e2e_sys.close()
 
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": METRIC, "n_gpus": world, "steps": args.steps,
         "warmup": effective_warmup(args), "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"cfg4 multi-aggregate collision, {n} particles ({args.copies} x aggregate.h), sinter+contact+Hamaker, "
-                               f"r_verlet=5r, rebuild every {REBUILD_EVERY} steps", "particles": n, "pairs": cnt["pairs"],
-                   "bonds_ordered": cnt["bonds"], "contacts": cnt["contacts"], "l2_policy": "working set (>400 MB) larger than L2",
+        "scaling": "weak" if args.config in ("5", "5d") else "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": workload_line(desc), "config": args.config, "particles": n, "pairs": cnt["pairs"],
+                   "bonds_ordered": cnt["bonds"], "contacts": cnt["contacts"],
+                   "l2_policy": ("working set larger than L2" if step_bytes > 3 * 126e6 else
+                                 f"working set {step_bytes / 1e6:.1f} MB per step is L2-resident by nature of this config (the whole "
+                                 "system is smaller than the 126 MB L2); every byte is rewritten each step"),
                    "kernel_variant": args.variant, "math_mode": "fast (<=1e-10 rel. forces, bit-exact sets)" if mode else "exact (bit-identical to the reference)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
     }
     if rank == 0 and not args.no_cpu_baseline:
-        line["cpu_baseline"] = run_reference_sample(args, steps=args.cpu_steps, warmup=5)
+        line["cpu_baseline"] = run_reference_sample(args, budget_s=args.cpu_seconds, in_gpu_line=True)
     if rank == 0:
         print(json.dumps(line))
 
 
-def run_slab(args, scn, world, rank, local_rank):
-    """N > 1: the same workload slab-decomposed along x, one rank per GPU (libgran_b200/slab.py).  Strong scaling:
-    the particle count is fixed, `value` = all particles * steps / max-over-ranks device time."""
+def run_slab(args, scn, desc, moves, world, rank, local_rank):
+    """N > 1: the same workload slab-decomposed along x, one rank per GPU (libgran_b200/slab.py).  Configs 2-4: strong
+    scaling (the particle count is fixed); configs 5 / 5d: weak scaling (1.25 M particles per GPU).
+    `value` = all particles * steps / max-over-ranks device time."""
     import torch
     import torch.distributed as dist
 
@@ -272,7 +336,7 @@ def run_slab(args, scn, world, rank, local_rank):
     cfg = scn.cfg
     n = cfg.n
     dev = torch.device("cuda", local_rank)
-    uv = numpy_unit_vectors(n + 1024)
+    uv = numpy_unit_vectors(n + 1024) if cfg.model_mask & S.MODEL_SINTER else None
     mode = 1 if args.math == "fast" else 0
     sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode)
     warm = effective_warmup(args)
@@ -326,7 +390,9 @@ def run_slab(args, scn, world, rank, local_rank):
     slow = float(worst[0])
     peak, peak_src = measured_peaks()
     ach = step_bytes_local / (force_avg_ms * 1e-3) / 1e9
-    roofline = {"bound": "hbm", "kernel": ("step_rows_kernel" if mode else "step_tiled_kernel") + " (fused pair force + Verlet + connectors), this rank", "achieved": round(ach, 1),
+    kbuf = create_string_buffer(64)
+    sysm.lib.lg_last_step_kernel(sysm.h, kbuf, 64)
+    roofline = {"bound": "hbm", "kernel": kbuf.value.decode() + " (fused pair force + Verlet + connectors), this rank", "achieved": round(ach, 1),
                 "peak": peak, "unit": "GB/s", "frac": round(ach / peak, 4), "traffic": None, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": int(step_bytes_local), "avg_launch_ms": round(force_avg_ms, 5),
                 "slowest_rank_launch_ms": round(slow, 5), "launches_timed": int(fl.value),
@@ -371,10 +437,10 @@ def run_slab(args, scn, world, rank, local_rank):
     del outs
     line = {
         "metric": METRIC, "value": round(value, 1), "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": warm,
-        "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True,
+        "scaling": "weak" if args.config in ("5", "5d") else "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"cfg4 multi-aggregate collision, {n} particles ({args.copies} x aggregate.h), sinter+contact+Hamaker, "
-                               f"r_verlet=5r, rebuild every {REBUILD_EVERY} steps", "particles": n, "pairs": cnt["pairs"],
+        "config": {"workload": workload_line(desc), "config": args.config, "particles": n, "pairs": cnt["pairs"],
                    "contacts": cnt["contacts"], "math_mode": "fast" if mode else "exact", "l2_policy": "per-rank working set larger than L2 up to 4 GPUs; at 8 GPUs "
                    "(~100 MB/step/rank) the step streams through L2 once per step, no reuse across steps is possible "
                    "because every byte is rewritten each step",
@@ -388,31 +454,81 @@ def run_slab(args, scn, world, rank, local_rank):
     dist.destroy_process_group()
 
 
-def run_reference_sample(args, steps, warmup):
-    """The reference's own OpenMP implementation on a bounded sample of the workload."""
+def host_threads() -> int:
+    """Physical cores of the host (the reference's advice: one OpenMP thread per core, Writerside/topics/Installation.md:22-24)."""
+    try:
+        import psutil
+
+        c = psutil.cpu_count(logical=False)
+        if c:
+            return int(min(c, len(os.sched_getaffinity(0))))
+    except Exception:
+        pass
+    return max(1, len(os.sched_getaffinity(0)))
+
+
+def run_reference_sample(args, budget_s: float, in_gpu_line: bool = False):
+    """The reference's own CPU implementation of the path on the host cores.  kind "reference" = the unmodified reference
+    (oracle/_ref/libref_timing.so, built from the reference's headers with its -O3 -fopenmp flags); kind "port" = the
+    oracle restatement, where the reference's dense N x N tables cannot hold the config.  Timed: at least 200 steps and
+    at least 2 s (whatever --steps says), after a 20-step warm-up, constructor excluded (test/hamaker_neighbor.cpp:119-127
+    times the loop only); the 1-thread figure is taken on a quarter of the steps."""
     os.environ.setdefault("OMP_PROC_BIND", "close")
+    os.environ.setdefault("OMP_WAIT_POLICY", "passive")
     from oracle import bindings as ob
 
-    sample = args.sample
-    scn = build_workload(sample)
+    scn, desc, moves = build_workload(args, 1, sample=True)
     cfg = scn.cfg
-    kind = "reference"
-    if ob.ref_available(timing=True):
-        threads = ob.load_ref(timing=True).ref_max_threads()
-        sysm = ob.RefSystem(cfg, *scn.state, timing=True)
+    use_ref = args.config in ("2", "4", "4c") and ob.ref_available(timing=True)
+    threads = host_threads()
+    if use_ref:
+        kind, lib = "reference", ob.load_ref(timing=True)
+        lib.ref_set_threads(threads)   # explicit: under torchrun OMP_NUM_THREADS defaults to 1
+        make = lambda: ob.RefSystem(cfg, *scn.state, timing=True)
     else:
-        kind = "port"
-        threads = ob.load_oracle().orc_max_threads()
-        sysm = ob.OracleSystem(cfg, *scn.state)
-    sysm.run(cfg.dt, warmup, REBUILD_EVERY)
+        kind, lib = "port", ob.load_oracle()
+        lib.orc_set_threads(threads)
+        make = lambda: ob.OracleSystem(cfg, *scn.state)
+    set_threads = lib.ref_set_threads if use_ref else lib.orc_set_threads
+
+    def loop(sysm, k):
+        if not moves:
+            sysm.run(cfg.dt, k, REBUILD_EVERY)
+            return
+        for s in range(k):  # driver loop with facet.update_positions(dt), test/surface.cpp style
+            if s % REBUILD_EVERY == 0:
+                sysm.update_neighbor_list()
+            sysm.do_step(cfg.dt)
+            sysm.facet_update_positions(cfg.dt)
+
+    sysm = make()
+    loop(sysm, 20)
     t0 = time.perf_counter()
-    sysm.run(cfg.dt, steps, REBUILD_EVERY)
+    loop(sysm, 20)
+    per20 = max(time.perf_counter() - t0, 1e-6)
+    steps = int(max(200, 20 * np.ceil(max(2.0, budget_s) / per20)))
+    steps = int(min(steps, 20 * max(10, np.ceil(4.0 * max(2.0, budget_s) / per20))))
+    t0 = time.perf_counter()
+    loop(sysm, steps)
     dt_s = time.perf_counter() - t0
     val = cfg.n * steps / dt_s
+    set_threads(1)
+    s1 = max(20, (steps // 4) // 20 * 20)
+    t0 = time.perf_counter()
+    loop(sysm, s1)
+    val1 = cfg.n * s1 / (time.perf_counter() - t0)
+    set_threads(threads)
     sysm.close()
-    return {"value": round(val, 1), "unit": METRIC, "cores": int(threads), "kind": kind,
-            "sample": f"{sample} of {args.copies} aggregates ({cfg.n} particles), {steps} steps after {warmup} warm-up, "
-                      f"constructor excluded; full size infeasible (232 B * N^2 dense tables)",
+    full = {"2": "the full config (10 000 particles, 7.2 GB dense spring table)",
+            "3": "the full config (100 000 particles; the unmodified reference would need 2.3 TB of dense tables -> oracle port)",
+            "4": f"{args.sample} of {args.copies} aggregates; the full size needs 232 B * N^2 = 232 TB of dense tables",
+            "4c": f"{args.sample} of {args.copies} aggregates; the full size needs 232 B * N^2 = 232 TB of dense tables",
+            "5": "a 125 000-particle packing at the same volume fraction (oracle port; the reference's 72 B * N^2 table would need 1.1 TB)",
+            "5d": "a 50^3 block of the same lattice (oracle port)"}[args.config]
+    return {"value": round(val, 1), "unit": METRIC, "cores": int(threads), "kind": kind, "one_thread_value": round(val1, 1),
+            "particles": int(cfg.n), "steps": int(steps), "same_config": args.config in ("2", "3"),
+            "march": "x86-64-v3 (prebuilt where /root/reference exists; the GPU box has no reference checkout to rebuild with -march=native)",
+            "sample": f"{workload_line(desc)} -- {full}; {steps} steps after 40 warm-up steps, constructor excluded",
             "seconds": round(dt_s, 3)}
 
 
@@ -420,16 +536,15 @@ def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    scn_n = 150 * args.copies
-    base = run_reference_sample(args, steps=args.steps, warmup=max(args.warmup, 1))
+    base = run_reference_sample(args, budget_s=max(2.0, args.cpu_seconds))
+    scn_desc = base["sample"]
     line = {
         "impl": "reference", "metric": METRIC, "value": base["value"], "unit": METRIC,
-        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": args.steps, "warmup": max(args.warmup, 1),
-        "ms_per_step": round(base["seconds"] / args.steps * 1e3, 4), "higher_is_better": True, "scaling": "strong",
+        "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": base["steps"], "warmup": 40,
+        "steps_requested": args.steps, "ms_per_step": round(base["seconds"] / base["steps"] * 1e3, 4), "higher_is_better": True,
+        "scaling": "weak" if args.config in ("5", "5d") else "strong",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"cfg4 multi-aggregate collision, {scn_n} particles ({args.copies} x aggregate.h), "
-                               f"sinter+contact+Hamaker, r_verlet=5r, rebuild every {REBUILD_EVERY} steps",
-                   "particles": scn_n},
+        "config": {"workload": scn_desc, "config": args.config, "particles": base["particles"], "same_config_as_gpu_arm": base["same_config"]},
         "cpu_baseline": base,
         "e2e": {"value": base["value"], "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -442,13 +557,14 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--copies", type=int, default=6667, help="aggregates in the workload (6667 -> 1 000 050 particles)")
+    ap.add_argument("--config", default="4", choices=["2", "3", "4", "4c", "5", "5d"], help="BASELINE.json config (see the module docstring)")
+    ap.add_argument("--copies", type=int, default=6667, help="configs 4 / 4c: aggregates in the workload (6667 -> 1 000 050 particles)")
     ap.add_argument("--sample", type=int, default=34, help="aggregates in the CPU-reference sample (34 -> 5100 particles)")
     ap.add_argument("--variant", type=int, default=None, help="force kernel variant (0 simple, 1 tiled)")
     ap.add_argument("--math", default="fast", choices=["fast", "exact"],
                     help="arithmetic of the step kernel: fast = LG_MATH_FAST (forces within 1e-10 of the reference, sets "
                          "bit-exact; tests/test_gpu_fast_math.py), exact = bit-identical to the reference")
-    ap.add_argument("--cpu-steps", type=int, default=10000, help="time steps of the CPU-reference sample (about 10 s of CPU work)")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="CPU work of the reference sample (seconds; at least 200 steps and 2 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--kernel-only", action="store_true", help="tuning runs: device-resident throughput + roofline only")
     args = ap.parse_args()

@@ -73,7 +73,9 @@ int lg_abi_version(void);
  * (LT/rotational_system/rotational_system.h:52-66).  Copies host -> device; resets a, alpha to zero
  * (:80,83-86) and re-arms the first-step half kick (LT/rotational_integrator/
  * rotational_velocity_verlet_half.h:45-60). `n_check` must equal the n given to lg_create, else
- * LG_ESIZE (rotational_system.h:69-70). */
+ * LG_ESIZE (rotational_system.h:69-70).  A second call starts a new trajectory exactly as constructing a new
+ * reference system would: contact and wall history springs are cleared, the neighbor list is empty again until
+ * lg_update_neighbor_list, the step counter of lg_run restarts; installed models and bond tables stay. */
 int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v, const double* theta,
                  const double* omega);
 
@@ -152,7 +154,9 @@ int lg_facet_get_vertices(lg_system* s, int facet_id, double out_9[9]);
 /* Selects the neighbor-list pair loop (LT/rotational_system/rotational_binary_system_neighbors_omp.h)
  * with Verlet radius r_verlet; without this call the system is the all-pairs loop
  * (LT/rotational_system/rotational_binary_system_omp.h:69-90).  As in the reference the list is
- * empty until the first lg_update_neighbor_list (:66). */
+ * empty until the first lg_update_neighbor_list (:66).  r_verlet must be >= 2 * r_part (LG_EINVAL otherwise):
+ * history springs of a pair are dropped when it leaves the list, which equals the reference's reset on a visited
+ * non-overlapping evaluation (contact_force.h:68-71) only while every overlapping pair is listed. */
 int lg_enable_neighbor_list(lg_system* s, double r_verlet);
 
 /* update_neighbor_list() (rotational_binary_system_neighbors_omp.h:102-116): rows
@@ -210,6 +214,18 @@ int lg_diagnostics(lg_system* s, double out_9[9]);
  *       contact run the exact Luding law so their history springs evolve as in the reference. */
 enum { LG_MATH_EXACT = 0, LG_MATH_FAST = 1 };
 int lg_set_math_mode(lg_system* s, int mode);
+
+/* ---- initial-condition tooling (host only, no device needed) ------------------------
+ * What a libgran driver does before the time loop (main.cpp:56-93, test/hamaker_3.cpp:60-87), for the synthetic
+ * inputs BASELINE.json's configs name.  Deterministic in (seed, n): std::mt19937_64 as in test/sintered.cpp:30-39. */
+
+/* Particle-cluster sticking: particle k sits at exactly 2 r from a uniformly chosen earlier particle, in a uniform
+ * random direction, rejected if within 2 r (1 + 1e-9) of any other particle.  x_out_3n: 3 * n doubles. */
+int lg_gen_fractal_aggregate(int64_t n, uint64_t seed, double r_part, double* x_out_3n);
+/* Random sequential addition of spheres to `volume_fraction` (<= 0.36) in a box aspect : 1 : 1 with its corner at the
+ * origin; min_gap_factor in (0.5, 1] scales the excluded diameter (1 = no overlaps).  box_out (nullable) = edges. */
+int lg_gen_random_packing(int64_t n, double volume_fraction, double aspect, double min_gap_factor, uint64_t seed,
+                          double r_part, double* x_out_3n, double box_out[3]);
 
 /* ---- slab decomposition (no reference counterpart -- the reference is single-process) ----
  * One lg_system per rank holds that rank's owned particles and its ghosts, ordered by global particle id.  The
@@ -277,9 +293,14 @@ int lg_get_stream(lg_system* s, void** stream);
 int lg_set_profiling(lg_system* s, int enabled);
 int lg_get_profile(lg_system* s, double* force_ms_total, int64_t* force_launches);
 
-/* Selects the force-kernel organisation: 0 = one thread per particle (simple, validation),
- * 1 = tiled pair-parallel kernel (default).  Both give bit-identical results. */
+/* Selects the force-kernel organisation: 0 = one thread per particle, unfused (validation; the reference's schedule
+ * literally), 1 = production (default): the fused step kernels, pair-tile kernel or -- in LG_MATH_FAST with short
+ * rows -- the row kernel, 2 = as 1 but the row kernel whatever the row length (LG_MATH_FAST only; coverage tests).
+ * Variants 0 and 1 give bit-identical results in LG_MATH_EXACT. */
 int lg_set_kernel_variant(lg_system* s, int variant);
+/* Name of the kernel the most recent force evaluation launched ("step_rows_kernel", "step_tiled_kernel",
+ * "force_simple_kernel"; "" before the first), copied into out[cap]. */
+int lg_last_step_kernel(lg_system* s, char* out, int cap);
 
 #ifdef __cplusplus
 }

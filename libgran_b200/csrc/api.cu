@@ -32,6 +32,12 @@ int fail(int code, const std::string& msg) {
     return code;
 }
 
+}  // namespace
+namespace lg {
+int fail_message(int code, const char* msg) { return fail(code, msg); }  // for the other translation units
+}
+namespace {
+
 #define LG_CUDA(expr)                                                                                   \
     do {                                                                                                \
         cudaError_t e_ = (expr);                                                                        \
@@ -173,6 +179,7 @@ struct lg_system {
 
     int64_t steps = 0, rebuilds = 0;
     int64_t launches0 = 0;
+    const char* last_kernel = "";  // lg_last_step_kernel
 
     // optional per-kernel timing (lg_set_profiling)
     bool profiling = false;
@@ -180,6 +187,20 @@ struct lg_system {
     size_t prof_used = 0;
     double prof_ms = 0.0;
     int64_t prof_count = 0;
+
+    // Releases what the DevBuf members do not own; runs on every exit path of lg_create as well (error returns
+    // destroy the half-built system through its unique_ptr).  The caller makes `device` current first.
+    ~lg_system() {
+        if (stream) {
+            cudaStreamSynchronize(stream);
+            cudaStreamDestroy(stream);
+        }
+        if (h_pinned) cudaFreeHost(h_pinned);
+        for (auto& ev : prof_events) {
+            cudaEventDestroy(ev.first);
+            cudaEventDestroy(ev.second);
+        }
+    }
 };
 
 namespace {
@@ -302,7 +323,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     {   // short rows (aggregates) -> row kernel; long rows (packings) -> tile kernel.  LGB200_ROWS_KERNEL=0 disables it.
         static const int rows_enabled = [] { const char* e = std::getenv("LGB200_ROWS_KERNEL"); return e ? std::atoi(e) : 1; }();
         const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
-        A.use_rows = (rows_enabled && s->math_mode && k_mean <= 24.0) ? 1 : 0;
+        A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= 24.0))) ? 1 : 0;  // variant 2: rows kernel whatever the row length
     }
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia);
     const bool fused = fused_dt >= 0.0;
@@ -324,6 +345,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         launch_step_tiled(A, s->mask, true, s->stream);
     else
         launch_force(A, s->mask, s->variant, s->stream);
+    s->last_kernel = s->variant == 0 ? "force_simple_kernel" : (A.fast && A.use_rows) ? "step_rows_kernel" : "step_tiled_kernel";
     if (s->profiling) LG_CUDA(cudaEventRecord(s->prof_events[s->prof_used++].second, s->stream));
     LG_CUDA(cudaGetLastError());
     if (fused) {
@@ -404,10 +426,10 @@ int rebuild(lg_system* s) {
     // The pending evaluation belongs to the OLD rows (it closed the previous do_step).  In the steady state of the
     // fused variant it stays pending: the new rows are built next to the old ones (they depend on x only, which
     // the evaluation does not change) and are installed by evaluate() once the evaluation has run.
-    const bool defer = s->pending && s->variant == 1 && s->rebuilds > 0 && s->n_pairs > 0;
+    const bool defer = s->pending && s->variant >= 1 && s->rebuilds > 0 && s->n_pairs > 0;
     if (!defer) LG_TRY(flush(s));
     const int n = (int)s->n;
-    if (s->variant == 1) {  // the second set of row buffers is allocated up front: no cudaMalloc in the steady state
+    if (s->variant >= 1) {  // the second set of row buffers is allocated up front: no cudaMalloc in the steady state
         LG_CUDA(s->row_ptr_new.reserve((size_t)n + 1));
         if (s->cols.cap > s->cols_new.cap) {
             LG_CUDA(s->cols_new.reserve(s->cols.cap - 16));
@@ -710,10 +732,10 @@ int lg_create(int64_t n, double r_part, double mass, double inertia, int device,
     } else if (device >= count) {
         return fail(LG_ENODEVICE, "device ordinal out of range");
     }
+    DeviceGuard guard(device);  // declared first: still in force when an error return destroys the half-built system
     std::unique_ptr<lg_system> s(new (std::nothrow) lg_system());
     if (!s) return fail(LG_ENOMEM, "host allocation failed");
     s->device = device;
-    DeviceGuard guard(device);
     s->n = n;
     s->mp.r = r_part;
     s->mp.mass = mass;
@@ -758,16 +780,7 @@ int lg_destroy(lg_system* s) {
     if (s == nullptr) return LG_OK;
     {
         DeviceGuard guard(s->device);
-        if (s->stream) {
-            cudaStreamSynchronize(s->stream);
-            cudaStreamDestroy(s->stream);
-        }
-        if (s->h_pinned) cudaFreeHost(s->h_pinned);
-        for (auto& ev : s->prof_events) {
-            cudaEventDestroy(ev.first);
-            cudaEventDestroy(ev.second);
-        }
-        delete s;  // DevBuf destructors free device memory while the device is current
+        delete s;  // ~lg_system releases the stream, pinned scratch and events; DevBuf destructors free device memory
     }
     return LG_OK;
 }
@@ -788,9 +801,25 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     s->state_set = true;
     s->kicked = false;
     s->half_kicked = false;
-    if (s->rows_staged) LG_TRY(install_staged_rows(s));  // the discarded evaluation would have installed them
-    s->grid_valid = false;  // new positions: the next rebuild measures the bounding box again
     s->pending = false;
+    s->rows_staged = false;
+    s->grid_valid = false;  // new positions: the next rebuild measures the bounding box again
+    // A new state is a new trajectory, i.e. what the reference gets from constructing a new system: no history springs
+    // (contact_force.h:53 zero-initialised), an empty neighbor list until update_neighbor_list is called
+    // (rotational_binary_system_neighbors_omp.h:66), step count 0 (lg_run's rebuild period restarts).  Bond tables stay.
+    s->steps = 0;
+    if (s->slots_ready) LG_CUDA(cudaMemsetAsync(s->sgid.p, 0xff, (size_t)s->n * s->S * sizeof(int32_t), s->stream));
+    for (size_t f = 0; f < s->facets.size(); f++) {
+        LG_CUDA(cudaMemsetAsync(s->wspr[f]->p, 0, (size_t)s->n * 9 * sizeof(double), s->stream));
+        LG_CUDA(cudaMemsetAsync(s->wact[f]->p, 0, (size_t)s->n, s->stream));
+    }
+    if (s->use_nl) {
+        s->n_pairs = 0;
+        s->rebuilds = 0;
+        LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, ((size_t)s->n + 1) * sizeof(uint32_t), s->stream));
+    } else if (s->allpairs_built) {
+        LG_TRY(retag(s));
+    }
     return LG_OK;
 }
 
@@ -989,6 +1018,9 @@ int lg_facet_get_vertices(lg_system* s, int id, double out[9]) {
 int lg_enable_neighbor_list(lg_system* s, double r_verlet) {
     LG_ENTER(s);
     if (!(r_verlet > 0.0)) return fail(LG_EINVAL, "r_verlet must be positive");
+    // Contact springs are dropped when a pair leaves the list, which equals the reference's reset on a visited
+    // non-overlapping evaluation only if every overlapping pair (distance < 2 r) is inside the list.
+    if (r_verlet < 2.0 * s->mp.r) return fail(LG_EINVAL, "r_verlet must be at least 2 * r_part (contact range)");
     s->use_nl = true;
     s->r_verlet = r_verlet;
     s->allpairs_built = false;
@@ -1494,17 +1526,24 @@ int lg_get_profile(lg_system* s, double* ms, int64_t* count) {
 int lg_set_math_mode(lg_system* s, int mode) {
     LG_ENTER(s);
     if (mode != 0 && mode != 1) return fail(LG_EINVAL, "math mode must be LG_MATH_EXACT (0) or LG_MATH_FAST (1)");
-    if (mode == 1 && s->variant != 1) return fail(LG_EINVAL, "the relaxed math mode exists for the tiled kernel variant only");
+    if (mode == 1 && s->variant < 1) return fail(LG_EINVAL, "the relaxed math mode exists for the production kernel variants (1, 2) only");
     LG_TRY(flush(s));
     s->math_mode = mode;
     return LG_OK;
 }
 
+int lg_last_step_kernel(lg_system* s, char* out, int cap) {
+    LG_ENTER(s);
+    if (!out || cap <= 0) return fail(LG_EINVAL, "null output");
+    std::snprintf(out, (size_t)cap, "%s", s->last_kernel);
+    return LG_OK;
+}
+
 int lg_set_kernel_variant(lg_system* s, int variant) {
     LG_ENTER(s);
-    if (variant != 0 && variant != 1) return fail(LG_EINVAL, "variant must be 0 or 1");
+    if (variant < 0 || variant > 2) return fail(LG_EINVAL, "variant must be 0 (validation), 1 (production) or 2 (row kernel forced)");
     LG_TRY(flush(s));
-    if (variant != 1 && s->math_mode != 0) return fail(LG_EINVAL, "the validation variant is bit-exact only; reset the math mode first");
+    if (variant == 0 && s->math_mode != 0) return fail(LG_EINVAL, "the validation variant is bit-exact only; reset the math mode first");
     s->variant = variant;
     return LG_OK;
 }

@@ -168,7 +168,7 @@ static void launch_simple(const ForceArgs& args, cudaStream_t st) {
 
 void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st) {
     if (args.n <= 0) return;
-    if (variant == 1) {
+    if (variant >= 1) {
         launch_step_tiled(args, mask, false, st);
         return;
     }

@@ -1,8 +1,8 @@
 // kernels_force_tiled.cu -- the production step kernels (sm_100a).  Two organisations of the same fused step:
 //   step_tiled_kernel  pair-parallel force evaluation over a shared-memory tile with an ordered per-particle
 //                      reduction; every model mask, both math modes, force-only or fused.  Below.
-//   step_rows_kernel   one thread per bond record + one thread per particle, no tile; relaxed arithmetic, fused only,
-//                      launched for short rows (aggregates).  Further down, with its own header comment.
+//   step_rows_kernel   one thread per bond record + one thread per particle, no tile; relaxed arithmetic, force-only or
+//                      fused, launched for short rows (aggregates).  Further down, with its own header comment.
 //
 // Either one replaces, in ONE launch per time step,
 //   LT/rotational_system/rotational_binary_system_neighbors_omp.h:78-98   (pair loop, ascending j)
@@ -578,9 +578,12 @@ __global__ void __launch_bounds__(TB, FAST ? LG_MINB : LG_MINB_EXACT) step_tiled
 //           Hamaker per pair, the bonded value looked up, Luding contact (rare for aggregates) evaluated in place
 //   pass 3  integrate, coalesced stores through the staged windows, connector update
 // There is no pair tile, no row map, no ballot compaction and no ordered shared-memory reduction: ~2.4x fewer
-// instructions per particle than the tile kernel (profiles/README.md r01f).  The accumulation order is still
-// ascending j with the pair value formed as (sinter | contact) + hamaker, i.e. the reference's order; only the
-// arithmetic inside the laws is the relaxed one.  Rows of a dense packing (~80 neighbors, several contacts per
+// instructions per particle than the tile kernel (profiles/README.md r01f).  Accumulation order: ascending j within
+// the pairs the hot loop evaluates, then ascending j within the pairs it only marked (contacts, rounding band,
+// unstaged bridges; rows_slow_pairs) -- a fixed order (deterministic), but not the reference's single ascending-j sweep
+// whenever a marked pair exists; the pair value is formed as (sinter | contact) + hamaker as in the reference.  The
+// arithmetic inside the laws is the relaxed one.  MODE_FORCE writes a, alpha and stops (lg_get_field(LG_A), first-step
+// evaluations); MODE_FUSED integrates.  Rows of a dense packing (~80 neighbors, several contacts per
 // particle) would serialise 80 iterations per thread and diverge on the contact law, so the host launches this kernel
 // only when the mean row length is small (launch_step_tiled: rows_kernel_suits).
 #ifndef LG_ROWS_TB
@@ -690,7 +693,7 @@ __device__ __noinline__ void rows_slow_pairs(const ForceArgs& A, const double* s
     store3(out6 + 3, acc_al);
 }
 
-template <int MASK, bool FACETS>
+template <int MASK, int MODE, bool FACETS>
 __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __grid_constant__ ForceArgs A) {
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
@@ -891,14 +894,33 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
             acc_a += u.a;
             acc_al += u.alpha;
         }
-        const double dt = A.dt;
-        vn = vi + acc_a * dt;   // increment_v(n, a * dt)
-        dxv = vn * dt;          // increment_x(n, v * dt), v already updated
-        xn = xi + dxv;
-        wn = wi + acc_al * dt;  // increment_omega
-        dth = wn * dt;          // increment_theta, omega already updated
+        if constexpr (MODE == MODE_FORCE) {  // force only: a, alpha leave through the (now free) v / omega windows
+            vn = acc_a;
+            wn = acc_al;
+        } else {
+            const double dt = A.dt;
+            vn = vi + acc_a * dt;   // increment_v(n, a * dt)
+            dxv = vn * dt;          // increment_x(n, v * dt), v already updated
+            xn = xi + dxv;
+            wn = wi + acc_al * dt;  // increment_omega
+            dth = wn * dt;          // increment_theta, omega already updated
+        }
     }
     __syncthreads();  // every read of the staged state and of the pass-1 results is done
+
+    if constexpr (MODE == MODE_FORCE) {
+        if (tid < nrows) {
+            store3(sv + 3 * tid, vn);
+            store3(sw + 3 * tid, wn);
+        }
+        __syncthreads();
+        for (int idx = tid; idx < 3 * nrows; idx += RT) {
+            const size_t gidx = 3 * (size_t)i0 + idx;
+            A.a[gidx] = sv[idx];
+            A.al[gidx] = sw[idx];
+        }
+        return;
+    }
 
     // ---- pass 3: outputs through the windows (coalesced stores), connector update -----------------------------
     if (tid < nrows) {
@@ -935,30 +957,31 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
     }
 }
 
-template <int MASK, bool FACETS>
+template <int MASK, int MODE, bool FACETS>
 void launch_rows_one(const ForceArgs& args, cudaStream_t st) {
     static bool configured = false;  // per instantiation
     if (!configured) {
-        cudaFuncSetAttribute(step_rows_kernel<MASK, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowsSmem));
+        cudaFuncSetAttribute(step_rows_kernel<MASK, MODE, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(RowsSmem));
         configured = true;
     }
-    step_rows_kernel<MASK, FACETS><<<(args.n + RT - 1) / RT, RT, sizeof(RowsSmem), st>>>(args);
+    step_rows_kernel<MASK, MODE, FACETS><<<(args.n + RT - 1) / RT, RT, sizeof(RowsSmem), st>>>(args);
     g_launch_count++;
 }
 
-template <int MASK>
+template <int MASK, int MODE>
 void launch_rows_facets(const ForceArgs& args, cudaStream_t st) {
-    if (args.n_facets > 0) launch_rows_one<MASK, true>(args, st); else launch_rows_one<MASK, false>(args, st);
+    if (args.n_facets > 0) launch_rows_one<MASK, MODE, true>(args, st); else launch_rows_one<MASK, MODE, false>(args, st);
 }
 
+template <int MODE>
 void launch_rows(const ForceArgs& args, int mask, cudaStream_t st) {
     switch (mask & (MODEL_CONTACT | MODEL_HAMAKER | MODEL_SINTER)) {
-        case MODEL_CONTACT: launch_rows_facets<MODEL_CONTACT>(args, st); break;
-        case MODEL_CONTACT | MODEL_HAMAKER: launch_rows_facets<MODEL_CONTACT | MODEL_HAMAKER>(args, st); break;
-        case MODEL_SINTER: launch_rows_facets<MODEL_SINTER>(args, st); break;
-        case MODEL_SINTER | MODEL_HAMAKER: launch_rows_facets<MODEL_SINTER | MODEL_HAMAKER>(args, st); break;
-        case MODEL_HAMAKER: launch_rows_facets<MODEL_HAMAKER>(args, st); break;
-        default: launch_rows_facets<0>(args, st); break;
+        case MODEL_CONTACT: launch_rows_facets<MODEL_CONTACT, MODE>(args, st); break;
+        case MODEL_CONTACT | MODEL_HAMAKER: launch_rows_facets<MODEL_CONTACT | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_SINTER: launch_rows_facets<MODEL_SINTER, MODE>(args, st); break;
+        case MODEL_SINTER | MODEL_HAMAKER: launch_rows_facets<MODEL_SINTER | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_HAMAKER: launch_rows_facets<MODEL_HAMAKER, MODE>(args, st); break;
+        default: launch_rows_facets<0, MODE>(args, st); break;
     }
 }
 
@@ -1006,9 +1029,10 @@ int tiled_tile_pairs() { return TILE; }
 // fused == true : additionally integrates into x_next, v_next, w_next, th, bconn_next  [MODE_FUSED]
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {
     if (args.n <= 0) return;
-    if (fused && args.fast && args.use_rows)
-        launch_rows(args, mask, st);
-    else if (fused)
+    if (args.fast && args.use_rows) {  // force-only and fused launches of the SAME kernel: what lg_get_field(LG_A) returns in
+                                        // fast mode is what the benched kernel computes
+        if (fused) launch_rows<MODE_FUSED>(args, mask, st); else launch_rows<MODE_FORCE>(args, mask, st);
+    } else if (fused)
         launch_mode<MODE_FUSED>(args, mask, st);
     else
         launch_mode<MODE_FORCE>(args, mask, st);

@@ -173,63 +173,23 @@ def aggregate(models: int = MODEL_SINTER | MODEL_HAMAKER, neighbor_list: bool = 
 # ---------------------------------------------------------------------------------------------
 # synthetic generators for the larger BASELINE configs
 # ---------------------------------------------------------------------------------------------
-class _HashGrid:
-    """Uniform hash grid for the rejection tests of the generators below (host-side set-up only)."""
+def _native():
+    """The C-ABI library's host-side generators (libgran_b200/csrc/generators.cu); they need no GPU."""
+    from .system import load_library
 
-    def __init__(self, cell: float):
-        self.cell = cell
-        self.cells = {}
-
-    def _key(self, p):
-        return (int(math.floor(p[0] / self.cell)), int(math.floor(p[1] / self.cell)), int(math.floor(p[2] / self.cell)))
-
-    def add(self, idx: int, p):
-        self.cells.setdefault(self._key(p), []).append(idx)
-
-    def near(self, p):
-        kx, ky, kz = self._key(p)
-        cells = self.cells
-        for dx in (-1, 0, 1):
-            for dy in (-1, 0, 1):
-                for dz in (-1, 0, 1):
-                    lst = cells.get((kx + dx, ky + dy, kz + dz))
-                    if lst:
-                        yield from lst
+    return load_library()
 
 
 def fractal_aggregate_coordinates(n: int, seed: int = 12345, r: float = R_PART) -> np.ndarray:
     """Deterministic particle-cluster sticking (configs 2 and 3): each new particle is placed at exactly
     2r from a uniformly chosen existing particle in a uniform random direction and rejected if it comes
-    within 2r(1 + 1e-9) of any other particle."""
-    rng = np.random.Generator(np.random.MT19937(seed))
+    within 2r(1 + 1e-9) of any other particle (lg_gen_fractal_aggregate)."""
+    import ctypes as C
+
     pts = np.zeros((n, 3), dtype=np.float64)
-    grid = _HashGrid(2.0 * r * 1.001)
-    grid.add(0, pts[0])
-    count = 1
-    lim2 = (2.0 * r * (1.0 + 1e-9)) ** 2
-    while count < n:
-        # draw in blocks to keep the Python overhead tolerable
-        parents = rng.integers(0, count, size=256)
-        dirs = rng.normal(size=(256, 3))
-        dirs /= np.linalg.norm(dirs, axis=1)[:, None]
-        for parent, d in zip(parents, dirs):
-            if parent >= count:
-                continue
-            cand = pts[parent] + 2.0 * r * d
-            ok = True
-            for j in grid.near(cand):
-                if j == parent:
-                    continue
-                dd = pts[j] - cand
-                if dd[0] * dd[0] + dd[1] * dd[1] + dd[2] * dd[2] < lim2:
-                    ok = False
-                    break
-            if ok:
-                pts[count] = cand
-                grid.add(count, cand)
-                count += 1
-                if count >= n:
-                    break
+    rc = _native().lg_gen_fractal_aggregate(int(n), int(seed), float(r), pts.ctypes.data_as(C.POINTER(C.c_double)))
+    if rc != 0:
+        raise RuntimeError(_native().lg_last_error().decode(errors="replace"))
     return pts
 
 
@@ -308,70 +268,52 @@ def multi_aggregate_collision(n_copies: int = 6667, models: int = MODEL_SINTER |
     return Scenario(f"multi_aggregate_{n}", cfg, np.ascontiguousarray(x0), v0, _zeros(n), _zeros(n))
 
 
+def multi_aggregate_in_contact(n_copies: int = 6667, overlap: float = 0.02, models: int = MODEL_SINTER | MODEL_HAMAKER,
+                               seed: int = 2, speed: float = 0.5) -> Scenario:
+    """Config 4 at the moment of impact: the same rotated copies of aggregate.h on the same grid, but every aggregate is
+    slid along -x until it first touches its -x neighbour with an overlap of `overlap` * r (exact first-contact
+    distance of the two rigid particle sets), so that whole rows of aggregates are in Luding contact and aggregates of
+    neighbouring grid rows come within the Verlet radius.  Velocities as config 4 (left half +x, right half -x)."""
+    base_scn = multi_aggregate_collision(n_copies, models=models, seed=seed, speed=speed)
+    x = base_scn.x0.reshape(n_copies, -1, 3).copy()
+    m = x.shape[1]
+    ny = nz = max(1, int(round((n_copies / 2.0) ** (1.0 / 3.0))))
+    d_touch = (2.0 - overlap) * R_PART
+    shift = np.zeros(n_copies)
+    # aggregate c sits at grid (ix, iy, iz) with c = (ix * ny + iy) * nz + iz: its -x neighbour is c - ny * nz
+    stride = ny * nz
+    for c in range(stride, n_copies):
+        a = x[c - stride] - np.array([shift[c - stride], 0.0, 0.0])   # neighbour, already slid
+        b = x[c]
+        dy = b[:, None, 1] - a[None, :, 1]
+        dz = b[:, None, 2] - a[None, :, 2]
+        lat2 = dy * dy + dz * dz
+        hit = lat2 < d_touch * d_touch
+        if not hit.any():
+            shift[c] = shift[c - stride]
+            continue
+        dx = b[:, None, 0] - a[None, :, 0]
+        slide = np.where(hit, dx - np.sqrt(np.where(hit, d_touch * d_touch - lat2, 0.0)), np.inf)
+        shift[c] = slide.min()
+    x[:, :, 0] -= shift[:, None]
+    x0 = np.ascontiguousarray(x.reshape(-1, 3))
+    return Scenario(f"multi_aggregate_in_contact_{len(x0)}", base_scn.cfg, x0, base_scn.v0, base_scn.theta0, base_scn.omega0)
+
+
 def random_packing(n: int = 1_250_000, volume_fraction: float = 0.30, models: int = MODEL_CONTACT | MODEL_HAMAKER,
-                   seed: int = 3, aspect: float = 8.0, v_scale: float = 0.05) -> Scenario:
+                   seed: int = 3, aspect: float = 8.0, v_scale: float = 0.05, min_gap_factor: float = 1.0) -> Scenario:
     """BASELINE config 5: random sequential addition of non-overlapping spheres to the given volume
-    fraction in a box elongated in x (aspect:1:1), small random velocities."""
-    r = R_PART
-    v_sphere = 4.0 / 3.0 * math.pi * r ** 3
-    vol = n * v_sphere / volume_fraction
-    ly = lz = (vol / aspect) ** (1.0 / 3.0)
-    lx = aspect * ly
-    box = np.array([lx, ly, lz])
-    rng = np.random.Generator(np.random.MT19937(seed))
-    cell = 2.0 * r * 1.0001
-    dims = np.maximum(1, np.floor(box / cell).astype(np.int64))
-    csz = box / dims
+    fraction in a box elongated in x (aspect:1:1), small random velocities (lg_gen_random_packing)."""
+    import ctypes as C
+
     pts = np.empty((n, 3), dtype=np.float64)
-    count = 0
-    lim2 = (2.0 * r) ** 2
-    # vectorised RSA: propose batches, reject against accepted points via a dense cell table
-    # (at most one centre fits in a cell of edge < 2r/sqrt(3); here cells hold a short list instead)
-    cap = 8
-    table = -np.ones((int(dims[0]), int(dims[1]), int(dims[2]), cap), dtype=np.int64)
-    fill = np.zeros((int(dims[0]), int(dims[1]), int(dims[2])), dtype=np.int64)
-    offs = np.array([(a, b, c) for a in (-1, 0, 1) for b in (-1, 0, 1) for c in (-1, 0, 1)], dtype=np.int64)
-    while count < n:
-        m = min(max(4096, (n - count) // 2), 1 << 18)
-        cand = rng.uniform(0.0, 1.0, size=(m, 3)) * box
-        cidx = np.minimum((cand / csz).astype(np.int64), dims - 1)
-        ok = np.ones(m, dtype=bool)
-        # reject against already accepted particles
-        for o in offs:
-            nb = cidx + o
-            valid = np.all((nb >= 0) & (nb < dims), axis=1)
-            nbc = np.where(valid[:, None], nb, 0)
-            ids = table[nbc[:, 0], nbc[:, 1], nbc[:, 2]]  # (m, cap)
-            has = (ids >= 0) & valid[:, None]
-            d = pts[np.where(has, ids, 0)] - cand[:, None, :]
-            d2 = np.einsum("mcj,mcj->mc", d, d)
-            ok &= ~np.any(has & (d2 < lim2), axis=1)
-        # reject conflicts inside the batch: process survivors sequentially (few per cell)
-        surv = np.nonzero(ok)[0]
-        for s in surv:
-            c = cidx[s]
-            p = cand[s]
-            good = True
-            for o in offs:
-                nb = c + o
-                if np.any(nb < 0) or np.any(nb >= dims):
-                    continue
-                k = fill[nb[0], nb[1], nb[2]]
-                for t in range(k):
-                    q = pts[table[nb[0], nb[1], nb[2], t]]
-                    dd = q - p
-                    if dd[0] * dd[0] + dd[1] * dd[1] + dd[2] * dd[2] < lim2:
-                        good = False
-                        break
-                if not good:
-                    break
-            if good and fill[c[0], c[1], c[2]] < cap:
-                pts[count] = p
-                table[c[0], c[1], c[2], fill[c[0], c[1], c[2]]] = count
-                fill[c[0], c[1], c[2]] += 1
-                count += 1
-                if count >= n:
-                    break
+    box = np.zeros(3)
+    dp = C.POINTER(C.c_double)
+    rc = _native().lg_gen_random_packing(int(n), float(volume_fraction), float(aspect), float(min_gap_factor), int(seed),
+                                         float(R_PART), pts.ctypes.data_as(dp), box.ctypes.data_as(dp))
+    if rc != 0:
+        raise RuntimeError(_native().lg_last_error().decode(errors="replace"))
+    rng = np.random.Generator(np.random.MT19937(seed))
     v0 = rng.uniform(-v_scale, v_scale, size=(n, 3))
     cfg = DemConfig(n=n, model_mask=models, use_neighbor_list=True)
     return Scenario(f"random_packing_{n}", cfg, pts, v0, _zeros(n), _zeros(n))
@@ -410,3 +352,22 @@ def stress_block(nx: int = 6, ny: int = 6, nz: int = 5, models: int = MODEL_CONT
     cfg = DemConfig(n=n, model_mask=models, use_neighbor_list=neighbor_list, facet_vertices=verts,
                     facet_v=tuple(facet_v), surf_A=1.0e-20, surf_contact=contact_params(mu=0.5), rebuild_every=5)
     return Scenario(f"stress_{nx}x{ny}x{nz}", cfg, np.ascontiguousarray(x0), v0, _zeros(n), w0)
+
+
+def aggregates_with_dense_block(n_copies: int = 20, block: int = 7, spacing: float = 1.96, jitter: float = 0.04,
+                                models: int = MODEL_SINTER | MODEL_HAMAKER, seed: int = 5, v_scale: float = 2.0) -> Scenario:
+    """Branch-coverage input for the short-row step kernel (not a reference set-up): `n_copies` soot aggregates (rows of
+    ~10 neighbors) followed by one over-dense jittered block of block^3 particles (rows of ~80 neighbors, overlapping
+    non-bonded pairs, six or more bonds per particle when the sinter model is on).  The mean row stays short, so the
+    production dispatch picks the row kernel while single rows exceed 64 pairs and single CTAs hold several hundred
+    bond records."""
+    agg = multi_aggregate_collision(n_copies, models=models)
+    rng = np.random.Generator(np.random.MT19937(seed))
+    g = np.stack(np.meshgrid(np.arange(block), np.arange(block), np.arange(block), indexing="ij"), axis=-1).reshape(-1, 3)
+    xb = (g.astype(np.float64) * spacing + rng.uniform(-jitter, jitter, size=g.shape)) * R_PART
+    xb += np.array([agg.x0[:, 0].max() + 12.0 * R_PART, 0.0, 0.0])
+    x0 = np.ascontiguousarray(np.concatenate([agg.x0, xb]))
+    n = len(x0)
+    v0 = np.concatenate([agg.v0, rng.uniform(-v_scale, v_scale, size=xb.shape)])
+    cfg = agg.cfg.with_(n=n)
+    return Scenario(f"aggregates_{n_copies}_block_{block}", cfg, x0, np.ascontiguousarray(v0), _zeros(n), _zeros(n))

@@ -30,7 +30,8 @@ ABI_SYMBOLS = (
     "lg_get_neighbor_count", "lg_get_neighbor_rows", "lg_get_contact_springs", "lg_get_bond", "lg_get_counters",
     "lg_diagnostics", "lg_set_kernel_variant", "lg_get_stream", "lg_set_profiling", "lg_get_profile",
     "lg_bond_table_create", "lg_bond_table_count", "lg_bond_table_records", "lg_bond_table_destroy", "lg_set_bond_table",
-    "lg_facet_set_vertices", "lg_set_math_mode",
+    "lg_facet_set_vertices", "lg_set_math_mode", "lg_last_step_kernel",
+    "lg_gen_fractal_aggregate", "lg_gen_random_packing",
     # slab decomposition support
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
@@ -119,6 +120,9 @@ def load_library(path: Optional[str] = None):
     lib.lg_set_bond_table.argtypes = [vp, cpp, C.c_double, C.c_double, vp]
     lib.lg_facet_set_vertices.argtypes = [vp, C.c_int, dp]
     lib.lg_set_math_mode.argtypes = [vp, C.c_int]
+    lib.lg_last_step_kernel.argtypes = [vp, C.c_char_p, C.c_int]
+    lib.lg_gen_fractal_aggregate.argtypes = [C.c_int64, C.c_uint64, C.c_double, dp]
+    lib.lg_gen_random_packing.argtypes = [C.c_int64, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_double, dp, dp]
     # slab decomposition support: device pointers travel as plain integers
     lib.lg_flush.argtypes = [vp]
     lib.lg_first_half_kick.argtypes = [vp, C.c_double]
@@ -327,6 +331,11 @@ class GranularSystem:
         ms, cnt = C.c_double(0.0), C.c_int64(0)
         self._check(self.lib.lg_get_profile(self.h, C.byref(ms), C.byref(cnt)))
         return float(ms.value), int(cnt.value)
+
+    def last_step_kernel(self) -> str:
+        buf = C.create_string_buffer(64)
+        self._check(self.lib.lg_last_step_kernel(self.h, buf, 64))
+        return buf.value.decode()
 
     def device_ptr(self, name: str) -> int:
         p = C.c_void_p()

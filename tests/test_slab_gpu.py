@@ -38,7 +38,7 @@ def _scenario(name):
     raise KeyError(name)
 
 
-def _worker(rank, world, port, name, out_dir, transport="p2p"):
+def _worker(rank, world, port, name, out_dir, transport="p2p", math_mode=0):
     import torch.distributed as dist
 
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), LGB200_HALO=transport)
@@ -50,7 +50,7 @@ def _worker(rank, world, port, name, out_dir, transport="p2p"):
         scn, steps, skin = _scenario(name)
         cfg = scn.cfg
         uv = _uv(4 * cfg.n) if cfg.model_mask & S.MODEL_SINTER else None
-        sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=rank, skin=skin)
+        sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=rank, skin=skin, math_mode=math_mode)
         res = {}
         done = 0
         for cp in (1, steps // 2, steps):
@@ -78,13 +78,13 @@ def _worker(rank, world, port, name, out_dir, transport="p2p"):
         dist.destroy_process_group()
 
 
-def _single(name):
+def _single(name, math_mode=0):
     from libgran_b200.system import from_config
 
     scn, steps, _ = _scenario(name)
     cfg = scn.cfg
     uv = _uv(4 * cfg.n) if cfg.model_mask & S.MODEL_SINTER else None
-    g = from_config(cfg, *scn.state, unit_vectors=uv, device=0)
+    g = from_config(cfg, *scn.state, unit_vectors=uv, device=0, math_mode=math_mode)
     res, done = {}, 0
     for cp in (1, steps // 2, steps):
         g.run(cfg.dt, cp - done, cfg.rebuild_every)
@@ -94,16 +94,20 @@ def _single(name):
     return res, g.counters(), g.diagnostics()
 
 
+@pytest.mark.parametrize("math_mode", [0, 1], ids=["exact", "fast"])
 @pytest.mark.parametrize("name", ["aggregates", "packing", "fractal"])
 @pytest.mark.parametrize("world", [1, 2, 4])
-def test_slab_equals_single_gpu(lib, tmp_path, name, world):
+def test_slab_equals_single_gpu(lib, tmp_path, name, world, math_mode):
+    """math_mode 1 is the mode the scaling bench runs (row kernel with an owned mask and ghost rows on the aggregate and
+    fractal inputs): the decomposition must not change a bit there either -- local order is ascending global id, so
+    every accumulation runs in the same order as on one GPU."""
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
 
-    mp.spawn(_worker, args=(world, _free_port(), name, str(tmp_path)), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, _free_port(), name, str(tmp_path), "p2p", math_mode), nprocs=world, join=True)
     got = np.load(os.path.join(str(tmp_path), "slab.npz"))
-    want, cnt, diag = _single(name)
+    want, cnt, diag = _single(name, math_mode)
     for key, val in want.items():
         assert np.array_equal(got[key], val), f"{name} world {world}: {key} differs, max abs {np.abs(got[key] - val).max():.3e}"
     assert int(got["pairs"]) == cnt["pairs"] and int(got["contacts"]) == cnt["contacts"]
