@@ -152,8 +152,9 @@ def build_workload(args, world: int = 1, sample: bool = False):
         if c == "4":
             scn = S.multi_aggregate_collision(copies)
             return scn, f"cfg4 multi-aggregate collision, {scn.cfg.n} particles ({copies} x aggregate.h), sinter+contact+Hamaker", False
-        scn = S.multi_aggregate_in_contact(copies)
-        return scn, (f"cfg4c multi-aggregate collision at impact (rows of aggregates slid into first contact, overlap 0.02 r), "
+        # CPU sample: the separated layout -- the reference's sinter constructor would bond the touching aggregates together
+        scn = S.multi_aggregate_collision(copies) if sample else S.multi_aggregate_in_contact(copies)
+        return scn, (f"cfg4c multi-aggregate collision at impact (rows of aggregates slid into first contact at the static-equilibrium overlap), "
                      f"{scn.cfg.n} particles ({copies} x aggregate.h), sinter+contact+Hamaker"), False
     if c == "5":
         n = 125_000 if sample else PER_GPU_5 * world
@@ -207,7 +208,8 @@ def run_ours(args):
 
     uv = numpy_unit_vectors(n + 1024) if cfg.model_mask & S.MODEL_SINTER else None
     mode = 1 if (args.math == "fast" and args.variant in (None, 1, 2)) else 0
-    sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)
+    bonds = scn.make_bonds(uv) if scn.make_bonds is not None else None
+    sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode, bonds=bonds)
     stream = torch.cuda.ExternalStream(sysm.stream_handle(), device=torch.device("cuda", local_rank))
 
     def timed_run(k):
@@ -274,7 +276,7 @@ def run_ours(args):
     host_np = [t.numpy() for t in pinned]
     outs = [torch.empty((n, 3), dtype=torch.float64).pin_memory() for _ in range(4)]
     out_np = [t.numpy() for t in outs]
-    e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode)  # model tables built once (as a ctor would)
+    e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode, bonds=bonds)  # model tables built once (as a ctor would)
     facet0 = e2e_sys.facet_vertices(0) if moves else None
     e2e_steps = args.steps
     # untimed priming with dt = 0: sizes the neighbor / scratch buffers for exactly this state and leaves positions,
@@ -338,7 +340,8 @@ def run_slab(args, scn, desc, moves, world, rank, local_rank):
     dev = torch.device("cuda", local_rank)
     uv = numpy_unit_vectors(n + 1024) if cfg.model_mask & S.MODEL_SINTER else None
     mode = 1 if args.math == "fast" else 0
-    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode)
+    bonds = scn.make_bonds(uv) if scn.make_bonds is not None else None
+    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode, bonds=bonds)
     warm = effective_warmup(args)
     sysm.run(cfg.dt, warm, REBUILD_EVERY)
     sysm.synchronize()
@@ -401,7 +404,7 @@ def run_slab(args, scn, desc, moves, world, rank, local_rank):
     # end to end: host buffers in, host buffers out, through the slab driver
     # (a fresh system, primed with dt = 0 like the single-GPU arm: same buffers, untouched state and connectors)
     sysm.close()
-    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode)
+    sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode, bonds=bonds)
     sysm.run(0.0, warm, REBUILD_EVERY)
     own = sysm.counters()["owned_local"]
     pinned = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in scn.state]

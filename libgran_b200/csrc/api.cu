@@ -321,9 +321,9 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.rows_per_block = rows_per_block(s);
     A.fast = s->math_mode;
     {   // short rows (aggregates) -> row kernel; long rows (packings) -> tile kernel.  LGB200_ROWS_KERNEL=0 disables it.
-        static const int rows_enabled = [] { const char* e = std::getenv("LGB200_ROWS_KERNEL"); return e ? std::atoi(e) : 1; }();
+        static const int rows_enabled = [] { const char* e = std::getenv("LGB200_ROWS_KERNEL"); return e ? std::atoi(e) : 2; }();  // 2 = step_rows2_kernel, 1 = step_rows_kernel, 0 = tile kernel
         const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
-        A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= 24.0))) ? 1 : 0;  // variant 2: rows kernel whatever the row length
+        A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= 24.0))) ? (rows_enabled == 1 ? 1 : 2) : 0;  // variant 2: row kernel whatever the row length
     }
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia);
     const bool fused = fused_dt >= 0.0;
@@ -345,7 +345,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         launch_step_tiled(A, s->mask, true, s->stream);
     else
         launch_force(A, s->mask, s->variant, s->stream);
-    s->last_kernel = s->variant == 0 ? "force_simple_kernel" : (A.fast && A.use_rows) ? "step_rows_kernel" : "step_tiled_kernel";
+    s->last_kernel = s->variant == 0 ? "force_simple_kernel" : (A.fast && A.use_rows) ? (A.use_rows == 2 ? "step_rows2_kernel" : "step_rows_kernel") : "step_tiled_kernel";
     if (s->profiling) LG_CUDA(cudaEventRecord(s->prof_events[s->prof_used++].second, s->stream));
     LG_CUDA(cudaGetLastError());
     if (fused) {

@@ -1,0 +1,431 @@
+// kernels_rows.cu -- step_rows2_kernel: the PERSISTENT, software-pipelined organisation of the short-row fused step
+// (relaxed arithmetic, LG_MATH_FAST; aggregates with ~10 neighbors and ~2 bond records per particle).
+//
+// Same mathematics, same inputs and outputs as step_rows_kernel (kernels_force_tiled.cu); what changes is how the
+// bytes move:
+//   * a grid of (SMs x resident CTAs) blocks loops over tiles of RT2 consecutive particles;
+//   * a PRODUCER warp (one elected lane) keeps the next tile's inputs in flight while the compute warps work on the
+//     current one: two shared-memory stages, a full / empty mbarrier pair per stage, every contiguous range of the tile
+//     -- x (with a halo of RH2 particles either side), v, omega, theta, row / bond pointer slices, columns, tags, and
+//     now also the tile's OWN bond records: connectors (120 B each), rest lengths, partner and mirror indices -- fetched
+//     by cp.async.bulk (UBLKCP) against the stage's full barrier;
+//   * pass 1 (one thread per bond record) reads its connectors from shared memory, and the mirror record too when the
+//     partner belongs to the tile (the common case inside an aggregate);
+//   * pass 2 walks each particle's row with LPP cooperating lanes (partial sums combined by shuffles, fixed order);
+//   * pass 3 integrates and moves the connectors IN the staged copy, and the results leave by bulk stores
+//     (cp.async.bulk.global.shared::cta) straight from the stage; the producer refills a stage once its stores have
+//     read it (cp.async.bulk.wait_group.read).
+// Replaces (like the other step kernels) LT/rotational_system/rotational_binary_system_neighbors_omp.h:78-98,
+// LG/granular_system/binary_force_container.h:20-32, LG/contact_force/contact_force.h:57-147,
+// LG/hamaker_force/hamaker_force.h:28-43, LG/sinter_bridge/sinter_bridge.h:24-94,214-259 and
+// LT/rotational_integrator/rotational_velocity_verlet_half.h:63-73.
+#include "step_common.cuh"
+
+namespace lg {
+
+namespace {
+
+#ifndef LG_R2_RT
+#define LG_R2_RT 128   // particles per tile
+#endif
+#ifndef LG_R2_LPP
+#define LG_R2_LPP 2    // lanes per particle in pass 2
+#endif
+#ifndef LG_R2_MINB
+#define LG_R2_MINB 1   // resident CTAs per SM the launch bound asks for
+#endif
+constexpr int RT2 = LG_R2_RT;
+constexpr int LPP = LG_R2_LPP;
+constexpr int NT2 = RT2 * LPP;        // compute threads
+constexpr int NTH2 = NT2 + 32;        // + the producer warp
+constexpr int RH2 = 128;              // halo of the staged x window (particles either side)
+constexpr int RPC2 = 12 * RT2;        // staged columns / tags per tile
+constexpr int RBC2 = 2 * RT2 + 32;    // staged bond records per tile
+static_assert(RT2 % 32 == 0 && (LPP == 1 || LPP == 2 || LPP == 4) && RPC2 % 16 == 0 && RBC2 % 16 == 0, "tile shape");
+
+struct alignas(16) Stage2 {
+    double wx[3 * (RT2 + 2 * RH2) + 4];
+    double wv[3 * RT2 + 4];
+    double ww[3 * RT2 + 4];
+    double wth[3 * RT2 + 4];
+    double wconn[15 * RBC2 + 4];
+    double wlen[5 * RBC2 + 4];
+    uint32_t wrow[RT2 + 12];
+    uint32_t wbond[RT2 + 12];
+    int32_t wcols[RPC2 + 8];
+    int32_t wbj[RBC2 + 8];
+    int32_t wrev[RBC2 + 8];
+    uint8_t wtag[RPC2 + 32];
+};
+
+struct alignas(16) Rows2Smem {
+    Stage2 st[2];
+    double res[6 * RBC2];     // pass 1 results per bond record; pass 3: dx, dtheta of every particle
+    uint8_t brow[RBC2];       // local row of every staged bond record
+    unsigned long long full[2], empty[2];
+};
+
+__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void compute_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(NT2) : "memory"); }
+
+// Bulk store shared -> global of [ssrc, ssrc + nbytes) to gdst; both addresses are congruent mod 16 (0 or 8) and nbytes is
+// a multiple of 8: the 16-byte aligned middle goes by cp.async.bulk, a leading / trailing double by an ordinary store.
+__device__ __forceinline__ void bulk_store(double* gdst, const double* ssrc, uint32_t nbytes) {
+    if (nbytes == 0) return;
+    if ((uintptr_t)gdst & 15u) {
+        *gdst = *ssrc;
+        gdst++;
+        ssrc++;
+        nbytes -= 8u;
+    }
+    const uint32_t mid = nbytes & ~15u;
+    if (mid)
+        asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(mid) : "memory");
+    if (nbytes & 8u) gdst[mid >> 3] = ssrc[mid >> 3];
+}
+
+template <int MASK, int MODE, bool FACETS>
+__global__ void __launch_bounds__(NTH2, LG_R2_MINB) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
+    constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
+    constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
+    constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    Rows2Smem& sm = *reinterpret_cast<Rows2Smem*>(smem_raw);
+
+    const int tid = threadIdx.x;
+    const int n_tiles = (A.n + RT2 - 1) / RT2;
+    const bool have_bonds = kSinter && A.bptr != nullptr;
+
+    if (tid == 0) {
+        for (int s = 0; s < 2; s++) {
+            mbar_init(&sm.full[s], 1);
+            mbar_init(&sm.empty[s], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncthreads();
+
+    if (tid >= NT2) {
+        // ================= producer: one lane keeps two tiles of inputs in flight ====================================
+        if (tid != NT2) return;
+        int tile = blockIdx.x;
+        if (tile >= n_tiles) return;
+        auto load_desc = [&](int t, uint32_t d[4]) {  // pair / bond-record ranges of tile t: four independent loads
+            const int i0 = t * RT2, nr = min(RT2, A.n - i0);
+            d[0] = A.row_ptr[i0];
+            d[1] = A.row_ptr[i0 + nr];
+            d[2] = have_bonds ? A.bptr[i0] : 0u;
+            d[3] = have_bonds ? A.bptr[i0 + nr] : 0u;
+        };
+        uint32_t d[4], dn[4] = {0u, 0u, 0u, 0u};
+        load_desc(tile, d);
+        for (int k = 0; tile < n_tiles; k++, tile += gridDim.x) {
+            const int s = k & 1;
+            const int nxt = tile + gridDim.x;
+            if (nxt < n_tiles) load_desc(nxt, dn);  // in flight while this tile's copies are issued
+            if (k >= 2) mbar_wait(&sm.empty[s], (uint32_t)(((k >> 1) - 1) & 1));
+            Stage2& S = sm.st[s];
+            const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
+            const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
+            const double* gx = A.x + 3 * (size_t)xlo;
+            const double* gv = A.v + 3 * (size_t)i0;
+            const double* gw = A.w + 3 * (size_t)i0;
+            const double* gth = A.th + 3 * (size_t)i0;
+            const uint32_t* grow = A.row_ptr + i0;
+            const uint32_t* gbond = have_bonds ? A.bptr + i0 : nullptr;
+            const uint32_t nb3 = 24u * (uint32_t)nrows, nbp = 4u * (uint32_t)(nrows + 1), nbx = 24u * (uint32_t)xcnt;
+            const uint32_t np0 = min(d[1] - d[0], (uint32_t)RPC2);
+            const uint32_t nbr = (d[3] - d[2] <= (uint32_t)RBC2) ? d[3] - d[2] : 0u;
+            const int32_t* gcols = A.cols + d[0];
+            const uint8_t* gtag = A.tag + d[0];
+            const double* gconn = A.bconn + 15 * (size_t)d[2];
+            const double* glen = A.blen + 5 * (size_t)d[2];
+            const int32_t* gbj = A.bj + d[2];
+            const int32_t* grev = A.brev + d[2];
+            uint32_t total = window_bytes(gx, nbx) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(grow, nbp) +
+                             window_bytes(gcols, 4u * np0);
+            if constexpr (MODE == MODE_FUSED) total += window_bytes(gth, nb3);
+            if (have_bonds) total += window_bytes(gbond, nbp);
+            if constexpr (kContact) total += window_bytes(gtag, np0);
+            if (nbr)
+                total += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(gbj, 4u * nbr) +
+                         window_bytes(grev, 4u * nbr);
+            mbar_expect_tx(&sm.full[s], total);
+            if (nbr) {
+                bulk_load(S.wconn, gconn, 120u * nbr, &sm.full[s]);
+                bulk_load(S.wlen, glen, 40u * nbr, &sm.full[s]);
+                bulk_load(S.wbj, gbj, 4u * nbr, &sm.full[s]);
+                bulk_load(S.wrev, grev, 4u * nbr, &sm.full[s]);
+            }
+            bulk_load(S.wx, gx, nbx, &sm.full[s]);
+            bulk_load(S.wv, gv, nb3, &sm.full[s]);
+            bulk_load(S.ww, gw, nb3, &sm.full[s]);
+            if constexpr (MODE == MODE_FUSED) bulk_load(S.wth, gth, nb3, &sm.full[s]);
+            bulk_load(S.wrow, grow, nbp, &sm.full[s]);
+            if (have_bonds) bulk_load(S.wbond, gbond, nbp, &sm.full[s]);
+            bulk_load(S.wcols, gcols, 4u * np0, &sm.full[s]);
+            if constexpr (kContact) bulk_load(S.wtag, gtag, np0, &sm.full[s]);
+#pragma unroll
+            for (int q = 0; q < 4; q++) d[q] = dn[q];
+        }
+        return;
+    }
+
+    // ===================== compute warps ==================================================================================
+    const int r = tid / LPP, lp = tid % LPP;  // particle of the tile and lane within it (pass 2)
+    int k = 0;
+    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, k++) {
+        const int s = k & 1;
+        Stage2& S = sm.st[s];
+        const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
+        const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
+        mbar_wait(&sm.full[s], (uint32_t)((k >> 1) & 1));
+
+        double* sxw = S.wx + (window_lead(A.x + 3 * (size_t)xlo) >> 3);  // x of particle xlo + q at sxw[3 q]
+        double* sx = sxw + 3 * (i0 - xlo);
+        double* sv = S.wv + (window_lead(A.v + 3 * (size_t)i0) >> 3);
+        double* sw = S.ww + (window_lead(A.w + 3 * (size_t)i0) >> 3);
+        double* sth = S.wth + (window_lead(A.th + 3 * (size_t)i0) >> 3);
+        const uint32_t* sptr = S.wrow + (window_lead(A.row_ptr + i0) >> 2);
+        const uint32_t* sbptr = S.wbond + (have_bonds ? (window_lead(A.bptr + i0) >> 2) : 0u);
+        const uint32_t p_begin = sptr[0];
+        const uint32_t b0 = have_bonds ? sbptr[0] : 0u;
+        const uint32_t nbond = have_bonds ? sbptr[nrows] - b0 : 0u;
+        const bool bonds_staged = nbond > 0 && nbond <= (uint32_t)RBC2;
+        const int32_t* scols = S.wcols + (window_lead(A.cols + p_begin) >> 2);
+        const uint8_t* stag = S.wtag + window_lead(A.tag + p_begin);
+        double* sconn = S.wconn + (window_lead(A.bconn + 15 * (size_t)b0) >> 3);
+        const double* slen = S.wlen + (window_lead(A.blen + 5 * (size_t)b0) >> 3);
+        const int32_t* sbj = S.wbj + (window_lead(A.bj + b0) >> 2);
+        const int32_t* srev = S.wrev + (window_lead(A.brev + b0) >> 2);
+
+        auto neighbour = [&](int j, const double* sp, const double* gsrc) -> d3 {  // v, omega: own particles staged
+            const unsigned rj = (unsigned)(j - i0);
+            return rj < (unsigned)nrows ? load3(sp + 3 * rj) : load3(gsrc + 3 * (size_t)j);
+        };
+        auto neighbour_x = [&](int j) -> d3 {
+            const unsigned rj = (unsigned)(j - xlo);
+            return rj < (unsigned)xcnt ? load3(sxw + 3 * rj) : load3(A.x + 3 * (size_t)j);
+        };
+
+        // ---- pass 1: one thread per bond record, operands from the stage -------------------------------------------
+        if constexpr (kSinter) {
+            if (bonds_staged) {
+                if (tid < nrows)
+                    for (uint32_t b = sbptr[tid]; b < sbptr[tid + 1]; b++) sm.brow[b - b0] = (uint8_t)tid;
+                compute_barrier();
+                for (uint32_t bl = tid; bl < nbond; bl += NT2) {
+                    const int rr = sm.brow[bl];
+                    const int j = sbj[bl];
+                    const uint32_t ml = (uint32_t)srev[bl] - b0;
+                    const double* ci = sconn + 15 * bl;
+                    const double* cj = ml < nbond ? sconn + 15 * ml : A.bconn + (size_t)srev[bl] * 15;
+                    const double* len = slen + 5 * bl;
+                    const d3 xi = load3(sx + 3 * rr), xj = neighbour_x(j);
+                    d3 fa, ta;
+                    if (A.mp.gamma_d != 0.0)
+                        bridge_fast<true>(A, ci, cj, len, xi, xj, load3(sv + 3 * rr), neighbour(j, sv, A.v), load3(sw + 3 * rr),
+                                          neighbour(j, sw, A.w), fa, ta);
+                    else
+                        bridge_fast<false>(A, ci, cj, len, xi, xj, zero3(), zero3(), zero3(), zero3(), fa, ta);
+                    store3(sm.res + 6 * bl, fa);
+                    store3(sm.res + 6 * bl + 3, ta);
+                }
+            }
+        }
+        compute_barrier();  // pass 1 results
+
+        // ---- pass 2: LPP lanes per particle walk its row (lane l: pairs pb + l, pb + l + LPP, ...) ---------------------
+        d3 acc_a = zero3(), acc_al = zero3();
+        unsigned long long slow = 0ull;  // bit q: pair pb + q (q < 64) is evaluated out of line afterwards
+        const bool live = r < nrows;
+        const d3 xi = live ? load3(sx + 3 * r) : zero3();
+        uint32_t pb = 0u, pe = 0u;
+        if (live) {
+            pb = sptr[r];
+            pe = sptr[r + 1];
+            for (uint32_t p = pb + (uint32_t)lp; p < pe; p += LPP) {
+                const uint32_t ps = p - p_begin;
+                const int j = ps < (uint32_t)RPC2 ? scols[ps] : A.cols[p];
+                const d3 xj = neighbour_x(j);
+                const PairGeom g = pair_geometry_fast(xi, xj);
+                d3 pa = zero3();
+                if constexpr (kHamaker) pa = hamaker_accel_fast(A.fc, g);
+                if constexpr (kContact) {
+                    const int t = ps < (uint32_t)RPC2 ? stag[ps] : A.tag[p];
+                    if (kSinter && t >= kTagBond && t != kTagNone) {
+                        if (bonds_staged) {
+                            const uint32_t bl = sbptr[r] + (uint32_t)(t - kTagBond) - b0;
+                            const d3 sa = load3(sm.res + 6 * bl);
+                            pa = kHamaker ? sa + pa : sa;  // pair value = sinter(i,j) + hamaker(i,j)
+                            acc_al += load3(sm.res + 6 * bl + 3);
+                        } else {
+                            if (p - pb < 64u) slow |= 1ull << (p - pb);
+                            continue;
+                        }
+                    } else {
+                        const double overlap = A.fc.two_r - g.len;
+                        if (overlap <= -A.fc.band) {  // clearly apart
+                            if (t != kTagNone) {  // reset_springs (contact_force.h:68-71)
+                                A.sgid[(size_t)(i0 + r) * A.S + t] = -1;
+                                A.tag[p] = (uint8_t)kTagNone;
+                            }
+                        } else {  // overlapping, or inside the rounding band of zero (decided on the exact expression)
+                            if (p - pb < 64u) slow |= 1ull << (p - pb);
+                            continue;
+                        }
+                    }
+                }
+                acc_a += pa;
+            }
+        }
+        if constexpr (LPP > 1) {  // fixed-shape combination of the lanes' partial sums (all 32 lanes take part)
+#pragma unroll
+            for (int off = 1; off < LPP; off <<= 1) {
+                acc_a.x += __shfl_xor_sync(0xffffffffu, acc_a.x, off);
+                acc_a.y += __shfl_xor_sync(0xffffffffu, acc_a.y, off);
+                acc_a.z += __shfl_xor_sync(0xffffffffu, acc_a.z, off);
+                acc_al.x += __shfl_xor_sync(0xffffffffu, acc_al.x, off);
+                acc_al.y += __shfl_xor_sync(0xffffffffu, acc_al.y, off);
+                acc_al.z += __shfl_xor_sync(0xffffffffu, acc_al.z, off);
+                if constexpr (kContact) slow |= __shfl_xor_sync(0xffffffffu, slow, off);
+            }
+        }
+        d3 xn = zero3(), vn = zero3(), wn = zero3(), dth = zero3(), dxv = zero3();
+        if (live && lp == 0) {
+            const d3 vi = load3(sv + 3 * r), wi = load3(sw + 3 * r);
+            if constexpr (kContact) {
+                if (slow != 0ull || pe - pb > 64u) {  // rare: out of line, so that the hot loop keeps its registers
+                    double out6[6];
+                    rows_slow_pairs<kSinter, kHamaker>(A, sxw, xlo, xcnt, r + (i0 - xlo), pb, pe, slow, bonds_staged,
+                                                       have_bonds ? sbptr[r] : 0u, out6);
+                    acc_a += load3(out6);
+                    acc_al += load3(out6 + 3);
+                }
+            }
+            if constexpr (FACETS) {
+                const Accel u = unary_forces(A, i0 + r, xi, vi, wi);
+                acc_a += u.a;
+                acc_al += u.alpha;
+            }
+            if constexpr (MODE == MODE_FORCE) {
+                vn = acc_a;
+                wn = acc_al;
+            } else {
+                const double dt = A.dt;
+                vn = vi + acc_a * dt;   // increment_v(n, a * dt)
+                dxv = vn * dt;          // increment_x(n, v * dt), v already updated
+                xn = xi + dxv;
+                wn = wi + acc_al * dt;  // increment_omega
+                dth = wn * dt;          // increment_theta, omega already updated
+            }
+        }
+        compute_barrier();  // every read of the staged state and of the pass-1 results is done
+
+        // ---- pass 3: results into the stage, connectors moved in place, bulk stores ----------------------------------------
+        if (live && lp == 0) {
+            store3(sv + 3 * r, vn);
+            store3(sw + 3 * r, wn);
+            if constexpr (MODE == MODE_FUSED) {
+                store3(sx + 3 * r, xn);
+                store3(sth + 3 * r, load3(sth + 3 * r) + dth);
+                store3(sm.res + 6 * r, dxv);
+                store3(sm.res + 6 * r + 3, dth);
+            }
+        }
+        if constexpr (MODE == MODE_FUSED && kSinter) {
+            if (have_bonds) {
+                compute_barrier();
+                // connectors of the tile's particles: c += dx ; c += dtheta x (c - x_new)   (sinter_bridge.h:36-41,67-74)
+                const int ncon = (int)nbond * 5;
+                if (bonds_staged) {
+                    for (int cq = tid; cq < ncon; cq += NT2) {
+                        const int rr = sm.brow[cq / 5];
+                        d3 ck = load3(sconn + 3 * cq) + load3(sm.res + 6 * rr);
+                        const d3 arm = ck - load3(sx + 3 * rr);
+                        ck = ck + cross(load3(sm.res + 6 * rr + 3), arm);
+                        store3(sconn + 3 * cq, ck);
+                    }
+                } else {  // more bond records than the stage holds: straight from / to global memory
+                    for (int cq = tid; cq < ncon; cq += NT2) {
+                        const int rr = find_row(sbptr, nrows, b0 + (uint32_t)(cq / 5));
+                        const size_t off = (size_t)b0 * 15 + 3 * (size_t)cq;
+                        d3 ck = load3(A.bconn + off) + load3(sm.res + 6 * rr);
+                        const d3 arm = ck - load3(sx + 3 * rr);
+                        ck = ck + cross(load3(sm.res + 6 * rr + 3), arm);
+                        store3(A.bconn_next + off, ck);
+                    }
+                }
+            }
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // this thread's shared-memory writes -> async proxy
+        compute_barrier();
+        if (tid == 0) {
+            const uint32_t nb3 = 24u * (uint32_t)nrows;
+            const size_t g0 = 3 * (size_t)i0;
+            if constexpr (MODE == MODE_FORCE) {
+                bulk_store(A.a + g0, sv, nb3);
+                bulk_store(A.al + g0, sw, nb3);
+            } else {
+                bulk_store(A.x_next + g0, sx, nb3);
+                bulk_store(A.v_next + g0, sv, nb3);
+                bulk_store(A.w_next + g0, sw, nb3);
+                bulk_store(A.th + g0, sth, nb3);
+                if (kSinter && bonds_staged) bulk_store(A.bconn_next + 15 * (size_t)b0, sconn, 120u * nbond);
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the stage may be overwritten
+            mbar_arrive(&sm.empty[s]);
+        }
+    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
+}
+
+int resident_ctas_rows2(const void* fn) {
+    int dev = 0, sms = 0, occ = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, NTH2, sizeof(Rows2Smem));
+    return sms * (occ > 0 ? occ : 1);
+}
+
+template <int MASK, int MODE, bool FACETS>
+void launch_rows2_one(const ForceArgs& args, cudaStream_t st) {
+    static int grid_cap = 0;  // per instantiation
+    if (grid_cap == 0) {
+        cudaFuncSetAttribute(step_rows2_kernel<MASK, MODE, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Rows2Smem));
+        grid_cap = resident_ctas_rows2((const void*)step_rows2_kernel<MASK, MODE, FACETS>);
+    }
+    const int n_tiles = (args.n + RT2 - 1) / RT2;
+    step_rows2_kernel<MASK, MODE, FACETS><<<min(n_tiles, grid_cap), NTH2, sizeof(Rows2Smem), st>>>(args);
+    g_launch_count++;
+}
+
+template <int MASK, int MODE>
+void launch_rows2_facets(const ForceArgs& args, cudaStream_t st) {
+    if (args.n_facets > 0) launch_rows2_one<MASK, MODE, true>(args, st); else launch_rows2_one<MASK, MODE, false>(args, st);
+}
+
+template <int MODE>
+void launch_rows2_mode(const ForceArgs& args, int mask, cudaStream_t st) {
+    switch (mask & (MODEL_CONTACT | MODEL_HAMAKER | MODEL_SINTER)) {
+        case MODEL_CONTACT: launch_rows2_facets<MODEL_CONTACT, MODE>(args, st); break;
+        case MODEL_CONTACT | MODEL_HAMAKER: launch_rows2_facets<MODEL_CONTACT | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_SINTER: launch_rows2_facets<MODEL_SINTER, MODE>(args, st); break;
+        case MODEL_SINTER | MODEL_HAMAKER: launch_rows2_facets<MODEL_SINTER | MODEL_HAMAKER, MODE>(args, st); break;
+        case MODEL_HAMAKER: launch_rows2_facets<MODEL_HAMAKER, MODE>(args, st); break;
+        default: launch_rows2_facets<0, MODE>(args, st); break;
+    }
+}
+
+}  // namespace
+
+void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {
+    if (fused) launch_rows2_mode<MODE_FUSED>(args, mask, st); else launch_rows2_mode<MODE_FORCE>(args, mask, st);
+}
+
+}  // namespace lg

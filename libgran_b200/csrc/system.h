@@ -73,7 +73,7 @@ struct ForceArgs {
     // tiled / fused kernel only
     int rows_per_block;
     int fast;           // relaxed arithmetic (lg_set_math_mode)
-    int use_rows;       // fast + fused only: short rows -> step_rows_kernel (one thread per particle) instead of the tile kernel
+    int use_rows;       // fast only: short rows -> a row kernel instead of the tile kernel (1 step_rows_kernel, 2 step_rows2_kernel)
     FastConsts fc;      // its host-computed constants
     double dt;          // integration step of the fused update
     double* x_next;     // next-step buffers (double-buffered state)
@@ -111,6 +111,7 @@ extern thread_local int64_t g_launch_count;
 void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st);
 // tiled kernel: force only (fused == false) or force + integrate into the next-step buffers (fused == true)
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st);
+void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st);  // kernels_rows.cu
 int tiled_max_rows_per_block();
 int tiled_tile_pairs();
 void launch_integrate(const IntegrateArgs& args, cudaStream_t st);

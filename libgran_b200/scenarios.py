@@ -76,6 +76,9 @@ class Scenario:
     v0: np.ndarray
     theta0: np.ndarray
     omega0: np.ndarray
+    #: optional: unit_vectors -> (ij, connectors, rest lengths) for lg_set_bonds, when the bridges are NOT what the sinter
+    #: constructor would detect from x0 (multi_aggregate_in_contact: touching aggregates must stay unbonded)
+    make_bonds: object = None
 
     @property
     def state(self):
@@ -268,13 +271,19 @@ def multi_aggregate_collision(n_copies: int = 6667, models: int = MODEL_SINTER |
     return Scenario(f"multi_aggregate_{n}", cfg, np.ascontiguousarray(x0), v0, _zeros(n), _zeros(n))
 
 
-def multi_aggregate_in_contact(n_copies: int = 6667, overlap: float = 0.02, models: int = MODEL_SINTER | MODEL_HAMAKER,
+def multi_aggregate_in_contact(n_copies: int = 6667, overlap: float = None, models: int = MODEL_SINTER | MODEL_HAMAKER,
                                seed: int = 2, speed: float = 0.5) -> Scenario:
     """Config 4 at the moment of impact: the same rotated copies of aggregate.h on the same grid, but every aggregate is
     slid along -x until it first touches its -x neighbour with an overlap of `overlap` * r (exact first-contact
     distance of the two rigid particle sets), so that whole rows of aggregates are in Luding contact and aggregates of
-    neighbouring grid rows come within the Verlet radius.  Velocities as config 4 (left half +x, right half -x)."""
+    neighbouring grid rows come within the Verlet radius.  Default overlap: the static equilibrium k * overlap =
+    F_Hamaker(h0) (7e-8 r), where a touching pair neither rebounds nor sinks, so the contacts persist through a run.
+    Velocities as config 4 (left half +x, right half -x)."""
     base_scn = multi_aggregate_collision(n_copies, models=models, seed=seed, speed=speed)
+    if overlap is None:
+        c, r, h = base_scn.cfg, R_PART, base_scn.cfg.hamaker_h0
+        f_h = c.hamaker_A / 6.0 * 64.0 * r ** 6 / (h * h * (2.0 * r + h) ** 3 * (4.0 * r + h) ** 2)  # hamaker_force.h:36-40 at h = h0
+        overlap = f_h / c.contact[0] / r
     x = base_scn.x0.reshape(n_copies, -1, 3).copy()
     m = x.shape[1]
     ny = nz = max(1, int(round((n_copies / 2.0) ** (1.0 / 3.0))))
@@ -297,7 +306,20 @@ def multi_aggregate_in_contact(n_copies: int = 6667, overlap: float = 0.02, mode
         shift[c] = slide.min()
     x[:, :, 0] -= shift[:, None]
     x0 = np.ascontiguousarray(x.reshape(-1, 3))
-    return Scenario(f"multi_aggregate_in_contact_{len(x0)}", base_scn.cfg, x0, base_scn.v0, base_scn.theta0, base_scn.omega0)
+
+    def make_bonds(unit_vectors):
+        # bridges INSIDE the aggregates only: detected on the separated layout (sinter_bridge.h:148-211 via
+        # lg_bond_table_create), then carried along with each aggregate's slide; the touching pairs BETWEEN aggregates
+        # are closer than critical_separation and would otherwise be sintered together instead of being in contact
+        from .system import host_bond_table
+
+        ij, conn, ln = host_bond_table(base_scn.x0, base_scn.cfg.r_part, base_scn.cfg.critical_separation, unit_vectors)
+        conn = conn.reshape(-1, 5, 3).copy()
+        conn[:, :, 0] -= shift[ij[:, 0] // m][:, None]
+        return ij, conn.reshape(-1, 15), ln
+
+    return Scenario(f"multi_aggregate_in_contact_{len(x0)}", base_scn.cfg, x0, base_scn.v0, base_scn.theta0, base_scn.omega0,
+                    make_bonds=make_bonds)
 
 
 def random_packing(n: int = 1_250_000, volume_fraction: float = 0.30, models: int = MODEL_CONTACT | MODEL_HAMAKER,

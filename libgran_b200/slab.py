@@ -407,7 +407,7 @@ class SlabSystem:
     Every rank constructs it with the same full initial state (the driver program's x0, v0, theta0, omega0)."""
 
     def __init__(self, cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = 0, group=None, skin: Optional[float] = None,
-                 axis: int = 0, max_contacts: int = 16, math_mode: int = 0):
+                 axis: int = 0, max_contacts: int = 16, math_mode: int = 0, bonds=None):
         from . import system as _sys
         from .scenarios import MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
 
@@ -436,11 +436,12 @@ class SlabSystem:
         self.repartitions = 0
         self.kicked = False
         self._models = (bool(cfg.model_mask & MODEL_CONTACT), bool(cfg.model_mask & MODEL_SINTER), bool(cfg.model_mask & MODEL_HAMAKER))
-        bonds = (None, None, None)
-        if cfg.model_mask & MODEL_SINTER:
-            if unit_vectors is None:
-                raise ValueError("the sinter model needs unit_vectors")
-            bonds = _sys.host_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors)
+        if bonds is None:
+            bonds = (None, None, None)
+            if cfg.model_mask & MODEL_SINTER:
+                if unit_vectors is None:
+                    raise ValueError("the sinter model needs unit_vectors")
+                bonds = _sys.host_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors)
         torch.cuda.set_device(self.device)
         t0 = block_tables(self.rank, self.world, x0, v0, theta0, omega0, self.S, *bonds, device=self.device)
         self._install(t0)

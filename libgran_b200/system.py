@@ -379,7 +379,7 @@ class GranularSystem:
 
 
 def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1, variant: Optional[int] = None,
-                math_mode: int = 0) -> GranularSystem:
+                math_mode: int = 0, bonds=None) -> GranularSystem:
     """Build a GranularSystem from a ``scenarios.DemConfig`` (same meaning as oracle/dem_config.h)."""
     from .scenarios import MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
 
@@ -392,9 +392,12 @@ def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1
     if cfg.model_mask & MODEL_CONTACT:
         sysm.set_contact(cfg.contact)
     if cfg.model_mask & MODEL_SINTER:
-        if unit_vectors is None:
-            raise ValueError("the sinter model needs unit_vectors (callable or array)")
-        sysm.build_sinter_bonds(cfg.contact, cfg.k_d, cfg.gamma_d, cfg.critical_separation, unit_vectors)
+        if bonds is not None:  # explicit tables (ij, connectors, rest lengths) instead of the constructor's scan
+            sysm.set_bonds(cfg.contact, cfg.k_d, cfg.gamma_d, *bonds)
+        else:
+            if unit_vectors is None:
+                raise ValueError("the sinter model needs unit_vectors (callable or array)")
+            sysm.build_sinter_bonds(cfg.contact, cfg.k_d, cfg.gamma_d, cfg.critical_separation, unit_vectors)
     if cfg.model_mask & MODEL_HAMAKER:
         sysm.set_hamaker(cfg.hamaker_A, cfg.hamaker_h0)
     if cfg.model_mask & MODEL_FACET:

@@ -8,12 +8,12 @@ mkdir -p ../variants
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   d=build/var_$name; mkdir -p $d
-  for f in api kernels_force kernels_force_tiled kernels_integrate kernels_neighbor kernels_halo; do
-    if [ $f = kernels_force_tiled ] || [ ! -f build/$f.o ]; then
+  for f in api kernels_force kernels_force_tiled kernels_rows kernels_integrate kernels_neighbor kernels_halo generators; do
+    if [ $f = kernels_force_tiled ] || [ $f = kernels_rows ] || [ ! -f build/$f.o ]; then
       /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -std=c++17 -O3 -lineinfo --fmad=false \
         -Xcompiler -fPIC,-ffp-contract=off -Xptxas -v $flags -c $f.cu -o $d/$f.o 2> $d/$f.ptxas.log &
     else cp build/$f.o $d/$f.o; fi
   done; wait
   /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -shared -o ../variants/liblgb200_$name.so $d/*.o
-  grep -A2 "step_rows_kernelILi6ELb0\|ILi6ELi1ELb0ELb1" $d/kernels_force_tiled.ptxas.log | grep -E "spill|Used" | tr '\n' ' '; echo " <- $name"
+  grep -A2 "step_rows2_kernelILi6ELi1ELb0" $d/kernels_rows.ptxas.log | grep -E "spill|Used" | tr '\n' ' '; echo " <- $name"
 done
