@@ -169,6 +169,13 @@ struct lg_system {
     NeighborGrid grid{};
     bool grid_valid = false;
     int grid_age = 0;
+    // Steady-state rebuilds make no host round trip: the bounding box that refreshes the grid and
+    // the pair count that sizes the column buffers are read back asynchronously and consumed at a later rebuild; a
+    // device-side guard (launch_pair_guard) keeps an unexpectedly large list from overrunning the buffers.
+    cudaEvent_t ev_bbox = nullptr, ev_pairs = nullptr;
+    bool bbox_pending = false, pairs_pending = false;
+    int64_t last_total = -1;          // exact pair count of the most recent rebuild whose read-back has been consumed
+    DevBuf<uint32_t> pair_total;      // [0] pairs of the last guarded rebuild, [1] overflow flag
 
     // diagnostics scratch
     DevBuf<double> diag_partials, diag_out;
@@ -196,6 +203,8 @@ struct lg_system {
             cudaStreamDestroy(stream);
         }
         if (h_pinned) cudaFreeHost(h_pinned);
+        if (ev_bbox) cudaEventDestroy(ev_bbox);
+        if (ev_pairs) cudaEventDestroy(ev_pairs);
         for (auto& ev : prof_events) {
             cudaEventDestroy(ev.first);
             cudaEventDestroy(ev.second);
@@ -212,6 +221,9 @@ int check_async(lg_system* s) {
     if (h & ERR_SLOT_OVERFLOW)
         return fail(LG_ECAPACITY, "a particle has more simultaneous contacts than lg_set_max_contacts allows");
     if (h & ERR_BOND_LOOKUP) return fail(LG_ECAPACITY, "bond table lookup failed");
+    if (h & ERR_PAIR_CAPACITY)
+        return fail(LG_ECAPACITY, "the neighbor list grew by more than 15 % within one rebuild period and did not fit its buffers; "
+                                  "rows were emptied (call lg_update_neighbor_list again after lg_synchronize)");
     if (h & ERR_HALO_TIMEOUT) return fail(LG_ECUDA, "halo exchange: a neighbouring rank did not publish its message in time");
     return LG_OK;
 }
@@ -419,10 +431,50 @@ int step(lg_system* s, double dt) {
     return LG_OK;
 }
 
+// The exact pair count of the most recent rebuild, if its asynchronous read-back is still outstanding.
+int sync_pairs(lg_system* s) {
+    if (!s->pairs_pending) return LG_OK;
+    LG_CUDA(cudaEventSynchronize(s->ev_pairs));
+    const int64_t v = (int64_t)reinterpret_cast<const uint32_t*>(s->h_pinned + 16)[0];
+    (s->rows_staged ? s->n_pairs_new : s->n_pairs) = v;
+    s->last_total = v;
+    s->pairs_pending = false;
+    return LG_OK;
+}
+
+int grid_from_bbox(lg_system* s, const double* bb) {
+    const int n = (int)s->n;
+    NeighborGrid g{};
+    double cell = s->r_verlet * (1.0 + 1e-6);
+    const double max_cells = 16.0 * (double)n + 65536.0;
+    for (;;) {
+        double total = 1.0;
+        for (int k = 0; k < 3; k++) {
+            double ext = bb[3 + k] - bb[k];
+            if (!(ext >= 0.0) || !std::isfinite(ext)) return fail(LG_EINVAL, "non-finite particle positions");
+            double d = std::floor(ext / cell) + 1.0;
+            g.dim[k] = d > 2.0e9 ? 2000000000 : (int)d;
+            total *= d;
+        }
+        if (total <= max_cells) {
+            g.n_cells = (int64_t)g.dim[0] * g.dim[1] * g.dim[2];
+            break;
+        }
+        cell *= 1.26;
+    }
+    g.cell = cell;
+    for (int k = 0; k < 3; k++) g.lo[k] = bb[k];
+    s->grid = g;
+    s->grid_valid = true;
+    s->grid_age = 0;
+    return LG_OK;
+}
+
 int rebuild(lg_system* s) {
     if (!s->use_nl) return LG_OK;  // granular_system (all pairs) has no update_neighbor_list
     if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
     LG_TRY(ensure_slots(s));
+    LG_TRY(sync_pairs(s));  // the previous rebuild's count: long since arrived in the steady state
     // The pending evaluation belongs to the OLD rows (it closed the previous do_step).  In the steady state of the
     // fused variant it stays pending: the new rows are built next to the old ones (they depend on x only, which
     // the evaluation does not change) and are installed by evaluate() once the evaluation has run.
@@ -440,41 +492,41 @@ int rebuild(lg_system* s) {
     DevBuf<int32_t>& cols = defer ? s->cols_new : s->cols;
     DevBuf<uint8_t>& tag = defer ? s->tag_new : s->tag;
     cudaStream_t st = s->stream;
-    // 1. bounding box -> grid (reused from the previous rebuild most of the time)
-    constexpr int kGridReuse = 15;
-    NeighborGrid g{};
-    if (s->grid_valid && s->grid_age < kGridReuse) {
-        g = s->grid;
-        s->grid_age++;
-    } else {
+    if (!s->ev_bbox) {
+        LG_CUDA(cudaEventCreateWithFlags(&s->ev_bbox, cudaEventDisableTiming));
+        LG_CUDA(cudaEventCreateWithFlags(&s->ev_pairs, cudaEventDisableTiming));
+        LG_CUDA(s->pair_total.reserve(2));
+    }
+    // 1. cell grid.  cell_coords clamps, so a grid that no longer covers every particle still yields the exact rows (the
+    //    cell list is only a candidate filter, cell edge >= r_verlet): the grid is refreshed from a bounding box that
+    //    was measured at an EARLIER rebuild and has arrived in pinned memory since -- no wait.  Only the first rebuild
+    //    after new positions were set measures and waits.
+    constexpr int kGridRefresh = 4;
+    double* h_bbox = s->h_pinned + 20;  // its own pinned slots: the copy may land at any later time
+    if (!s->grid_valid) {
+        if (s->bbox_pending) {  // a measurement of positions that have been replaced since: discard
+            LG_CUDA(cudaEventSynchronize(s->ev_bbox));
+            s->bbox_pending = false;
+        }
         launch_bbox(n, s->x.p, s->bbox_scratch.p, s->bbox_out.p, st);
         LG_CUDA(cudaGetLastError());
-        LG_CUDA(cudaMemcpyAsync(s->h_pinned, s->bbox_out.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaMemcpyAsync(h_bbox, s->bbox_out.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
         LG_CUDA(cudaStreamSynchronize(st));
-        double cell = s->r_verlet * (1.0 + 1e-6);
-        const double max_cells = 16.0 * (double)n + 65536.0;
-        for (;;) {
-            double total = 1.0;
-            for (int k = 0; k < 3; k++) {
-                double ext = s->h_pinned[3 + k] - s->h_pinned[k];
-                if (!(ext >= 0.0) || !std::isfinite(ext)) return fail(LG_EINVAL, "non-finite particle positions");
-                double d = std::floor(ext / cell) + 1.0;
-                g.dim[k] = d > 2.0e9 ? 2000000000 : (int)d;
-                total *= d;
-            }
-            if (total <= max_cells) {
-                g.n_cells = (int64_t)g.dim[0] * g.dim[1] * g.dim[2];
-                break;
-            }
-            cell *= 1.26;
+        LG_TRY(grid_from_bbox(s, h_bbox));
+    } else if (s->bbox_pending) {
+        if (cudaEventQuery(s->ev_bbox) == cudaSuccess) {
+            s->bbox_pending = false;
+            LG_TRY(grid_from_bbox(s, h_bbox));
         }
-        g.cell = cell;
-        for (int k = 0; k < 3; k++) g.lo[k] = s->h_pinned[k];
-        s->last_cells = g.n_cells;
-        s->grid = g;
-        s->grid_valid = true;
+    } else if (++s->grid_age >= kGridRefresh) {
+        launch_bbox(n, s->x.p, s->bbox_scratch.p, s->bbox_out.p, st);
+        LG_CUDA(cudaGetLastError());
+        LG_CUDA(cudaMemcpyAsync(h_bbox, s->bbox_out.p, 6 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaEventRecord(s->ev_bbox, st));
+        s->bbox_pending = true;
         s->grid_age = 0;
     }
+    const NeighborGrid g = s->grid;
     s->last_cells = g.n_cells;
     // 2. histogram, scan, scatter
     const size_t nc1 = (size_t)g.n_cells + 1;
@@ -492,22 +544,38 @@ int rebuild(lg_system* s) {
     LG_CUDA(cudaMemsetAsync(row_ptr.p + n, 0, sizeof(uint32_t), st));
     launch_exclusive_scan_u32(row_ptr.p, (size_t)n + 1, s->scan_scratch.p, st);
     LG_CUDA(cudaGetLastError());
-    uint32_t total_pairs = 0;
-    LG_CUDA(cudaMemcpyAsync(&total_pairs, row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    LG_CUDA(cudaStreamSynchronize(st));
-    if ((size_t)total_pairs > cols.cap) {
-        LG_CUDA(cols.reserve((size_t)total_pairs, 1.25));
-        LG_CUDA(tag.reserve(cols.cap));
+    // The pair count sizes the column buffers.  With 15 % of headroom over the previous rebuild's count the buffers are
+    // kept, the count is read back asynchronously (consumed by the next rebuild or by whoever asks for it) and a
+    // device-side guard covers the impossible-in-practice case of a list that grew faster; otherwise wait for it.
+    uint32_t* h_total = reinterpret_cast<uint32_t*>(s->h_pinned + 16);
+    const bool async_ok = defer && s->rebuilds >= 2 && s->last_total > 0 &&
+                          (double)cols.cap >= 1.15 * (double)s->last_total + 1024.0;
+    int64_t total_pairs = 0;
+    if (async_ok) {
+        launch_pair_guard(n, row_ptr.p, (uint32_t)std::min<size_t>(cols.cap, 0xffffffffu), s->pair_total.p, s->err.p, st);
+        LG_CUDA(cudaMemcpyAsync(h_total, s->pair_total.p, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaEventRecord(s->ev_pairs, st));
+        s->pairs_pending = true;
+        total_pairs = s->last_total;  // estimate until the read-back is consumed (sync_pairs)
+    } else {
+        LG_CUDA(cudaMemcpyAsync(h_total, row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaStreamSynchronize(st));
+        total_pairs = (int64_t)h_total[0];
+        s->last_total = total_pairs;
+        if ((size_t)total_pairs > cols.cap || (double)cols.cap < 1.15 * (double)total_pairs + 1024.0) {
+            LG_CUDA(cols.reserve((size_t)((double)total_pairs * 1.3) + 2048));
+            LG_CUDA(tag.reserve(cols.cap));
+        }
     }
     launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, cols.p, owned, st);
     LG_CUDA(cudaGetLastError());
     s->rebuilds++;
     if (defer) {
-        s->n_pairs_new = (int64_t)total_pairs;
+        s->n_pairs_new = total_pairs;
         s->rows_staged = true;
         return LG_OK;
     }
-    s->n_pairs = (int64_t)total_pairs;
+    s->n_pairs = total_pairs;
     return retag(s);
 }
 
@@ -790,6 +858,7 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     if (n_check != s->n)
         return fail(LG_ESIZE, "size mismatch in arguments passed to lg_set_state (x0, v0, theta0, omega0 must hold n particles)");
     if (!x || !v || !theta || !omega) return fail(LG_EINVAL, "null state pointer");
+    LG_TRY(sync_pairs(s));
     const size_t bytes = 3 * (size_t)s->n * sizeof(double);
     LG_CUDA(cudaMemcpyAsync(s->x.p, x, bytes, cudaMemcpyHostToDevice, s->stream));
     LG_CUDA(cudaMemcpyAsync(s->v.p, v, bytes, cudaMemcpyHostToDevice, s->stream));
@@ -816,6 +885,7 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     if (s->use_nl) {
         s->n_pairs = 0;
         s->rebuilds = 0;
+        s->last_total = -1;
         LG_CUDA(cudaMemsetAsync(s->row_ptr.p, 0, ((size_t)s->n + 1) * sizeof(uint32_t), s->stream));
     } else if (s->allpairs_built) {
         LG_TRY(retag(s));
@@ -1021,6 +1091,8 @@ int lg_enable_neighbor_list(lg_system* s, double r_verlet) {
     // Contact springs are dropped when a pair leaves the list, which equals the reference's reset on a visited
     // non-overlapping evaluation only if every overlapping pair (distance < 2 r) is inside the list.
     if (r_verlet < 2.0 * s->mp.r) return fail(LG_EINVAL, "r_verlet must be at least 2 * r_part (contact range)");
+    LG_TRY(sync_pairs(s));
+    s->last_total = -1;
     s->use_nl = true;
     s->r_verlet = r_verlet;
     s->allpairs_built = false;
@@ -1077,6 +1149,7 @@ int lg_get_neighbor_count(lg_system* s, int64_t* n_pairs) {
         return LG_OK;
     }
     LG_TRY(flush(s));  // rows rebuilt behind a pending evaluation are installed by it
+    LG_TRY(sync_pairs(s));
     *n_pairs = s->n_pairs;
     return LG_OK;
 }
@@ -1089,6 +1162,7 @@ int lg_get_neighbor_rows(lg_system* s, int64_t* row_ptr, int64_t* cols) {
         LG_TRY(build_allpairs(s));
     }
     LG_TRY(flush(s));  // rows rebuilt behind a pending evaluation are installed by it
+    LG_TRY(sync_pairs(s));
     const size_t n = (size_t)s->n, p = (size_t)s->n_pairs;
     std::vector<uint32_t> hp(n + 1);
     std::vector<int32_t> hc(p);
@@ -1211,6 +1285,7 @@ int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, c
                            const double* d_a, const double* d_alpha, int kicked) {
     LG_ENTER(s);
     if (!d_x || !d_v || !d_theta || !d_omega) return fail(LG_EINVAL, "null state pointer");
+    LG_TRY(sync_pairs(s));
     const size_t bytes = 3 * (size_t)s->n * sizeof(double);
     cudaStream_t st = s->stream;
     LG_CUDA(cudaMemcpyAsync(s->x.p, d_x, bytes, cudaMemcpyDeviceToDevice, st));

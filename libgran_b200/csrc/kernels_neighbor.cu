@@ -295,6 +295,26 @@ void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cel
     g_launch_count++;
 }
 
+// Capacity check of a rebuild that runs without a host round trip: d_total[0] <- number of pairs, d_total[1] <- 1 and
+// every row emptied when they do not fit into `cap` column slots (the host learns it from the error flag at its next
+// synchronisation; nothing is written out of bounds and later kernels see empty rows).
+__global__ void pair_guard_kernel(const uint32_t* row_ptr, int n, uint32_t cap, uint32_t* d_total, int* err) {
+    const uint32_t total = row_ptr[n];
+    d_total[0] = total;
+    d_total[1] = total > cap ? 1u : 0u;
+    if (total > cap) atomicOr(err, ERR_PAIR_CAPACITY);
+}
+__global__ void __launch_bounds__(256) pair_clamp_kernel(uint32_t* row_ptr, int n, const uint32_t* d_total) {
+    if (d_total[1] == 0u) return;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i <= n) row_ptr[i] = 0u;
+}
+void launch_pair_guard(int n, uint32_t* row_ptr, uint32_t cap, uint32_t* d_total, int* err, cudaStream_t st) {
+    pair_guard_kernel<<<1, 1, 0, st>>>(row_ptr, n, cap, d_total, err);
+    pair_clamp_kernel<<<(n + 256) / 256, 256, 0, st>>>(row_ptr, n, d_total);
+    g_launch_count += 2;
+}
+
 // all-pairs loop (rotational_binary_system_omp.h:72-75): row(i) = every j != i, ascending
 __global__ void __launch_bounds__(256) allpairs_fill_kernel(int n, uint32_t* row_ptr, int32_t* cols) {
     const int i = blockIdx.x;

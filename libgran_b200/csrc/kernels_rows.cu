@@ -4,17 +4,18 @@
 // Same mathematics, same inputs and outputs as step_rows_kernel (kernels_force_tiled.cu); what changes is how the
 // bytes move:
 //   * a grid of (SMs x resident CTAs) blocks loops over tiles of RT2 consecutive particles;
-//   * a PRODUCER warp (one elected lane) keeps the next tile's inputs in flight while the compute warps work on the
-//     current one: two shared-memory stages, a full / empty mbarrier pair per stage, every contiguous range of the tile
-//     -- x (with a halo of RH2 particles either side), v, omega, theta, row / bond pointer slices, columns, tags, and
-//     now also the tile's OWN bond records: connectors (120 B each), rest lengths, partner and mirror indices -- fetched
-//     by cp.async.bulk (UBLKCP) against the stage's full barrier;
+//   * every contiguous range of a tile -- x (with a halo of RH2 particles either side), v, omega, theta, row / bond
+//     pointer slices, columns, tags, and now also the tile's OWN bond records: connectors (120 B each), rest lengths,
+//     partner and mirror indices -- arrives by cp.async.bulk (UBLKCP) against one mbarrier; the copies of tile t + 1 are
+//     issued by one thread the moment tile t's results have left the stage, and at that time they are L2 hits, because
+//     the same thread asked for them with cp.async.bulk.prefetch.L2 when tile t started.  Two CTAs share an SM and
+//     cover each other's copy phases.  (A two-stage ring with a dedicated producer warp per CTA hid the copies
+//     completely but left 8 compute warps per SM: 477 us per launch against 310 us; profiles/README.md r02b.)
 //   * pass 1 (one thread per bond record) reads its connectors from shared memory, and the mirror record too when the
 //     partner belongs to the tile (the common case inside an aggregate);
 //   * pass 2 walks each particle's row with LPP cooperating lanes (partial sums combined by shuffles, fixed order);
 //   * pass 3 integrates and moves the connectors IN the staged copy, and the results leave by bulk stores
-//     (cp.async.bulk.global.shared::cta) straight from the stage; the producer refills a stage once its stores have
-//     read it (cp.async.bulk.wait_group.read).
+//     (cp.async.bulk.global.shared::cta) straight from the stage.
 // Replaces (like the other step kernels) LT/rotational_system/rotational_binary_system_neighbors_omp.h:78-98,
 // LG/granular_system/binary_force_container.h:20-32, LG/contact_force/contact_force.h:57-147,
 // LG/hamaker_force/hamaker_force.h:28-43, LG/sinter_bridge/sinter_bridge.h:24-94,214-259 and
@@ -32,12 +33,11 @@ namespace {
 #define LG_R2_LPP 2    // lanes per particle in pass 2
 #endif
 #ifndef LG_R2_MINB
-#define LG_R2_MINB 1   // resident CTAs per SM the launch bound asks for
+#define LG_R2_MINB 2   // resident CTAs per SM the launch bound asks for
 #endif
 constexpr int RT2 = LG_R2_RT;
 constexpr int LPP = LG_R2_LPP;
 constexpr int NT2 = RT2 * LPP;        // compute threads
-constexpr int NTH2 = NT2 + 32;        // + the producer warp
 constexpr int RH2 = 128;              // halo of the staged x window (particles either side)
 constexpr int RPC2 = 12 * RT2;        // staged columns / tags per tile
 constexpr int RBC2 = 2 * RT2 + 32;    // staged bond records per tile
@@ -59,16 +59,13 @@ struct alignas(16) Stage2 {
 };
 
 struct alignas(16) Rows2Smem {
-    Stage2 st[2];
+    Stage2 st;
     double res[6 * RBC2];     // pass 1 results per bond record; pass 3: dx, dtheta of every particle
     uint8_t brow[RBC2];       // local row of every staged bond record
-    unsigned long long full[2], empty[2];
+    unsigned long long full;
 };
 
-__device__ __forceinline__ void mbar_arrive(unsigned long long* bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void compute_barrier() { asm volatile("bar.sync 1, %0;" ::"n"(NT2) : "memory"); }
+__device__ __forceinline__ void compute_barrier() { __syncthreads(); }
 
 // Bulk store shared -> global of [ssrc, ssrc + nbytes) to gdst; both addresses are congruent mod 16 (0 or 8) and nbytes is
 // a multiple of 8: the 16-byte aligned middle goes by cp.async.bulk, a leading / trailing double by an ordinary store.
@@ -86,8 +83,16 @@ __device__ __forceinline__ void bulk_store(double* gdst, const double* ssrc, uin
     if (nbytes & 8u) gdst[mid >> 3] = ssrc[mid >> 3];
 }
 
+// global -> L2 prefetch of the 16-byte aligned window around [begin, begin + nbytes)
+__device__ __forceinline__ void l2_prefetch(const void* begin, uint32_t nbytes) {
+    const uint32_t bytes = window_bytes(begin, nbytes);
+    if (bytes == 0) return;
+    const void* src = (const void*)((uintptr_t)begin & ~(uintptr_t)15u);
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
+
 template <int MASK, int MODE, bool FACETS>
-__global__ void __launch_bounds__(NTH2, LG_R2_MINB) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
+__global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
     constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
@@ -99,91 +104,92 @@ __global__ void __launch_bounds__(NTH2, LG_R2_MINB) step_rows2_kernel(const __gr
     const int n_tiles = (A.n + RT2 - 1) / RT2;
     const bool have_bonds = kSinter && A.bptr != nullptr;
 
-    if (tid == 0) {
-        for (int s = 0; s < 2; s++) {
-            mbar_init(&sm.full[s], 1);
-            mbar_init(&sm.empty[s], 1);
+    // pair / bond-record ranges of tile t: four independent loads (requested a tile ahead, consumed when its copies are issued)
+    auto load_desc = [&](int t, uint32_t d[4]) {
+        const int i0 = t * RT2, nr = min(RT2, A.n - i0);
+        d[0] = A.row_ptr[i0];
+        d[1] = A.row_ptr[i0 + nr];
+        d[2] = have_bonds ? A.bptr[i0] : 0u;
+        d[3] = have_bonds ? A.bptr[i0 + nr] : 0u;
+    };
+    // bulk copies of every contiguous range tile t reads, completion counted on sm.full (one thread)
+    auto issue_loads = [&](int tile, const uint32_t d[4]) {
+        Stage2& S = sm.st;
+        const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
+        const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
+        const double* gx = A.x + 3 * (size_t)xlo;
+        const double* gv = A.v + 3 * (size_t)i0;
+        const double* gw = A.w + 3 * (size_t)i0;
+        const double* gth = A.th + 3 * (size_t)i0;
+        const uint32_t* grow = A.row_ptr + i0;
+        const uint32_t* gbond = have_bonds ? A.bptr + i0 : nullptr;
+        const uint32_t nb3 = 24u * (uint32_t)nrows, nbp = 4u * (uint32_t)(nrows + 1), nbx = 24u * (uint32_t)xcnt;
+        const uint32_t np0 = min(d[1] - d[0], (uint32_t)RPC2);
+        const uint32_t nbr = (d[3] - d[2] <= (uint32_t)RBC2) ? d[3] - d[2] : 0u;
+        const int32_t* gcols = A.cols + d[0];
+        const uint8_t* gtag = A.tag + d[0];
+        const double* gconn = A.bconn + 15 * (size_t)d[2];
+        const double* glen = A.blen + 5 * (size_t)d[2];
+        const int32_t* gbj = A.bj + d[2];
+        const int32_t* grev = A.brev + d[2];
+        uint32_t total = window_bytes(gx, nbx) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(grow, nbp) +
+                         window_bytes(gcols, 4u * np0);
+        if constexpr (MODE == MODE_FUSED) total += window_bytes(gth, nb3);
+        if (have_bonds) total += window_bytes(gbond, nbp);
+        if constexpr (kContact) total += window_bytes(gtag, np0);
+        if (nbr)
+            total += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(gbj, 4u * nbr) +
+                     window_bytes(grev, 4u * nbr);
+        mbar_expect_tx(&sm.full, total);
+        if (nbr) {
+            bulk_load(S.wconn, gconn, 120u * nbr, &sm.full);
+            bulk_load(S.wlen, glen, 40u * nbr, &sm.full);
+            bulk_load(S.wbj, gbj, 4u * nbr, &sm.full);
+            bulk_load(S.wrev, grev, 4u * nbr, &sm.full);
         }
+        bulk_load(S.wx, gx, nbx, &sm.full);
+        bulk_load(S.wv, gv, nb3, &sm.full);
+        bulk_load(S.ww, gw, nb3, &sm.full);
+        if constexpr (MODE == MODE_FUSED) bulk_load(S.wth, gth, nb3, &sm.full);
+        bulk_load(S.wrow, grow, nbp, &sm.full);
+        if (have_bonds) bulk_load(S.wbond, gbond, nbp, &sm.full);
+        bulk_load(S.wcols, gcols, 4u * np0, &sm.full);
+        if constexpr (kContact) bulk_load(S.wtag, gtag, np0, &sm.full);
+    };
+    // the big ranges of tile t pulled into L2 (no shared memory needed): by the time the stage is free its copies are L2 hits
+    auto prefetch_tile = [&](int t, const uint32_t d[4]) {
+        const int j0 = t * RT2, nr = min(RT2, A.n - j0);
+        l2_prefetch(A.v + 3 * (size_t)j0, 24u * (uint32_t)nr);
+        l2_prefetch(A.w + 3 * (size_t)j0, 24u * (uint32_t)nr);
+        l2_prefetch(A.x + 3 * (size_t)j0, 24u * (uint32_t)nr);
+        if constexpr (MODE == MODE_FUSED) l2_prefetch(A.th + 3 * (size_t)j0, 24u * (uint32_t)nr);
+        l2_prefetch(A.cols + d[0], 4u * (d[1] - d[0]));
+        if (have_bonds && d[3] > d[2]) {
+            l2_prefetch(A.bconn + 15 * (size_t)d[2], 120u * (d[3] - d[2]));
+            l2_prefetch(A.blen + 5 * (size_t)d[2], 40u * (d[3] - d[2]));
+        }
+    };
+
+    uint32_t dn[4] = {0u, 0u, 0u, 0u};  // thread 0: ranges of the NEXT tile of this CTA
+    if (tid == 0) {
+        mbar_init(&sm.full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        uint32_t d0[4];
+        load_desc(blockIdx.x, d0);
+        issue_loads(blockIdx.x, d0);
+        if ((int)(blockIdx.x + gridDim.x) < n_tiles) load_desc(blockIdx.x + gridDim.x, dn);
     }
     __syncthreads();
 
-    if (tid >= NT2) {
-        // ================= producer: one lane keeps two tiles of inputs in flight ====================================
-        if (tid != NT2) return;
-        int tile = blockIdx.x;
-        if (tile >= n_tiles) return;
-        auto load_desc = [&](int t, uint32_t d[4]) {  // pair / bond-record ranges of tile t: four independent loads
-            const int i0 = t * RT2, nr = min(RT2, A.n - i0);
-            d[0] = A.row_ptr[i0];
-            d[1] = A.row_ptr[i0 + nr];
-            d[2] = have_bonds ? A.bptr[i0] : 0u;
-            d[3] = have_bonds ? A.bptr[i0 + nr] : 0u;
-        };
-        uint32_t d[4], dn[4] = {0u, 0u, 0u, 0u};
-        load_desc(tile, d);
-        for (int k = 0; tile < n_tiles; k++, tile += gridDim.x) {
-            const int s = k & 1;
-            const int nxt = tile + gridDim.x;
-            if (nxt < n_tiles) load_desc(nxt, dn);  // in flight while this tile's copies are issued
-            if (k >= 2) mbar_wait(&sm.empty[s], (uint32_t)(((k >> 1) - 1) & 1));
-            Stage2& S = sm.st[s];
-            const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
-            const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
-            const double* gx = A.x + 3 * (size_t)xlo;
-            const double* gv = A.v + 3 * (size_t)i0;
-            const double* gw = A.w + 3 * (size_t)i0;
-            const double* gth = A.th + 3 * (size_t)i0;
-            const uint32_t* grow = A.row_ptr + i0;
-            const uint32_t* gbond = have_bonds ? A.bptr + i0 : nullptr;
-            const uint32_t nb3 = 24u * (uint32_t)nrows, nbp = 4u * (uint32_t)(nrows + 1), nbx = 24u * (uint32_t)xcnt;
-            const uint32_t np0 = min(d[1] - d[0], (uint32_t)RPC2);
-            const uint32_t nbr = (d[3] - d[2] <= (uint32_t)RBC2) ? d[3] - d[2] : 0u;
-            const int32_t* gcols = A.cols + d[0];
-            const uint8_t* gtag = A.tag + d[0];
-            const double* gconn = A.bconn + 15 * (size_t)d[2];
-            const double* glen = A.blen + 5 * (size_t)d[2];
-            const int32_t* gbj = A.bj + d[2];
-            const int32_t* grev = A.brev + d[2];
-            uint32_t total = window_bytes(gx, nbx) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(grow, nbp) +
-                             window_bytes(gcols, 4u * np0);
-            if constexpr (MODE == MODE_FUSED) total += window_bytes(gth, nb3);
-            if (have_bonds) total += window_bytes(gbond, nbp);
-            if constexpr (kContact) total += window_bytes(gtag, np0);
-            if (nbr)
-                total += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(gbj, 4u * nbr) +
-                         window_bytes(grev, 4u * nbr);
-            mbar_expect_tx(&sm.full[s], total);
-            if (nbr) {
-                bulk_load(S.wconn, gconn, 120u * nbr, &sm.full[s]);
-                bulk_load(S.wlen, glen, 40u * nbr, &sm.full[s]);
-                bulk_load(S.wbj, gbj, 4u * nbr, &sm.full[s]);
-                bulk_load(S.wrev, grev, 4u * nbr, &sm.full[s]);
-            }
-            bulk_load(S.wx, gx, nbx, &sm.full[s]);
-            bulk_load(S.wv, gv, nb3, &sm.full[s]);
-            bulk_load(S.ww, gw, nb3, &sm.full[s]);
-            if constexpr (MODE == MODE_FUSED) bulk_load(S.wth, gth, nb3, &sm.full[s]);
-            bulk_load(S.wrow, grow, nbp, &sm.full[s]);
-            if (have_bonds) bulk_load(S.wbond, gbond, nbp, &sm.full[s]);
-            bulk_load(S.wcols, gcols, 4u * np0, &sm.full[s]);
-            if constexpr (kContact) bulk_load(S.wtag, gtag, np0, &sm.full[s]);
-#pragma unroll
-            for (int q = 0; q < 4; q++) d[q] = dn[q];
-        }
-        return;
-    }
-
-    // ===================== compute warps ==================================================================================
     const int r = tid / LPP, lp = tid % LPP;  // particle of the tile and lane within it (pass 2)
     int k = 0;
     for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, k++) {
-        const int s = k & 1;
-        Stage2& S = sm.st[s];
+        Stage2& S = sm.st;
         const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
         const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
-        mbar_wait(&sm.full[s], (uint32_t)((k >> 1) & 1));
+        const int nxt = tile + gridDim.x;
+        mbar_wait(&sm.full, (uint32_t)(k & 1));
 
         double* sxw = S.wx + (window_lead(A.x + 3 * (size_t)xlo) >> 3);  // x of particle xlo + q at sxw[3 q]
         double* sx = sxw + 3 * (i0 - xlo);
@@ -238,6 +244,7 @@ __global__ void __launch_bounds__(NTH2, LG_R2_MINB) step_rows2_kernel(const __gr
             }
         }
         compute_barrier();  // pass 1 results
+        if (tid == 0 && nxt < n_tiles) prefetch_tile(nxt, dn);  // its ranges were requested a tile ago: no wait here
 
         // ---- pass 2: LPP lanes per particle walk its row (lane l: pairs pb + l, pb + l + LPP, ...) ---------------------
         d3 acc_a = zero3(), acc_al = zero3();
@@ -379,7 +386,10 @@ __global__ void __launch_bounds__(NTH2, LG_R2_MINB) step_rows2_kernel(const __gr
             }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the stage may be overwritten
-            mbar_arrive(&sm.empty[s]);
+            if (nxt < n_tiles) {
+                issue_loads(nxt, dn);
+                if (nxt + (int)gridDim.x < n_tiles) load_desc(nxt + gridDim.x, dn);
+            }
         }
     }
     if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
@@ -389,7 +399,7 @@ int resident_ctas_rows2(const void* fn) {
     int dev = 0, sms = 0, occ = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, NTH2, sizeof(Rows2Smem));
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, NT2, sizeof(Rows2Smem));
     return sms * (occ > 0 ? occ : 1);
 }
 
@@ -401,7 +411,7 @@ void launch_rows2_one(const ForceArgs& args, cudaStream_t st) {
         grid_cap = resident_ctas_rows2((const void*)step_rows2_kernel<MASK, MODE, FACETS>);
     }
     const int n_tiles = (args.n + RT2 - 1) / RT2;
-    step_rows2_kernel<MASK, MODE, FACETS><<<min(n_tiles, grid_cap), NTH2, sizeof(Rows2Smem), st>>>(args);
+    step_rows2_kernel<MASK, MODE, FACETS><<<min(n_tiles, grid_cap), NT2, sizeof(Rows2Smem), st>>>(args);
     g_launch_count++;
 }
 

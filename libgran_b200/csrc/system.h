@@ -37,7 +37,7 @@ constexpr int kMaxBondsPerParticle = 120;
 constexpr int kMaxSlots = 120;
 
 // asynchronous error flags raised by kernels (checked at synchronisation points)
-enum : int { ERR_SLOT_OVERFLOW = 1, ERR_BOND_LOOKUP = 2, ERR_HALO_TIMEOUT = 4 };
+enum : int { ERR_SLOT_OVERFLOW = 1, ERR_BOND_LOOKUP = 2, ERR_HALO_TIMEOUT = 4, ERR_PAIR_CAPACITY = 8 };
 
 struct ModelParams {
     double r, mass, inertia;
@@ -131,6 +131,7 @@ void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* ce
 void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
                      double r_verlet, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned, cudaStream_t st);
 void launch_allpairs_fill(int n, uint32_t* row_ptr, int32_t* cols, cudaStream_t st);
+void launch_pair_guard(int n, uint32_t* row_ptr, uint32_t cap, uint32_t* d_total, int* err, cudaStream_t st);
 // recompute tag[] for every row from the slot table and the bond CSR; frees slots whose partner left the row
 void launch_retag(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
                   const uint32_t* bptr, const int32_t* bj, int* err, cudaStream_t st);
