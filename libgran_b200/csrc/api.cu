@@ -152,6 +152,9 @@ struct lg_system {
     DevBuf<double> blen;
     std::vector<uint32_t> h_bptr;
     std::vector<int32_t> h_bj;
+    // step_rows2_kernel: per tile of rows2_tile_particles() particles, the bridges to evaluate (build_bridge_work)
+    DevBuf<uint16_t> bwork;
+    DevBuf<uint32_t> bwork_cnt;
 
     // facets
     std::vector<Facet> facets;
@@ -322,6 +325,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.spr = s->spr.p; A.sgid = s->sgid.p; A.S = s->S;
     A.bptr = s->n_bonds > 0 ? s->bptr.p : nullptr;
     A.bj = s->bj.p; A.brev = s->brev.p; A.bconn = s->bconn.p; A.blen = s->blen.p;
+    A.bwork = s->bwork.p; A.bwork_cnt = s->bwork_cnt.p;
     A.mp = s->mp;
     A.n_facets = (int)facets.size();
     for (int f = 0; f < A.n_facets; f++) {
@@ -596,6 +600,44 @@ struct lg_bond_table {
 
 namespace {
 
+// Work lists of step_rows2_kernel's bridge pass.  Inside a tile of T consecutive particles every bridge whose two ends
+// both belong to the tile is evaluated ONCE, by the record with the lower index: the springs of (j, i) are those of (i, j)
+// reversed, so force_j = -force_i exactly and only the torque arm differs (sinter_bridge.h:244-256).  Item = tile-relative
+// record index, bit 15 set when the item also produces its mirror's value.  Records whose mirror lies in another tile, or
+// whose two orientations carry different rest lengths (possible with explicit tables), stay one-sided.  Tiles with more
+// records than the kernel stages get an empty list (the kernel evaluates them from global memory).
+int build_bridge_work(lg_system* s, const std::vector<uint32_t>& bptr, const std::vector<int32_t>& brev,
+                      const std::vector<double>& len) {
+    const int T = rows2_tile_particles(), cap = rows2_tile_records();
+    const size_t n = (size_t)s->n, nb = brev.size();
+    const size_t n_tiles = (n + (size_t)T - 1) / (size_t)T;
+    std::vector<uint16_t> work(nb + 16, 0);
+    std::vector<uint32_t> cnt(n_tiles + 1, 0);
+    for (size_t t = 0; t < n_tiles; t++) {
+        const size_t i0 = t * (size_t)T, i1 = std::min(n, i0 + (size_t)T);
+        const uint32_t b0 = bptr[i0], b1 = bptr[i1];
+        if (b1 - b0 > (uint32_t)cap) continue;
+        uint32_t w = 0;
+        for (uint32_t b = b0; b < b1; b++) {
+            const uint32_t m = (uint32_t)brev[b];
+            const bool in_tile = m >= b0 && m < b1;
+            const bool same_len = in_tile && std::memcmp(&len[5 * (size_t)b], &len[5 * (size_t)m], 5 * sizeof(double)) == 0;
+            if (in_tile && same_len) {
+                if (b < m) work[b0 + w++] = (uint16_t)((b - b0) | 0x8000u);
+            } else {
+                work[b0 + w++] = (uint16_t)(b - b0);
+            }
+        }
+        cnt[t] = w;
+    }
+    LG_CUDA(s->bwork.reserve(nb + 16));
+    LG_CUDA(s->bwork_cnt.reserve(n_tiles + 1));
+    LG_CUDA(cudaMemcpyAsync(s->bwork.p, work.data(), (nb + 16) * sizeof(uint16_t), cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaMemcpyAsync(s->bwork_cnt.p, cnt.data(), (n_tiles + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    return LG_OK;
+}
+
 int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
     // CSR by (i, j) ascending
     std::sort(recs.begin(), recs.end(), [](HostBond const& a, HostBond const& b) { return a.i != b.i ? a.i < b.i : a.j < b.j; });
@@ -637,6 +679,7 @@ int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
         LG_CUDA(cudaMemcpyAsync(s->blen.p, len.data(), nb * 5 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
     }
     LG_CUDA(cudaStreamSynchronize(s->stream));
+    LG_TRY(build_bridge_work(s, bptr, brev, len));
     s->n_bonds = (int64_t)nb;
     s->h_bptr = std::move(bptr);
     s->h_bj = std::move(bj);
@@ -1370,7 +1413,8 @@ int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, doubl
     LG_CUDA(s->blen.reserve((size_t)nb * 5 + 16));
     LG_CUDA(cudaMemcpyAsync(s->bptr.p, d_bptr, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     std::vector<uint32_t> bptr(n + 1);
-    std::vector<int32_t> bj((size_t)nb);
+    std::vector<int32_t> bj((size_t)nb), h_brev((size_t)nb);
+    std::vector<double> h_len((size_t)nb * 5);
     LG_CUDA(cudaMemcpyAsync(bptr.data(), d_bptr, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     if (nb) {
         LG_CUDA(cudaMemcpyAsync(s->bj.p, d_bj, (size_t)nb * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
@@ -1378,9 +1422,14 @@ int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, doubl
         LG_CUDA(cudaMemcpyAsync(s->bconn.p, d_bconn, (size_t)nb * 15 * sizeof(double), cudaMemcpyDeviceToDevice, st));
         LG_CUDA(cudaMemcpyAsync(s->blen.p, d_blen, (size_t)nb * 5 * sizeof(double), cudaMemcpyDeviceToDevice, st));
         LG_CUDA(cudaMemcpyAsync(bj.data(), d_bj, (size_t)nb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaMemcpyAsync(h_brev.data(), d_brev, (size_t)nb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaMemcpyAsync(h_len.data(), d_blen, (size_t)nb * 5 * sizeof(double), cudaMemcpyDeviceToHost, st));
     }
     LG_CUDA(cudaStreamSynchronize(st));
     if (bptr[n] != (uint32_t)nb) return fail(LG_EINVAL, "bptr[n] does not match the number of bond records");
+    for (size_t b = 0; b < (size_t)nb; b++)
+        if (h_brev[b] < 0 || h_brev[b] >= (int32_t)nb) return fail(LG_EINVAL, "mirror index out of range");
+    LG_TRY(build_bridge_work(s, bptr, h_brev, h_len));
     for (size_t i = 0; i < n; i++)
         if (bptr[i + 1] - bptr[i] > (uint32_t)kMaxBondsPerParticle) return fail(LG_ECAPACITY, "more than 120 bonds on one particle");
     to_cp(contact, s->mp.cp);

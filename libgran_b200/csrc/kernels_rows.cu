@@ -55,6 +55,7 @@ struct alignas(16) Stage2 {
     int32_t wcols[RPC2 + 8];
     int32_t wbj[RBC2 + 8];
     int32_t wrev[RBC2 + 8];
+    uint16_t wwork[RBC2 + 16];
     uint8_t wtag[RPC2 + 32];
 };
 
@@ -63,6 +64,7 @@ struct alignas(16) Rows2Smem {
     double res[6 * RBC2];     // pass 1 results per bond record; pass 3: dx, dtheta of every particle
     uint8_t brow[RBC2];       // local row of every staged bond record
     unsigned long long full;
+    uint32_t nwork;           // bridge work items of the staged tile
 };
 
 __device__ __forceinline__ void compute_barrier() { __syncthreads(); }
@@ -132,6 +134,7 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
         const double* glen = A.blen + 5 * (size_t)d[2];
         const int32_t* gbj = A.bj + d[2];
         const int32_t* grev = A.brev + d[2];
+        const uint16_t* gwork = A.bwork + d[2];
         uint32_t total = window_bytes(gx, nbx) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(grow, nbp) +
                          window_bytes(gcols, 4u * np0);
         if constexpr (MODE == MODE_FUSED) total += window_bytes(gth, nb3);
@@ -139,13 +142,15 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
         if constexpr (kContact) total += window_bytes(gtag, np0);
         if (nbr)
             total += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(gbj, 4u * nbr) +
-                     window_bytes(grev, 4u * nbr);
+                     window_bytes(grev, 4u * nbr) + window_bytes(gwork, 2u * nbr);
+        sm.nwork = nbr ? A.bwork_cnt[tile] : 0u;  // published to the other threads by the barrier's release / acquire
         mbar_expect_tx(&sm.full, total);
         if (nbr) {
             bulk_load(S.wconn, gconn, 120u * nbr, &sm.full);
             bulk_load(S.wlen, glen, 40u * nbr, &sm.full);
             bulk_load(S.wbj, gbj, 4u * nbr, &sm.full);
             bulk_load(S.wrev, grev, 4u * nbr, &sm.full);
+            bulk_load(S.wwork, gwork, 2u * nbr, &sm.full);
         }
         bulk_load(S.wx, gx, nbx, &sm.full);
         bulk_load(S.wv, gv, nb3, &sm.full);
@@ -208,6 +213,7 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
         const double* slen = S.wlen + (window_lead(A.blen + 5 * (size_t)b0) >> 3);
         const int32_t* sbj = S.wbj + (window_lead(A.bj + b0) >> 2);
         const int32_t* srev = S.wrev + (window_lead(A.brev + b0) >> 2);
+        const uint16_t* swork = S.wwork + (window_lead(A.bwork + b0) >> 1);
 
         auto neighbour = [&](int j, const double* sp, const double* gsrc) -> d3 {  // v, omega: own particles staged
             const unsigned rj = (unsigned)(j - i0);
@@ -218,28 +224,53 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
             return rj < (unsigned)xcnt ? load3(sxw + 3 * rj) : load3(A.x + 3 * (size_t)j);
         };
 
-        // ---- pass 1: one thread per bond record, operands from the stage -------------------------------------------
+        // ---- pass 1: one thread per bridge work item, operands from the stage.  An item is a bond record (i, j) of the
+        //      tile; when its mirror (j, i) is in the tile as well (97 % of the records of config 4) the item carries bit 15
+        //      and the thread produces BOTH records' values from one evaluation of the five springs -----------------------
         if constexpr (kSinter) {
             if (bonds_staged) {
                 if (tid < nrows)
                     for (uint32_t b = sbptr[tid]; b < sbptr[tid + 1]; b++) sm.brow[b - b0] = (uint8_t)tid;
                 compute_barrier();
-                for (uint32_t bl = tid; bl < nbond; bl += NT2) {
+                const uint32_t nwork = sm.nwork;
+                const bool damped = A.mp.gamma_d != 0.0;
+                for (uint32_t wq = tid; wq < nwork; wq += NT2) {
+                    const uint32_t item = swork[wq];
+                    const uint32_t bl = item & 0x7fffu;
+                    const bool paired = (item & 0x8000u) != 0u;
                     const int rr = sm.brow[bl];
                     const int j = sbj[bl];
                     const uint32_t ml = (uint32_t)srev[bl] - b0;
                     const double* ci = sconn + 15 * bl;
-                    const double* cj = ml < nbond ? sconn + 15 * ml : A.bconn + (size_t)srev[bl] * 15;
+                    const double* cj = paired ? sconn + 15 * ml : A.bconn + (size_t)srev[bl] * 15;
                     const double* len = slen + 5 * bl;
                     const d3 xi = load3(sx + 3 * rr), xj = neighbour_x(j);
-                    d3 fa, ta;
-                    if (A.mp.gamma_d != 0.0)
-                        bridge_fast<true>(A, ci, cj, len, xi, xj, load3(sv + 3 * rr), neighbour(j, sv, A.v), load3(sw + 3 * rr),
-                                          neighbour(j, sw, A.w), fa, ta);
-                    else
-                        bridge_fast<false>(A, ci, cj, len, xi, xj, zero3(), zero3(), zero3(), zero3(), fa, ta);
+                    d3 vi = zero3(), vj = zero3(), wi = zero3(), wj = zero3();
+                    if (damped) {
+                        vi = load3(sv + 3 * rr);
+                        vj = neighbour(j, sv, A.v);
+                        wi = load3(sw + 3 * rr);
+                        wj = neighbour(j, sw, A.w);
+                    }
+                    d3 force = zero3(), ti = zero3(), tj = zero3();
+                    if (damped) {
+#pragma unroll RBU
+                        for (int q = 0; q < 5; q++)
+                            bonded_spring_pair_fast<true>(A.mp.k_d, A.mp.gamma_d, len[q], load3(ci + 3 * q), load3(cj + 3 * q), xi, xj,
+                                                          vi, vj, wi, wj, force, ti, tj);
+                    } else {
+#pragma unroll RBU
+                        for (int q = 0; q < 5; q++)
+                            bonded_spring_pair_fast<false>(A.mp.k_d, 0.0, len[q], load3(ci + 3 * q), load3(cj + 3 * q), xi, xj, vi, vj,
+                                                           wi, wj, force, ti, tj);
+                    }
+                    const d3 fa = force * A.fc.inv_mass;
                     store3(sm.res + 6 * bl, fa);
-                    store3(sm.res + 6 * bl + 3, ta);
+                    store3(sm.res + 6 * bl + 3, ti * A.fc.inv_inertia);
+                    if (paired) {
+                        store3(sm.res + 6 * ml, -fa);
+                        store3(sm.res + 6 * ml + 3, tj * A.fc.inv_inertia);
+                    }
                 }
             }
         }
@@ -433,6 +464,9 @@ void launch_rows2_mode(const ForceArgs& args, int mask, cudaStream_t st) {
 }
 
 }  // namespace
+
+int rows2_tile_particles() { return RT2; }
+int rows2_tile_records() { return RBC2; }
 
 void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {
     if (fused) launch_rows2_mode<MODE_FUSED>(args, mask, st); else launch_rows2_mode<MODE_FORCE>(args, mask, st);

@@ -36,7 +36,8 @@ struct Accel {
 LG_HD Accel operator+(Accel l, Accel r) { return Accel{l.a + r.a, l.alpha + r.alpha}; }
 LG_HD Accel zero_accel() { return Accel{zero3(), zero3()}; }
 
-enum : int { MODEL_CONTACT = 1, MODEL_HAMAKER = 2, MODEL_SINTER = 4, MODEL_FACET = 8 };
+enum : int { MODEL_CONTACT = 1, MODEL_HAMAKER = 2, MODEL_SINTER = 4, MODEL_FACET = 8, MODEL_ALT_SINTER = 16 };
+enum : int { HAMAKER_STANDARD = 0, HAMAKER_LIMITED_RANGE = 1, HAMAKER_SIMPLIFIED = 2 };
 
 // Separation geometry shared by the contact and Hamaker laws of one ordered pair (i, j):
 // contact uses n = normalized(x_i - x_j) (contact_force.h:65), Hamaker uses normalized(x_j - x_i)
@@ -130,10 +131,54 @@ LG_HD Accel wall_contact_force(const ContactParams& p, double r, double mass, do
     return Accel{(f_n * n + f_t) / mass, (((-tau_t) + tau_r) + tau_o) / inertia};
 }
 
+// Bonded pair of alt_sinter_functor (LG/sinter_bridge/alt_sinter_bridge.h:92-160): the contact kinematics with the
+// bond's own stiffnesses, NO overlap test (the bond also pulls), no Coulomb limit -- the three springs always grow by
+// v_rel * dt after the test force is taken.  b = {k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o}.
+LG_HD d3 alt_shear_spring(d3& xi, d3 n, double stiffness, double damping, d3 rel_v, double dt) {
+    d3 xi_new = xi - dot(xi, n) * n;
+    double z_new = dot(xi_new, xi_new);
+    if (sqrt(z_new) > 0.0) {
+        xi_new = xi_new / sqrt(z_new);
+        xi_new = xi_new * norm(xi);
+    }
+    xi = xi_new;
+    d3 f_0 = (-stiffness) * xi - damping * rel_v;
+    xi = xi + rel_v * dt;
+    return f_0;
+}
+LG_HD Accel alt_bonded_force(const double* b, double dt, double r, double mass, double inertia, const PairGeom& g, d3 vi, d3 vj,
+                             d3 wi, d3 wj, Springs& s) {
+    d3 n = g.n;
+    double overlap = 2.0 * r - dot(g.dx, n);
+    double r_prime = r - overlap / 2.0;
+    double v_n = -dot(vi - vj, n);
+    double f_n = b[0] * overlap + b[1] * v_n;
+    d3 ncwi = cross(n, wi), ncwj = cross(n, wj);
+    d3 v_ij = ((vi - vj) + r_prime * ncwi) + r_prime * ncwj;
+    d3 v_t = v_ij - dot(v_ij, n) * n;
+    d3 v_r = (-r_prime) * (ncwi - ncwj);
+    d3 v_o = (r * (dot(n, wi) - dot(n, wj))) * n;
+    d3 f_t = alt_shear_spring(s.xi[0], n, b[2], b[3], v_t, dt);
+    d3 f_r = alt_shear_spring(s.xi[1], n, b[4], b[5], v_r, dt);
+    d3 f_o = alt_shear_spring(s.xi[2], n, b[6], b[7], v_o, dt);
+    d3 tau_t = r_prime * cross(n, f_t);
+    d3 tau_r = r * cross(n, f_r);
+    d3 tau_o = r * f_o;
+    return Accel{(f_n * n + f_t) / mass, (((-tau_t) + tau_r) + tau_o) / inertia};
+}
+
 // Hamaker sphere-sphere attraction on i from j; g is the geometry of (i, j) so x_j - x_i = -g.dx.
-LG_HD d3 hamaker_accel(double A, double h0, double r, double mass, const PairGeom& g) {
+// kind: hamaker_functor | limited_range_hamaker_functor (zero beyond `cutoff` between centres,
+// limited_range_hamaker_force.h:34-35) | simplified_hamaker_functor (2 A r / h^2, simplified_hamaker_force.h:27).
+LG_HD d3 hamaker_accel(double A, double h0, double r, double mass, const PairGeom& g, int kind = HAMAKER_STANDARD,
+                       double cutoff = 0.0) {
+    if (kind == HAMAKER_LIMITED_RANGE && g.len > cutoff) return zero3();
     double h = g.len - 2.0 * r;
     if (h < h0) h = h0;
+    if (kind == HAMAKER_SIMPLIFIED) {
+        d3 fs = (2.0 * A * r / square(h)) * (-g.n);
+        return fs / mass;
+    }
     double coef = -A / 6.0 *
                   ((4.0 * r + 2.0 * h) / (4.0 * r + h) / h - 2.0 / (2.0 * r + h) - 4.0 * square(r) / cube(2.0 * r + h) -
                    2.0 * square(r) * (4.0 * r + 2.0 * h) / square(4.0 * r + h) / square(h));
@@ -181,26 +226,40 @@ __device__ __forceinline__ d3 cross_fma(d3 a, d3 b) {
 // hardware seed (MUFU.RCP64H / MUFU.RSQ64H, >= 20 bits) refined by Newton steps to ~1 ulp.  Unlike 1.0 / x and rsqrt(x)
 // there is no special-case slow path, hence no CALL in the instruction stream: a call inside the pair loop makes the
 // compiler park the loop's accumulators in local memory (profiles/README.md r01f).
+// ITER Newton steps: the seed carries >= 20 good bits, each step doubles them (20 -> 40 -> 80), so two steps reach the
+// last bit or two of a double -- enough wherever 1e-10 is asked (directions, Hamaker); three where the result feeds a
+// cancelling difference (bridge spring lengths, refined once more there).
+template <int ITER = 2>
 __device__ __forceinline__ double rcp_nr(double x) {
     double y;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
-    double e = fma(-x, y, 1.0);
-    y = fma(y, e, y);
-    e = fma(-x, y, 1.0);
-    y = fma(y, e, y);
-    e = fma(-x, y, 1.0);
-    return fma(y, e, y);
+#pragma unroll
+    for (int k = 0; k < ITER; k++) {
+        const double e = fma(-x, y, 1.0);
+        y = fma(y, e, y);
+    }
+    return y;
 }
+template <int ITER = 2>
 __device__ __forceinline__ double rsqrt_nr(double x) {
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
     const double hx = 0.5 * x;
-    double e = fma(-hx * y, y, 0.5);   // 0.5 (1 - x y^2)
-    y = fma(y, e, y);
-    e = fma(-hx * y, y, 0.5);
-    y = fma(y, e, y);
-    e = fma(-hx * y, y, 0.5);
-    return fma(y, e, y);
+#pragma unroll
+    for (int k = 0; k < ITER; k++) {
+        const double e = fma(-hx * y, y, 0.5);   // 0.5 (1 - x y^2)
+        y = fma(y, e, y);
+    }
+    return y;
+}
+// sqrt(z) and 1 / sqrt(z) for z >= 0 without the library's special-case path: g = z y refined by the residual z - g^2
+// (the closing step of the correctly rounded square root; the result is the correctly rounded one except for arguments
+// within ~2^-100 of a rounding tie).  z == 0 -> both 0 (a coincident connector pair contributes no force).
+__device__ __forceinline__ void sqrt_and_rsqrt(double z, double& root, double& inv) {
+    const double y = z > 0.0 ? rsqrt_nr<3>(z) : 0.0;
+    const double g = z * y;
+    root = fma(0.5 * y, fma(-g, g, z), g);
+    inv = y;
 }
 
 __device__ __forceinline__ PairGeom pair_geometry_fast(d3 xi, d3 xj) {
@@ -220,10 +279,15 @@ struct FastConsts {
     double r2, r4, h0;
     double two_r, band;  // contact decision: |2r - len| < band is re-taken on the exact expression
     double inv_mass, inv_inertia;
+    int kind;            // HAMAKER_*
+    double cutoff;       // limited range: zero beyond this centre distance
+    double c_simple;     // simplified: 2 A r / mass
 };
-inline FastConsts fast_consts(double A, double h0, double r, double mass, double inertia) {
+inline FastConsts fast_consts(double A, double h0, double r, double mass, double inertia, int kind = HAMAKER_STANDARD,
+                              double cutoff = 0.0) {
     const double r3 = r * r * r;
-    return FastConsts{A / 6.0 * 64.0 * r3 * r3 / mass, 2.0 * r, 4.0 * r, h0, 2.0 * r, 1e-12 * r, 1.0 / mass, 1.0 / inertia};
+    return FastConsts{A / 6.0 * 64.0 * r3 * r3 / mass, 2.0 * r, 4.0 * r, h0, 2.0 * r, 1e-12 * r, 1.0 / mass, 1.0 / inertia,
+                      kind, cutoff, 2.0 * A * r / mass};
 }
 typedef FastConsts HamakerFast;
 #if defined(__CUDACC__)
@@ -231,6 +295,13 @@ typedef FastConsts HamakerFast;
 __device__ __forceinline__ d3 hamaker_accel_fast(const HamakerFast& hf, const PairGeom& g) {
     double h = g.len - hf.r2;
     if (h < hf.h0) h = hf.h0;
+    if (hf.kind != HAMAKER_STANDARD) {  // uniform over the launch: no divergence
+        if (hf.kind == HAMAKER_LIMITED_RANGE) {
+            if (g.len > hf.cutoff) return zero3();
+        } else {
+            return (-(hf.c_simple * rcp_nr(h * h))) * g.n;
+        }
+    }
     const double s = hf.r2 + h, q = hf.r4 + h;
     const double hq = h * q;
     const double den = (hq * hq) * (s * s * s);
@@ -241,12 +312,12 @@ __device__ __forceinline__ d3 hamaker_accel_fast(const HamakerFast& hf, const Pa
 template <bool DAMPED>
 __device__ __forceinline__ void bonded_spring_fast(double k_d, double gamma_d, double eq, d3 ci, d3 cj, d3 xi, d3 xj, d3 vi,
                                                    d3 vj, d3 wi, d3 wj, d3& force, d3& torque) {
-    // The stretch (length - eq) cancels to ~1e-5 of the length near equilibrium, so the length keeps the
-    // reference's exact value (same sum order, IEEE sqrt); only the direction uses a shared reciprocal.
+    // The stretch (length - eq) cancels to ~1e-5 of the length near equilibrium, so the length is computed to the
+    // reference's value (same sum order, correctly rounded square root: sqrt_and_rsqrt); the direction shares its reciprocal.
     const d3 spring = cj - ci;
     const double z = dot(spring, spring);
-    const double spring_length = sqrt(z);
-    const double inv = z > 0.0 ? 1.0 / spring_length : 0.0;
+    double spring_length, inv;
+    sqrt_and_rsqrt(z, spring_length, inv);
     const d3 arm = ci - xi;
     d3 dforce = (((-(eq - spring_length)) * k_d) * inv) * spring;
     if constexpr (DAMPED) {
@@ -257,6 +328,26 @@ __device__ __forceinline__ void bonded_spring_fast(double k_d, double gamma_d, d
     }
     force += dforce;
     torque += cross_fma(arm, dforce);
+}
+
+// Both orientations of one bridge in one pass (step_rows2_kernel, both ends in the same tile): the springs of (j, i) are
+// those of (i, j) reversed, so dF_ji = -dF_ij exactly; force_j = -force_i, torque_j = sum (c_j - x_j) x (-dF).
+template <bool DAMPED>
+__device__ __forceinline__ void bonded_spring_pair_fast(double k_d, double gamma_d, double eq, d3 ci, d3 cj, d3 xi, d3 xj, d3 vi,
+                                                        d3 vj, d3 wi, d3 wj, d3& force, d3& torque_i, d3& torque_j) {
+    const d3 spring = cj - ci;
+    const double z = dot(spring, spring);
+    double spring_length, inv;
+    sqrt_and_rsqrt(z, spring_length, inv);
+    const d3 arm_i = ci - xi, arm_j = cj - xj;
+    d3 dforce = (((-(eq - spring_length)) * k_d) * inv) * spring;
+    if constexpr (DAMPED) {
+        const d3 rel_v = (vj + cross_fma(wj, arm_j)) - (vi + cross_fma(wi, arm_i));
+        dforce = d3{fma(gamma_d, rel_v.x, dforce.x), fma(gamma_d, rel_v.y, dforce.y), fma(gamma_d, rel_v.z, dforce.z)};
+    }
+    force += dforce;
+    torque_i += cross_fma(arm_i, dforce);
+    torque_j = torque_j - cross_fma(arm_j, dforce);
 }
 #endif
 

@@ -44,6 +44,11 @@ struct ModelParams {
     ContactParams cp;
     double hamaker_A, hamaker_h0;
     double k_d, gamma_d;
+    // SURVEY.md section 8f variants
+    int hamaker_kind;       // HAMAKER_*
+    double hamaker_cutoff;
+    int alt_bonds;          // the bond table belongs to alt_sinter_functor: no connectors, three springs per ordered bond
+    double alt[8];          // its k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o
 };
 
 struct ForceArgs {
@@ -64,6 +69,13 @@ struct ForceArgs {
     const int32_t* brev;
     const double* bconn;
     const double* blen;
+    double* bspr;               // alt_sinter: 9 doubles per ordered bond record (its three springs), updated in place
+    int fixed;                  // fixed_particle_step_handler: this particle's velocity increments are dropped (-1: none)
+    int central_on;             // central_attraction_functor (unary): a += k_a / m * (x_i - x0)
+    double central_k;
+    d3 central_x0;
+    const uint16_t* bwork;      // step_rows2_kernel: bridge work items per tile (api.cu: build_bridge_work)
+    const uint32_t* bwork_cnt;  // items per tile
     ModelParams mp;
     int n_facets;
     Facet facets[kMaxFacets];
@@ -95,6 +107,8 @@ struct IntegrateArgs {
     double* bconn;
     int64_t n_bonds;       // ordered bonds
     double dt;
+    int scheme;            // 0 velocity-Verlet half (leap-frog), 1 forward Euler with the two-term Taylor position update
+    int fixed;             // particle whose increment_v is dropped, -1 none
 };
 
 struct NeighborGrid {
@@ -112,10 +126,12 @@ void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st)
 // tiled kernel: force only (fused == false) or force + integrate into the next-step buffers (fused == true)
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st);
 void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st);  // kernels_rows.cu
+int rows2_tile_particles();
+int rows2_tile_records();
 int tiled_max_rows_per_block();
 int tiled_tile_pairs();
 void launch_integrate(const IntegrateArgs& args, cudaStream_t st);
-void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, cudaStream_t st);
+void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, int fixed, cudaStream_t st);
 
 // bounding box of x -> d_out[6] = {min xyz, max xyz}
 void launch_bbox(int n, const double* x, double* d_scratch, double* d_out, cudaStream_t st);

@@ -16,7 +16,9 @@ from typing import Tuple
 
 import numpy as np
 
-MODEL_CONTACT, MODEL_HAMAKER, MODEL_SINTER, MODEL_FACET = 1, 2, 4, 8
+MODEL_CONTACT, MODEL_HAMAKER, MODEL_SINTER, MODEL_FACET, MODEL_ALT_SINTER = 1, 2, 4, 8, 16
+HAMAKER_STANDARD, HAMAKER_LIMITED_RANGE, HAMAKER_SIMPLIFIED = 0, 1, 2
+INTEGRATOR_VERLET_HALF, INTEGRATOR_FORWARD_EULER = 0, 1
 
 R_PART = 1.4e-8
 RHO = 1700.0
@@ -63,6 +65,12 @@ class DemConfig:
     surf_h0: float = 1.0e-9
     dt: float = DT
     rebuild_every: int = 20
+    # SURVEY.md section 8f variants
+    alt_bond: Tuple[float, ...] = (0.0,) * 8   # alt_sinter_functor: k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o
+    hamaker_kind: int = 0
+    hamaker_cutoff: float = 0.0
+    integrator: int = 0
+    fixed_particle: int = -1
 
     def with_(self, **kw) -> "DemConfig":
         return replace(self, **kw)
@@ -132,6 +140,20 @@ def sintered_lattice(models: int = MODEL_SINTER, neighbor_list: bool = False) ->
     n = len(x0)
     cfg = DemConfig(n=n, model_mask=models, use_neighbor_list=neighbor_list, rng_seed=0)
     return Scenario("sintered_lattice", cfg, x0, v0, _zeros(n), _zeros(n))
+
+
+def alt_sintered_lattice(neighbor_list: bool = False, hamaker: bool = False) -> Scenario:
+    """3x3x3 lattice bonded by alt_sinter_functor (test/alt_sintered.cpp:43-113): dt = 5e-14, bond stiffness 1000 with
+    critical damping, the embedded contact model with the common parameters."""
+    base = sintered_lattice()
+    dt = 5e-14
+    k_bond = 1000.0
+    gamma_n_bond = 2.0 * math.sqrt(2.0 * MASS * k_bond)
+    alt = (k_bond, gamma_n_bond, k_bond, 0.2 * gamma_n_bond, k_bond, 0.05 * gamma_n_bond, k_bond, 0.05 * gamma_n_bond)
+    models = MODEL_ALT_SINTER | (MODEL_HAMAKER if hamaker else 0)
+    cfg = DemConfig(n=base.cfg.n, model_mask=models, use_neighbor_list=neighbor_list, contact=contact_params(dt=dt), dt=dt,
+                    alt_bond=alt, critical_separation=1.0e-9)
+    return Scenario("alt_sintered_lattice", cfg, base.x0, base.v0, base.theta0, base.omega0)
 
 
 def surface_drop() -> Scenario:

@@ -22,7 +22,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
-MODEL_CONTACT, MODEL_HAMAKER, MODEL_SINTER, MODEL_FACET = 1, 2, 4, 8
+MODEL_CONTACT, MODEL_HAMAKER, MODEL_SINTER, MODEL_FACET, MODEL_ALT_SINTER = 1, 2, 4, 8, 16
 FIELD_X, FIELD_V, FIELD_A, FIELD_THETA, FIELD_OMEGA, FIELD_ALPHA = range(6)
 FIELDS = {"x": 0, "v": 1, "a": 2, "theta": 3, "omega": 4, "alpha": 5}
 
@@ -50,6 +50,11 @@ class DemConfigStruct(C.Structure):
         ("surf_contact", C.c_double * 15),
         ("surf_A", C.c_double),
         ("surf_h0", C.c_double),
+        ("alt_bond", C.c_double * 8),
+        ("hamaker_kind", C.c_int32),
+        ("integrator", C.c_int32),
+        ("hamaker_cutoff", C.c_double),
+        ("fixed_particle", C.c_int64),
     ]
 
 
@@ -73,6 +78,12 @@ def to_struct(cfg) -> DemConfigStruct:
     for k, val in enumerate(cfg.surf_contact):
         s.surf_contact[k] = float(val)
     s.surf_A, s.surf_h0 = float(cfg.surf_A), float(cfg.surf_h0)
+    for k, val in enumerate(getattr(cfg, "alt_bond", (0.0,) * 8)):
+        s.alt_bond[k] = float(val)
+    s.hamaker_kind = int(getattr(cfg, "hamaker_kind", 0))
+    s.integrator = int(getattr(cfg, "integrator", 0))
+    s.hamaker_cutoff = float(getattr(cfg, "hamaker_cutoff", 0.0))
+    s.fixed_particle = int(getattr(cfg, "fixed_particle", -1))
     return s
 
 

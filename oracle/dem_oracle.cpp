@@ -5,7 +5,7 @@
 // (72 B * N^2 contact springs, contact_force.h:53; 232 B * N^2 with sinter bridges,
 // sinter_bridge.h:139-141) do not fit in memory.  Parity is PINNED: the restatement is proven
 // bit-identical to the unmodified reference (oracle/_ref/libref_oracle.so) by
-// tests/test_oracle_vs_reference.py and against the committed golden vectors by tests/test_golden.py.
+// tests/test_oracle.py (live lock-step against the reference and against the committed golden vectors).
 //
 // Compile with -ffp-contract=off (oracle/Makefile): every expression below spells out the
 // evaluation order of the corresponding Eigen expression in the reference, including
@@ -28,6 +28,11 @@
 //   deps/libtimestep/.../rotational_binary_system_neighbors_omp.h:69-116 -> evaluate, update_neighbor_list
 //   deps/libtimestep/.../rotational_velocity_verlet_half.h:43-76    -> do_step
 //   test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26   -> orc_diagnostics
+// SURVEY.md section 8f variants:
+//   include/libgran/sinter_bridge/alt_sinter_bridge.h:56-156        -> build_alt_bonds, alt_pair
+//   include/libgran/hamaker_force/limited_range_hamaker_force.h:29-47, simplified_hamaker_force.h:18-30 -> hamaker_pair
+//   deps/libtimestep/.../rotational_forward_euler.h:44-63           -> do_step_forward_euler
+//   Writerside/topics/Custom-step-handler.md:48-146 (fixed_particle_step_handler: increment_v skipped) -> fixed_particle
 #include "dem_oracle.h"
 
 #include <algorithm>
@@ -194,7 +199,8 @@ struct Oracle {
     int64_t n;
     double r, mass, inertia;
     ContactParams cp, sp;
-    bool has_contact, has_hamaker, has_sinter, has_facet, neigh;
+    bool has_contact, has_hamaker, has_sinter, has_facet, has_alt, neigh;
+    std::vector<std::vector<SpringRec>> alt_springs;  // per-i springs of the alt-bonded ordered pairs (i, j), ascending j
     bool brute_force = false;
     std::vector<V3> x, v, a, theta, omega, alpha;
     std::vector<std::vector<int64_t>> rows;      // neighbor rows (ascending j); all-pairs mode leaves them empty
@@ -214,6 +220,7 @@ struct Oracle {
         has_hamaker = (c.model_mask & DEM_MODEL_HAMAKER) != 0;
         has_sinter = (c.model_mask & DEM_MODEL_SINTER) != 0;
         has_facet = (c.model_mask & DEM_MODEL_FACET) != 0;
+        has_alt = (c.model_mask & DEM_MODEL_ALT_SINTER) != 0;
         neigh = c.use_neighbor_list != 0;
         auto load = [&](std::vector<V3>& dst, const double* src) {
             dst.resize((size_t)n);
@@ -231,6 +238,88 @@ struct Oracle {
             wall_springs.assign((size_t)n, z);
         }
         if (has_sinter) build_bonds();
+        if (has_alt) build_alt_bonds();
+    }
+
+    // ---- alt_sinter_bridge.h:56-89: bonds with |dist - 2 r| < critical_separation (strict), i < j in lexicographic
+    //      order, a bond that would close a cycle is skipped (:70-73; the subset relabelling of :83-87 is a union-find
+    //      "same component?" test) --------------------------------------------------------------------------------------
+    void build_alt_bonds() {
+        alt_springs.resize((size_t)n);
+        const double crit = cfg.critical_separation;
+        std::vector<std::vector<int64_t>> cand((size_t)n);
+        if (n <= 2048 || brute_force) {
+            for (int64_t i = 0; i < n - 1; i++)
+                for (int64_t j = i + 1; j < n; j++) cand[(size_t)i].push_back(j);
+        } else {
+            for_each_near(2.0 * r + crit, [&](int64_t i, int64_t j) {
+                if (j > i) cand[(size_t)i].push_back(j);
+            });
+            for (auto& row : cand) std::sort(row.begin(), row.end());
+        }
+        std::vector<int64_t> parent((size_t)n);
+        for (int64_t i = 0; i < n; i++) parent[(size_t)i] = i;
+        auto find = [&](int64_t a0) {
+            int64_t root = a0;
+            while (parent[(size_t)root] != root) root = parent[(size_t)root];
+            while (parent[(size_t)a0] != root) {
+                int64_t nx = parent[(size_t)a0];
+                parent[(size_t)a0] = root;
+                a0 = nx;
+            }
+            return root;
+        };
+        for (int64_t i = 0; i < n - 1; i++)
+            for (int64_t j : cand[(size_t)i]) {
+                if (!(std::fabs(norm(sub(x[(size_t)i], x[(size_t)j])) - 2.0 * r) < crit)) continue;
+                const int64_t ri = find(i), rj = find(j);
+                if (ri == rj) continue;  // "preventing neck insertion to avoid a cycle"
+                parent[(size_t)rj] = ri;
+                alt_springs[(size_t)i].push_back(SpringRec{j, Springs{{zero3(), zero3(), zero3()}}});
+                alt_springs[(size_t)j].push_back(SpringRec{i, Springs{{zero3(), zero3(), zero3()}}});
+            }
+        for (auto& row : alt_springs) std::sort(row.begin(), row.end(), [](SpringRec const& p, SpringRec const& q) { return p.j < q.j; });
+    }
+
+    // alt_sinter_bridge.h:141-160: spring rotated into the tangent plane keeping its length, test force, spring += v dt
+    V3 alt_shear(V3& xi, V3 nrm, double stiffness, double damping, V3 rel_v) const {
+        V3 xi_new = sub(xi, scale(dot(xi, nrm), nrm));
+        if (norm(xi_new) > 0.0) {
+            xi_new = divs(xi_new, std::sqrt(dot(xi_new, xi_new)));
+            xi_new = scale(norm(xi), xi_new);
+        }
+        xi = xi_new;
+        V3 f_0 = sub(scale(-stiffness, xi), scale(damping, rel_v));
+        xi = add(xi, scale(cp.dt, rel_v));
+        return f_0;
+    }
+
+    // ---- alt_sinter_bridge.h:92-131 ------------------------------------------------------------------------------------
+    Accel alt_pair(int64_t i, int64_t j) {
+        auto& row = alt_springs[(size_t)i];
+        auto it = std::lower_bound(row.begin(), row.end(), j, [](SpringRec const& p, int64_t key) { return p.j < key; });
+        if (it == row.end() || it->j != j) return contact_pair(i, j);
+        Springs& s = it->s;
+        const double* b = cfg.alt_bond;  // k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o
+        V3 dx = sub(x[(size_t)i], x[(size_t)j]);
+        V3 nrm = normalized(dx);
+        double overlap = 2.0 * r - dot(dx, nrm);
+        double r_prime = r - overlap / 2.0;
+        V3 vi = v[(size_t)i], vj = v[(size_t)j], wi = omega[(size_t)i], wj = omega[(size_t)j];
+        double v_n = -dot(sub(vi, vj), nrm);
+        double f_n = b[0] * overlap + b[1] * v_n;
+        V3 ncwi = cross(nrm, wi), ncwj = cross(nrm, wj);
+        V3 v_ij = add(add(sub(vi, vj), scale(r_prime, ncwi)), scale(r_prime, ncwj));
+        V3 v_t = sub(v_ij, scale(dot(v_ij, nrm), nrm));
+        V3 v_r = scale(-r_prime, sub(ncwi, ncwj));
+        V3 v_o = scale(r * (dot(nrm, wi) - dot(nrm, wj)), nrm);
+        V3 f_t = alt_shear(s.xi[0], nrm, b[2], b[3], v_t);
+        V3 f_r = alt_shear(s.xi[1], nrm, b[4], b[5], v_r);
+        V3 f_o = alt_shear(s.xi[2], nrm, b[6], b[7], v_o);
+        V3 tau_t = scale(r_prime, cross(nrm, f_t));
+        V3 tau_r = scale(r, cross(nrm, f_r));
+        V3 tau_o = scale(r, f_o);
+        return Accel{divs(add(scale(f_n, nrm), f_t), mass), divs(add(add(neg(tau_t), tau_r), tau_o), inertia)};
     }
 
     // ---- candidate pairs within `range` of each other, via a uniform grid (any range) ------------
@@ -393,10 +482,17 @@ struct Oracle {
 
     // ---- hamaker_force.h:28-43 -----------------------------------------------------------------
     Accel hamaker_pair(int64_t i, int64_t j) const {
+        if (cfg.hamaker_kind == DEM_HAMAKER_LIMITED_RANGE) {  // limited_range_hamaker_force.h:34-35
+            if (norm(sub(x[(size_t)i], x[(size_t)j])) > cfg.hamaker_cutoff) return Accel{zero3(), zero3()};
+        }
         V3 rv = sub(x[(size_t)j], x[(size_t)i]);
         double h = norm(rv) - 2.0 * r;
         if (h < cfg.hamaker_h0) h = cfg.hamaker_h0;
         double A = cfg.hamaker_A;
+        if (cfg.hamaker_kind == DEM_HAMAKER_SIMPLIFIED) {  // simplified_hamaker_force.h:27
+            V3 fs = scale(2.0 * A * r / square(h), normalized(rv));
+            return Accel{divs(fs, mass), zero3()};
+        }
         double coef = -A / 6.0 *
                       ((4.0 * r + 2.0 * h) / (4.0 * r + h) / h - 2.0 / (2.0 * r + h) - 4.0 * square(r) / cube(2.0 * r + h) -
                        2.0 * square(r) * (4.0 * r + 2.0 * h) / square(4.0 * r + h) / square(h));
@@ -432,7 +528,11 @@ struct Oracle {
 
     // ---- binary_force_container.h:20-32 : (f1(i,j) + (f2(i,j) + ...)) in container order ----------
     Accel binary(int64_t i, int64_t j) {
-        // at most {contact | sinter} and {hamaker}: a two-term fold, contact/sinter first
+        // at most {contact | sinter | alt_sinter} and {hamaker}: a two-term fold, contact/sinter first
+        if (has_alt) {
+            Accel s = alt_pair(i, j);
+            return has_hamaker ? s + hamaker_pair(i, j) : s;
+        }
         if (has_sinter) {
             Accel s = sinter_pair(i, j);
             return has_hamaker ? s + hamaker_pair(i, j) : s;
@@ -545,12 +645,42 @@ struct Oracle {
 
     // ---- rotational_velocity_verlet_half.h:43-76 with rotational_step_handler.h:19-68 or
     //      sinter_step_handler (sinter_bridge.h:24-86) ---------------------------------------------
+    // ---- rotational_forward_euler.h:44-63 (two-term Taylor expansion in x and theta; v, omega copied BEFORE the
+    //      increments, a / alpha by reference) with the step handlers as below ---------------------------------------------
+    void do_step_forward_euler(double dt) {
+        evaluate();
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; i++) {
+            size_t s = (size_t)i;
+            const V3 vc = v[s];
+            const V3 wc = omega[s];
+            V3 dx = add(scale(dt, vc), scale(dt, scale(dt, scale(0.5, a[s]))));  // v*dt + ((0.5*a)*dt)*dt
+            x[s] = add(x[s], dx);
+            for (auto& b : bonds[s])
+                for (int k = 0; k < 5; k++) b.conn[k] = add(b.conn[k], dx);
+            if (i != cfg.fixed_particle) v[s] = add(v[s], scale(dt, a[s]));
+            V3 dth = add(scale(dt, wc), scale(dt, scale(dt, scale(0.5, alpha[s]))));
+            theta[s] = add(theta[s], dth);
+            for (auto& b : bonds[s])
+                for (int k = 0; k < 5; k++) {
+                    V3 sv = sub(b.conn[k], x[s]);
+                    b.conn[k] = add(b.conn[k], cross(dth, sv));
+                }
+            omega[s] = add(omega[s], scale(dt, alpha[s]));
+        }
+    }
+
     void do_step(double dt) {
+        if (cfg.integrator == DEM_INTEGRATOR_FORWARD_EULER) {
+            do_step_forward_euler(dt);
+            return;
+        }
         if (!velocities_initialized) {
             evaluate();
             velocities_initialized = true;
             for (int64_t i = 0; i < n; i++) {
-                v[(size_t)i] = add(v[(size_t)i], divs(scale(dt, neg(a[(size_t)i])), 2.0));
+                if (i != cfg.fixed_particle)  // increment_v of the fixed particle is swallowed by its step handler
+                    v[(size_t)i] = add(v[(size_t)i], divs(scale(dt, neg(a[(size_t)i])), 2.0));
                 omega[(size_t)i] = add(omega[(size_t)i], divs(scale(dt, neg(alpha[(size_t)i])), 2.0));
             }
             evaluate();
@@ -558,7 +688,7 @@ struct Oracle {
 #pragma omp parallel for schedule(static)
         for (int64_t i = 0; i < n; i++) {
             size_t s = (size_t)i;
-            v[s] = add(v[s], scale(dt, a[s]));
+            if (i != cfg.fixed_particle) v[s] = add(v[s], scale(dt, a[s]));
             V3 dx = scale(dt, v[s]);
             x[s] = add(x[s], dx);
             for (auto& b : bonds[s])
@@ -588,8 +718,9 @@ struct Oracle {
 extern "C" {
 
 void* orc_create(const dem_config* cfg, const double* x0, const double* v0, const double* th0, const double* om0) {
-    const int bin = cfg->model_mask & (DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER | DEM_MODEL_SINTER);
-    if (bin == 0 || ((bin & DEM_MODEL_CONTACT) && (bin & DEM_MODEL_SINTER))) return nullptr;
+    const int bin = cfg->model_mask & (DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER | DEM_MODEL_SINTER | DEM_MODEL_ALT_SINTER);
+    const int excl = ((bin & DEM_MODEL_CONTACT) != 0) + ((bin & DEM_MODEL_SINTER) != 0) + ((bin & DEM_MODEL_ALT_SINTER) != 0);
+    if (bin == 0 || excl > 1) return nullptr;  // sinter and alt_sinter embed the contact model
     return new Oracle(*cfg, x0, v0, th0, om0);
 }
 void orc_destroy(void* h) { delete static_cast<Oracle*>(h); }
@@ -640,9 +771,19 @@ void orc_get_contact_springs(void* h, int64_t i, int64_t j, double* out9) {
     std::fill(out9, out9 + 9, 0.0);
     for (auto const& s : o->springs[(size_t)i])
         if (s.j == j) std::memcpy(out9, s.s.xi, 72);
+    if (o->has_alt)
+        for (auto const& s : o->alt_springs[(size_t)i])
+            if (s.j == j) std::memcpy(out9, s.s.xi, 72);
 }
 int orc_get_bond(void* h, int64_t i, int64_t j, double* conn15, double* len5) {
     Oracle* o = static_cast<Oracle*>(h);
+    if (o->has_alt) {  // no connectors in this model: only the flag
+        std::fill(conn15, conn15 + 15, 0.0);
+        std::fill(len5, len5 + 5, 0.0);
+        for (auto const& s : o->alt_springs[(size_t)i])
+            if (s.j == j) return 1;
+        return 0;
+    }
     const Bond* b = o->find_bond(i, j);
     if (!b) return 0;
     std::memcpy(conn15, b->conn, 120);
@@ -660,6 +801,7 @@ int64_t orc_n_bonds(void* h) {
     Oracle* o = static_cast<Oracle*>(h);
     int64_t c = 0;
     for (auto const& b : o->bonds) c += (int64_t)b.size();
+    for (auto const& b : o->alt_springs) c += (int64_t)b.size();
     return c;
 }
 int64_t orc_n_contacts(void* h) {

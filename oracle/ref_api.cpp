@@ -27,8 +27,21 @@ static std::vector<Eigen::Vector3d> as_vec(const double* p, int64_t n) {
 extern "C" {
 
 void* ref_create(const dem_config* c, const double* x0, const double* v0, const double* th0, const double* om0) {
-    const int bin = c->model_mask & (DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER | DEM_MODEL_SINTER);
+    const int bin = c->model_mask & (DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER | DEM_MODEL_SINTER | DEM_MODEL_ALT_SINTER);
     try {
+        if (c->fixed_particle >= 0) return nullptr;  // the tutorial's step handler is not part of the reference headers
+        if (c->integrator == DEM_INTEGRATOR_FORWARD_EULER) {
+            if (c->hamaker_kind != DEM_HAMAKER_STANDARD) return nullptr;
+            if (bin == (DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER)) return ref_make_binary_fe_1(c, x0, v0, th0, om0);
+            if (bin == (DEM_MODEL_SINTER | DEM_MODEL_HAMAKER)) return ref_make_binary_fe_3(c, x0, v0, th0, om0);
+            return nullptr;
+        }
+        if (bin == DEM_MODEL_ALT_SINTER) return ref_make_binary_5(c, x0, v0, th0, om0);
+        if (c->hamaker_kind != DEM_HAMAKER_STANDARD) {
+            if (bin != (DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER)) return nullptr;
+            return c->hamaker_kind == DEM_HAMAKER_LIMITED_RANGE ? ref_make_binary_6(c, x0, v0, th0, om0)
+                                                                : ref_make_binary_7(c, x0, v0, th0, om0);
+        }
         switch (bin) {
             case DEM_MODEL_CONTACT: return ref_make_binary_0(c, x0, v0, th0, om0);
             case DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER: return ref_make_binary_1(c, x0, v0, th0, om0);

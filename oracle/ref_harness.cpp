@@ -14,7 +14,10 @@
 // compile times parallel:
 //   0: contact            1: contact + hamaker      2: sinter
 //   3: sinter + hamaker   4: hamaker
+//   5: alt_sinter         6: contact + limited_range_hamaker      7: contact + simplified_hamaker
 // and each instantiates {all-pairs, neighbor list} x {no unary force, one triangular facet}.
+// -DREF_INTEGRATOR=1 builds the same combination with rotational_forward_euler instead of
+// rotational_velocity_verlet_half (factory ref_make_binary_fe_<k>).
 
 #include <array>
 #include <cmath>
@@ -33,6 +36,7 @@
 #include <string>
 #include <iterator>
 #include <type_traits>
+#include <iostream>
 #include <omp.h>
 
 #include <Eigen/Eigen>
@@ -48,9 +52,17 @@
 // must be visible before triangular_facet.h; surface_hamaker_force.h needs hamaker_force.h first)
 #include <libgran/contact_force/contact_force.h>
 #include <libgran/contact_force/surface_contact_force.h>
+#if REF_BINARY == 6
+#include <libgran/hamaker_force/limited_range_hamaker_force.h>  // defines square / cube itself: cannot be co-included
+#else
 #include <libgran/hamaker_force/hamaker_force.h>
+#endif
+#if REF_BINARY == 7
+#include <libgran/hamaker_force/simplified_hamaker_force.h>
+#endif
 #include <libgran/hamaker_force/surface_hamaker_force.h>
 #include <libgran/sinter_bridge/sinter_bridge.h>
+#include <libgran/sinter_bridge/alt_sinter_bridge.h>
 #include <libgran/granular_system/granular_system.h>
 #undef binary_system_implementation
 #include <libgran/granular_system/granular_system_neighbor_list.h>
@@ -62,14 +74,29 @@
 #include "ref_iface.h"
 
 #ifndef REF_BINARY
-#error "compile with -DREF_BINARY=0..4"
+#error "compile with -DREF_BINARY=0..7"
+#endif
+#ifndef REF_INTEGRATOR
+#define REF_INTEGRATOR 0
+#endif
+#if REF_INTEGRATOR == 1
+#define REF_INTEGRATOR_T rotational_forward_euler
+#else
+#define REF_INTEGRATOR_T rotational_velocity_verlet_half
 #endif
 
 namespace {
 
 using V3 = Eigen::Vector3d;
 using contact_t = contact_force_functor<V3, double>;
+#if REF_BINARY == 6
+using hamaker_t = limited_range_hamaker_functor<V3, double>;
+#elif REF_BINARY == 7
+using hamaker_t = simplified_hamaker_functor<V3, double>;
+#else
 using hamaker_t = hamaker_functor<V3, double>;
+#endif
+using alt_sinter_t = alt_sinter_functor<V3, double>;
 using sinter_t = sinter_functor<V3, double>;
 using surf_contact_t = surface_contact_force_functor<V3, double>;
 using surf_hamaker_t = surface_hamaker_functor<V3, double>;
@@ -93,8 +120,15 @@ using binary_t = binary_force_functor_container<V3, double, sinter_t, hamaker_t>
 #elif REF_BINARY == 4
 constexpr int kMask = DEM_MODEL_HAMAKER;
 using binary_t = binary_force_functor_container<V3, double, hamaker_t>;
+#elif REF_BINARY == 5
+constexpr int kMask = DEM_MODEL_ALT_SINTER;
+using binary_t = binary_force_functor_container<V3, double, alt_sinter_t>;
+#elif REF_BINARY == 6 || REF_BINARY == 7
+constexpr int kMask = DEM_MODEL_CONTACT | DEM_MODEL_HAMAKER;
+using binary_t = binary_force_functor_container<V3, double, contact_t, hamaker_t>;
 #endif
 constexpr bool kSinter = (kMask & DEM_MODEL_SINTER) != 0;
+constexpr bool kAlt = (kMask & DEM_MODEL_ALT_SINTER) != 0;
 
 using unary_none_t = unary_force_functor_container<V3, double>;
 using unary_facet_t = unary_force_functor_container<V3, double, facet_t>;
@@ -104,23 +138,23 @@ struct system_sel;
 #if REF_BINARY == 2 || REF_BINARY == 3
 template <typename unary_t>
 struct system_sel<false, unary_t> {
-    using type = granular_system<V3, double, rotational_velocity_verlet_half, sinter_step_handler_double, binary_t, unary_t>;
+    using type = granular_system<V3, double, REF_INTEGRATOR_T, sinter_step_handler_double, binary_t, unary_t>;
     using handler = sinter_step_handler_double<std::vector<V3>, V3>;
 };
 template <typename unary_t>
 struct system_sel<true, unary_t> {
-    using type = granular_system_neighbor_list<V3, double, rotational_velocity_verlet_half, sinter_step_handler_double, binary_t, unary_t>;
+    using type = granular_system_neighbor_list<V3, double, REF_INTEGRATOR_T, sinter_step_handler_double, binary_t, unary_t>;
     using handler = sinter_step_handler_double<std::vector<V3>, V3>;
 };
 #else
 template <typename unary_t>
 struct system_sel<false, unary_t> {
-    using type = granular_system<V3, double, rotational_velocity_verlet_half, rotational_step_handler, binary_t, unary_t>;
+    using type = granular_system<V3, double, REF_INTEGRATOR_T, rotational_step_handler, binary_t, unary_t>;
     using handler = rotational_step_handler<std::vector<V3>, V3>;
 };
 template <typename unary_t>
 struct system_sel<true, unary_t> {
-    using type = granular_system_neighbor_list<V3, double, rotational_velocity_verlet_half, rotational_step_handler, binary_t, unary_t>;
+    using type = granular_system_neighbor_list<V3, double, REF_INTEGRATOR_T, rotational_step_handler, binary_t, unary_t>;
     using handler = rotational_step_handler<std::vector<V3>, V3>;
 };
 #endif
@@ -144,6 +178,7 @@ struct RefImpl final : RefSystem {
     std::unique_ptr<contact_t> contact;
     std::unique_ptr<hamaker_t> hamaker;
     std::unique_ptr<sinter_t> sinter;
+    std::unique_ptr<alt_sinter_t> alt;
     std::unique_ptr<surf_contact_t> surf_contact;
     std::unique_ptr<surf_hamaker_t> surf_hamaker;
     std::unique_ptr<facet_t> facet;
@@ -167,11 +202,21 @@ struct RefImpl final : RefSystem {
         const V3 zero = V3::Zero();
         std::vector<V3> x = to_vec(x0, c.n), v = to_vec(v0, c.n), th = to_vec(th0, c.n), om = to_vec(om0, c.n);
 
-        if constexpr ((kMask & DEM_MODEL_CONTACT) != 0)
+        if constexpr ((kMask & DEM_MODEL_CONTACT) != 0 || kAlt)
             contact = std::make_unique<contact_t>(n, p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8], p[9], p[10],
                                                   p[11], p[12], p[13], c.r_part, c.mass, c.inertia, p[14], zero, 0.0);
-        if constexpr ((kMask & DEM_MODEL_HAMAKER) != 0)
+        if constexpr ((kMask & DEM_MODEL_HAMAKER) != 0) {
+#if REF_BINARY == 6
+            hamaker = std::make_unique<hamaker_t>(c.hamaker_A, c.hamaker_h0, c.hamaker_cutoff, c.r_part, c.mass, zero, 0.0);
+#else
             hamaker = std::make_unique<hamaker_t>(c.hamaker_A, c.hamaker_h0, c.r_part, c.mass, zero, 0.0);
+#endif
+        }
+        if constexpr (kAlt) {  // test/alt_sintered.cpp:111-113
+            const double* b = c.alt_bond;
+            alt = std::make_unique<alt_sinter_t>(n, x, b[0], b[1], b[2], b[3], b[4], b[5], b[6], b[7], c.r_part, c.mass,
+                                                 c.inertia, p[14], zero, 0.0, c.critical_separation, *contact);
+        }
         if constexpr (kSinter)
             sinter = std::make_unique<sinter_t>(n, c.k_d, c.gamma_d, p[0], p[1], p[2], p[3], p[4], p[5], p[6], p[7], p[8],
                                                 p[9], p[10], p[11], p[12], p[13], c.r_part, c.mass, c.inertia, p[14], zero,
@@ -203,8 +248,12 @@ struct RefImpl final : RefSystem {
             return binary_t{*sinter};
 #elif REF_BINARY == 3
             return binary_t{*sinter, *hamaker};
-#else
+#elif REF_BINARY == 4
             return binary_t{*hamaker};
+#elif REF_BINARY == 5
+            return binary_t{*alt};
+#else
+            return binary_t{*contact, *hamaker};
 #endif
         };
         auto make_unary = [&]() -> unary_t {
@@ -281,7 +330,16 @@ struct RefImpl final : RefSystem {
     // Hidden per-ordered-pair contact springs (contact_force.h:156): 9 doubles for pair (i, j).
     void get_contact_springs(int64_t i, int64_t j, double* out9) const override {
         const contact_t* cf = nullptr;
-        if constexpr (kSinter)
+        if constexpr (kAlt) {  // bonded pairs keep their springs in the alt functor's own table (alt_sinter_bridge.h:146)
+            if (alt->bonded_contacts[(size_t)(i * cfg.n + j)]) {
+                auto const& rec = alt->contact_springs[(size_t)(i * cfg.n + j)];
+                std::memcpy(out9 + 0, std::get<0>(rec).data(), 24);
+                std::memcpy(out9 + 3, std::get<1>(rec).data(), 24);
+                std::memcpy(out9 + 6, std::get<2>(rec).data(), 24);
+                return;
+            }
+            cf = &alt->contact_force;
+        } else if constexpr (kSinter)
             cf = &sinter->contact_force;
         else if constexpr ((kMask & DEM_MODEL_CONTACT) != 0)
             cf = contact.get();
@@ -304,6 +362,10 @@ struct RefImpl final : RefSystem {
             for (int k = 0; k < 5; k++) std::memcpy(conn15 + 3 * k, sinter->spring_connectors[idx][(size_t)k].data(), 24);
             std::memcpy(len5, sinter->spring_lengths[idx].data(), 40);
             return 1;
+        } else if constexpr (kAlt) {  // no connectors in this model: only the flag
+            std::fill(conn15, conn15 + 15, 0.0);
+            std::fill(len5, len5 + 5, 0.0);
+            return alt->bonded_contacts[(size_t)(i * cfg.n + j)] ? 1 : 0;
         } else {
             (void)i; (void)j; (void)conn15; (void)len5;
             return 0;
@@ -328,7 +390,12 @@ struct RefImpl final : RefSystem {
 #define REF_CONCAT(a, b) REF_CONCAT2(a, b)
 
 // One factory per translation unit; ref_api.cpp dispatches on the binary-model mask.
-RefSystem* REF_CONCAT(ref_make_binary_, REF_BINARY)(const dem_config* c, const double* x0, const double* v0,
+#if REF_INTEGRATOR == 1
+#define REF_FACTORY REF_CONCAT(ref_make_binary_fe_, REF_BINARY)
+#else
+#define REF_FACTORY REF_CONCAT(ref_make_binary_, REF_BINARY)
+#endif
+RefSystem* REF_FACTORY(const dem_config* c, const double* x0, const double* v0,
                                                      const double* th0, const double* om0) {
     const bool facet = (c->model_mask & DEM_MODEL_FACET) != 0;
     if (c->use_neighbor_list) {

@@ -26,6 +26,11 @@ RefSystem* ref_make_binary_1(const dem_config*, const double*, const double*, co
 RefSystem* ref_make_binary_2(const dem_config*, const double*, const double*, const double*, const double*);
 RefSystem* ref_make_binary_3(const dem_config*, const double*, const double*, const double*, const double*);
 RefSystem* ref_make_binary_4(const dem_config*, const double*, const double*, const double*, const double*);
+RefSystem* ref_make_binary_5(const dem_config*, const double*, const double*, const double*, const double*);
+RefSystem* ref_make_binary_6(const dem_config*, const double*, const double*, const double*, const double*);
+RefSystem* ref_make_binary_7(const dem_config*, const double*, const double*, const double*, const double*);
+RefSystem* ref_make_binary_fe_1(const dem_config*, const double*, const double*, const double*, const double*);
+RefSystem* ref_make_binary_fe_3(const dem_config*, const double*, const double*, const double*, const double*);
 
 extern "C" {
 #endif
