@@ -106,6 +106,8 @@ struct lg_system {
     int mask = 0;  // binary models
     int variant = 1;
     int math_mode = 0;  // 0 = bit-exact (reference operand order, IEEE division), 1 = relaxed (lg_set_math_mode)
+    int fixed_particle = -1;  // fixed_particle_step_handler: increment_v of this particle is dropped (lg_set_fixed_particle)
+    int integrator = 0;       // 0 = rotational_velocity_verlet_half, 1 = rotational_forward_euler (lg_set_integrator)
 
     PingPong x, v, w;         // read by other particles' pair evaluations -> double-buffered
     DevBuf<double> a, th, al;  // private to their particle -> single
@@ -410,7 +412,7 @@ int step(lg_system* s, double dt) {
         // first call: evaluate, half kick back, evaluate again (rotational_velocity_verlet_half.h:45-60)
         if (!s->half_kicked) {
             LG_TRY(evaluate(s, s->facets));
-            launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
+            launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->fixed_particle, s->stream);
             LG_CUDA(cudaGetLastError());
         }
         LG_TRY(evaluate(s, s->facets));
@@ -1318,7 +1320,7 @@ int lg_first_half_kick(lg_system* s, double dt) {
     LG_TRY(prepare(s));
     if (s->kicked || s->half_kicked) return LG_OK;
     LG_TRY(evaluate(s, s->facets));
-    launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->stream);
+    launch_half_kick_back((int)s->n, s->v.p, s->w.p, s->a.p, s->al.p, dt, s->fixed_particle, s->stream);
     LG_CUDA(cudaGetLastError());
     s->half_kicked = true;
     return LG_OK;

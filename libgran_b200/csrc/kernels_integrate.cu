@@ -64,17 +64,18 @@ void launch_integrate(const IntegrateArgs& args, cudaStream_t st) {
 
 // rotational_velocity_verlet_half.h:51-57: increment_v(n, -a * dt / 2.0), increment_omega(n, -alpha * dt / 2.0)
 __global__ void __launch_bounds__(256)
-    half_kick_back_kernel(int n3, double* v, double* w, const double* a, const double* al, double dt) {
+    half_kick_back_kernel(int n3, double* v, double* w, const double* a, const double* al, double dt, int fixed) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n3) return;
-    v[k] = v[k] + ((-a[k]) * dt) / 2.0;
+    if (k / 3 != fixed) v[k] = v[k] + ((-a[k]) * dt) / 2.0;  // fixed_particle_step_handler drops increment_v of one particle
     w[k] = w[k] + ((-al[k]) * dt) / 2.0;
 }
 
-void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, cudaStream_t st) {
+void launch_half_kick_back(int n, double* v, double* w, const double* a, const double* al, double dt, int fixed,
+                           cudaStream_t st) {
     if (n <= 0) return;
     const int n3 = 3 * n, threads = 256;
-    half_kick_back_kernel<<<(n3 + threads - 1) / threads, threads, 0, st>>>(n3, v, w, a, al, dt);
+    half_kick_back_kernel<<<(n3 + threads - 1) / threads, threads, 0, st>>>(n3, v, w, a, al, dt, fixed);
     g_launch_count++;
 }
 
