@@ -206,7 +206,7 @@ def run_ours(args):
     if world > 1:
         return run_slab(args, scn, desc, moves, world, rank, local_rank)
 
-    uv = numpy_unit_vectors(n + 1024) if cfg.model_mask & S.MODEL_SINTER else None
+    uv = numpy_unit_vectors((4 * n if args.config == "3" else n) + 1024) if cfg.model_mask & S.MODEL_SINTER else None
     mode = 1 if (args.math == "fast" and args.variant in (None, 1, 2)) else 0
     bonds = scn.make_bonds(uv) if scn.make_bonds is not None else None
     sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode, bonds=bonds)
@@ -338,7 +338,7 @@ def run_slab(args, scn, desc, moves, world, rank, local_rank):
     cfg = scn.cfg
     n = cfg.n
     dev = torch.device("cuda", local_rank)
-    uv = numpy_unit_vectors(n + 1024) if cfg.model_mask & S.MODEL_SINTER else None
+    uv = numpy_unit_vectors((4 * n if args.config == "3" else n) + 1024) if cfg.model_mask & S.MODEL_SINTER else None
     mode = 1 if args.math == "fast" else 0
     bonds = scn.make_bonds(uv) if scn.make_bonds is not None else None
     sysm = SlabSystem(cfg, *scn.state, unit_vectors=uv, device=local_rank, math_mode=mode, bonds=bonds)

@@ -126,6 +126,41 @@ int lg_bond_table_destroy(lg_bond_table* t);
 int lg_set_bond_table(lg_system* s, const lg_contact_params* contact, double k_d, double gamma_d,
                       const lg_bond_table* t);
 
+/* ---- model, integrator and step-handler variants ------------------------------------------------
+ * Systems that use alt_sinter bonds, forward Euler, a fixed particle or the central attraction run the reference's schedule
+ * literally (kernel variant 0: integrate kernel + one-thread-per-particle force kernel, exact arithmetic); the Hamaker
+ * variants run in every kernel. */
+
+/* limited_range_hamaker_functor (LG/hamaker_force/limited_range_hamaker_force.h:19-45: zero when the centre distance
+ * exceeds r_cutoff, :34-35) and simplified_hamaker_functor (LG/hamaker_force/simplified_hamaker_force.h:10-34:
+ * F = 2 A r / h^2, :27).  Call after lg_set_hamaker, which supplies A and h0. */
+enum { LG_HAMAKER_STANDARD = 0, LG_HAMAKER_LIMITED_RANGE = 1, LG_HAMAKER_SIMPLIFIED = 2 };
+int lg_set_hamaker_variant(lg_system* s, int kind, double r_cutoff);
+
+/* The integrator template argument of granular_system: rotational_velocity_verlet_half (default) or
+ * rotational_forward_euler (LT/rotational_integrator/rotational_forward_euler.h:44-63: evaluate, then
+ * x += v dt + 0.5 a dt dt, v += a dt, theta += omega dt + 0.5 alpha dt dt, omega += alpha dt).  Before the first step. */
+enum { LG_INTEGRATOR_VERLET_HALF = 0, LG_INTEGRATOR_FORWARD_EULER = 1 };
+int lg_set_integrator(lg_system* s, int integrator);
+
+/* fixed_particle_step_handler (Writerside/topics/Custom-step-handler.md:48-146): increment_v of particle `index` is
+ * dropped, every other increment goes to the base step handler.  -1 = none. */
+int lg_set_fixed_particle(lg_system* s, int64_t index);
+
+/* central_attraction_functor (Writerside/topics/Custom-unary-force-model.md:44-121): a_i = k_a / mass * (x_i - x0),
+ * alpha_i = 0; x0 is what its update_center_of_mass() last computed -- the caller passes it (the header template sums
+ * get_x() in index order on the host, as the tutorial does). */
+int lg_set_central_attraction(lg_system* s, double k_a, const double x0[3]);
+
+/* alt_sinter_functor (LG/sinter_bridge/alt_sinter_bridge.h:16-176).  lg_alt_bond_table_create is its constructor's bond
+ * scan (:56-89; host only): pairs with |dist - 2 r| < critical_separation (strict) in lexicographic i < j order, a bond
+ * that would close a cycle is skipped.  lg_set_alt_bond_table installs the table, the embedded contact model (:33,95-96)
+ * and the bond's own coefficients bond_params = {k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o, dt} (:18-30).
+ * lg_get_alt_bond copies contact_springs[i * n + j] of a bonded pair (:162-164). */
+int lg_alt_bond_table_create(int64_t n, const double* x_3n, double r_part, double critical_separation, lg_bond_table** out);
+int lg_set_alt_bond_table(lg_system* s, const lg_contact_params* contact, const double bond_params[9], const lg_bond_table* t);
+int lg_get_alt_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double springs_9[9]);
+
 /* Capacity of the per-particle table of simultaneously overlapping non-bonded neighbours
  * (replaces the dense N x N spring store of contact_force.h:53; default 16, kissing number is 12).
  * Must be called before the first step. Exceeding it at run time makes the step return LG_ECAPACITY. */

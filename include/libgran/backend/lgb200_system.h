@@ -82,10 +82,11 @@ protected:
                   binary_force_functor_container_t binary, unary_force_functor_container_t unary)
         : binary_force_functors(std::move(binary)), unary_force_functors(std::move(unary)) {
         static_assert(requires { integrator_t<field_container_t, field_value_t, real_t, int, step_handler_t>::lgb200_integrator_kind; },
-                      "libgran-b200: this integrator has no device implementation (rotational_velocity_verlet_half only)");
+                      "libgran-b200: this integrator has no device implementation (rotational_velocity_verlet_half and "
+                      "rotational_forward_euler only)");
         static_assert(requires { step_handler_instance_t::lgb200_step_handler_kind; },
                       "libgran-b200: user-written step handlers cannot run on the device "
-                      "(rotational_step_handler and sinter_step_handler only; there is no CPU fallback)");
+                      "(rotational_step_handler, sinter_step_handler and fixed_particle_step_handler over either; no CPU fallback)");
         static_assert(n_binary + n_unary > 0, "at least one force functor must be provided");
         if (x0.size() != v0.size() || x0.size() != theta0.size() || x0.size() != omega0.size())
             throw SizeMismatchException("Size mismatch in arguments passed to granular system constructor: x0, v0, theta0, "
@@ -122,6 +123,10 @@ protected:
                 binary_force_functors.binary_force_functors);
             if (needs_connectors && step_handler_instance_t::lgb200_step_handler_kind != STEP_SINTER_CONNECTORS)
                 throw Lgb200BackendError(LG_EINVAL, "sinter_functor requires the step handler returned by its get_step_handler()");
+            constexpr int integrator_kind = integrator_t<field_container_t, field_value_t, real_t, int, step_handler_t>::lgb200_integrator_kind;
+            if constexpr (integrator_kind != 0) LGB200_CHECK(lg_set_integrator(handle, integrator_kind));
+            if constexpr (requires { step_handler_instance_t::lgb200_fixes_a_particle; })
+                LGB200_CHECK(lg_set_fixed_particle(handle, static_cast<std::int64_t>(step_handler.lgb200_fixed_particle())));
             (void)step_handler;
             std::size_t k = 0;
             std::apply(
@@ -131,7 +136,7 @@ protected:
                             using T = std::decay_t<decltype(g)>;
                             static_assert(requires { T::lgb200_unary_model; },
                                           "libgran-b200: this unary force functor has no device implementation "
-                                          "(triangular_facet only; no CPU fallback)");
+                                          "(triangular_facet and central_attraction_functor only; no CPU fallback)");
                             facet_ids[k++] = g.lgb200_install(handle);
                         }(f),
                         ...);
@@ -175,9 +180,12 @@ private:
             [&](auto&... f) {
                 (
                     [&](auto& g) {
-                        double vtx[9];
-                        LGB200_CHECK(lg_facet_get_vertices(handle, facet_ids[k++], vtx));
-                        g.lgb200_set_vertices(vtx);
+                        const int id = facet_ids[k++];
+                        if constexpr (requires(double* q) { g.lgb200_set_vertices(q); }) {
+                            double vtx[9];
+                            LGB200_CHECK(lg_facet_get_vertices(handle, id, vtx));
+                            g.lgb200_set_vertices(vtx);
+                        }
                     }(f),
                     ...);
             },

@@ -108,6 +108,12 @@ struct lg_system {
     int math_mode = 0;  // 0 = bit-exact (reference operand order, IEEE division), 1 = relaxed (lg_set_math_mode)
     int fixed_particle = -1;  // fixed_particle_step_handler: increment_v of this particle is dropped (lg_set_fixed_particle)
     int integrator = 0;       // 0 = rotational_velocity_verlet_half, 1 = rotational_forward_euler (lg_set_integrator)
+    bool simple_only = false; // a SURVEY 8f variant is active (alt_sinter, forward Euler, fixed particle, central attraction):
+                              // the system runs the reference's schedule literally (kernel variant 0, exact arithmetic)
+    bool central_on = false;  // central_attraction_functor (lg_set_central_attraction)
+    double central_k = 0.0;
+    double central_x0[3] = {0.0, 0.0, 0.0};
+    DevBuf<double> bspr;      // alt_sinter_functor: three springs (9 doubles) per ordered bond record
 
     PingPong x, v, w;         // read by other particles' pair evaluations -> double-buffered
     DevBuf<double> a, th, al;  // private to their particle -> single
@@ -328,6 +334,11 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.bptr = s->n_bonds > 0 ? s->bptr.p : nullptr;
     A.bj = s->bj.p; A.brev = s->brev.p; A.bconn = s->bconn.p; A.blen = s->blen.p;
     A.bwork = s->bwork.p; A.bwork_cnt = s->bwork_cnt.p;
+    A.bspr = s->bspr.p;
+    A.fixed = s->fixed_particle;
+    A.central_on = s->central_on ? 1 : 0;
+    A.central_k = s->central_k;
+    A.central_x0 = mk3(s->central_x0[0], s->central_x0[1], s->central_x0[2]);
     A.mp = s->mp;
     A.n_facets = (int)facets.size();
     for (int f = 0; f < A.n_facets; f++) {
@@ -343,7 +354,7 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
         A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= 24.0))) ? (rows_enabled == 1 ? 1 : 2) : 0;  // variant 2: row kernel whatever the row length
     }
-    A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia);
+    A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia, s->mp.hamaker_kind, s->mp.hamaker_cutoff);
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;
     A.x_next = s->x.next; A.v_next = s->v.next; A.w_next = s->w.next; A.th = s->th.p; A.bconn_next = s->bconn.next;
@@ -398,16 +409,26 @@ int integrate_in_place(lg_system* s, double dt) {
     IntegrateArgs I{};
     I.n = (int)s->n;
     I.x = s->x.p; I.v = s->v.p; I.th = s->th.p; I.w = s->w.p; I.a = s->a.p; I.al = s->al.p;
-    I.bptr = s->n_bonds > 0 ? s->bptr.p : nullptr;
+    I.bptr = (s->n_bonds > 0 && !s->mp.alt_bonds) ? s->bptr.p : nullptr;  // alt_sinter bonds carry no connectors
     I.bconn = s->bconn.p;
     I.n_bonds = s->n_bonds;
     I.dt = dt;
+    I.scheme = s->integrator;
+    I.fixed = s->fixed_particle;
     launch_integrate(I, s->stream);
     LG_CUDA(cudaGetLastError());
     return LG_OK;
 }
 
 int step(lg_system* s, double dt) {
+    if (s->integrator == 1) {
+        // rotational_forward_euler.h:44-62: update_acceleration(), then the two-term Taylor update; no half kick, and
+        // a / alpha stay those of the state BEFORE the step, as get_a() of the reference shows them
+        LG_TRY(evaluate(s, s->facets));
+        LG_TRY(integrate_in_place(s, dt));
+        s->steps++;
+        return LG_OK;
+    }
     if (!s->kicked) {
         // first call: evaluate, half kick back, evaluate again (rotational_velocity_verlet_half.h:45-60)
         if (!s->half_kicked) {
@@ -598,6 +619,7 @@ struct lg_bond_table {
     int64_t n = 0;
     int64_t bonds = 0;  // unordered
     std::vector<HostBond> recs;  // ordered records, two per bond
+    bool alt = false;            // built by lg_alt_bond_table_create: no connectors, cycle-free
 };
 
 namespace {
@@ -694,53 +716,53 @@ int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
 // Host-side restatement of the bond scan of sinter_functor's constructor (sinter_bridge.h:148-211) on a uniform
 // grid instead of the O(N^2) double loop; pairs are still visited in lexicographic (i < j) order so the
 // generator is consumed exactly like the reference.  Needs no GPU.
-static void scan_bonds(int64_t n, const std::vector<double>& hx, double r, double crit, lg_unit_vector_fn gen, void* user,
-                       std::vector<HostBond>& recs, int64_t& bonds) {
-    auto X = [&](int64_t i) { return mk3(hx[3 * (size_t)i], hx[3 * (size_t)i + 1], hx[3 * (size_t)i + 2]); };
-
-    // candidate partners j > i within 2r + crit (uniform host grid), visited in lexicographic order
-    // so that the generator is consumed exactly like the i < j double loop of sinter_bridge.h:148-149
-    const double range = 2.0 * r + crit;
-    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
-    for (int64_t i = 0; i < n; i++)
-        for (int k = 0; k < 3; k++) {
-            lo[k] = std::min(lo[k], hx[3 * (size_t)i + k]);
-            hi[k] = std::max(hi[k], hx[3 * (size_t)i + k]);
-        }
-    double cell = range * 1.0001;
+// Uniform host grid over the positions: candidates(i) = particles j > i in the 27 cells around i, ascending, i.e. the
+// partners the reference's i < j double loops (sinter_bridge.h:148-149, alt_sinter_bridge.h:65-66) could accept within `range`.
+struct HostGrid {
+    const std::vector<double>& hx;
+    double lo[3], cell;
     int64_t dim[3];
-    for (;;) {
-        double total = 1.0;
-        for (int k = 0; k < 3; k++) {
-            double d = std::floor((hi[k] - lo[k]) / cell) + 1.0;
-            dim[k] = (int64_t)d;
-            total *= d;
+    std::vector<int64_t> start, order;
+    HostGrid(int64_t n, const std::vector<double>& hx_, double range) : hx(hx_) {
+        double hi[3] = {-1e300, -1e300, -1e300};
+        lo[0] = lo[1] = lo[2] = 1e300;
+        for (int64_t i = 0; i < n; i++)
+            for (int k = 0; k < 3; k++) {
+                lo[k] = std::min(lo[k], hx[3 * (size_t)i + k]);
+                hi[k] = std::max(hi[k], hx[3 * (size_t)i + k]);
+            }
+        cell = range * 1.0001;
+        for (;;) {
+            double total = 1.0;
+            for (int k = 0; k < 3; k++) {
+                double d = std::floor((hi[k] - lo[k]) / cell) + 1.0;
+                dim[k] = (int64_t)d;
+                total *= d;
+            }
+            if (total <= 16.0 * (double)n + 65536.0) break;
+            cell *= 1.26;
         }
-        if (total <= 16.0 * (double)n + 65536.0) break;
-        cell *= 1.26;
+        const int64_t ncell = dim[0] * dim[1] * dim[2];
+        start.assign((size_t)ncell + 1, 0);
+        order.resize((size_t)n);
+        std::vector<int64_t> cidx((size_t)n);
+        for (int64_t i = 0; i < n; i++) {
+            int64_t c[3];
+            cell_of(i, c);
+            cidx[(size_t)i] = (c[0] * dim[1] + c[1]) * dim[2] + c[2];
+            start[(size_t)cidx[(size_t)i] + 1]++;
+        }
+        for (int64_t c = 0; c < ncell; c++) start[(size_t)c + 1] += start[(size_t)c];
+        std::vector<int64_t> cur(start.begin(), start.end() - 1);
+        for (int64_t i = 0; i < n; i++) order[(size_t)cur[(size_t)cidx[(size_t)i]]++] = i;  // ascending id inside a cell
     }
-    auto cell_of = [&](int64_t i, int64_t c[3]) {
+    void cell_of(int64_t i, int64_t c[3]) const {
         for (int k = 0; k < 3; k++) {
             int64_t t = (int64_t)std::floor((hx[3 * (size_t)i + k] - lo[k]) / cell);
             c[k] = std::min(std::max<int64_t>(t, 0), dim[k] - 1);
         }
-    };
-    const int64_t ncell = dim[0] * dim[1] * dim[2];
-    std::vector<int64_t> start((size_t)ncell + 1, 0), order((size_t)n), cidx((size_t)n);
-    for (int64_t i = 0; i < n; i++) {
-        int64_t c[3];
-        cell_of(i, c);
-        cidx[(size_t)i] = (c[0] * dim[1] + c[1]) * dim[2] + c[2];
-        start[(size_t)cidx[(size_t)i] + 1]++;
     }
-    for (int64_t c = 0; c < ncell; c++) start[(size_t)c + 1] += start[(size_t)c];
-    {
-        std::vector<int64_t> cur(start.begin(), start.end() - 1);
-        for (int64_t i = 0; i < n; i++) order[(size_t)cur[(size_t)cidx[(size_t)i]]++] = i;  // ascending id inside a cell
-    }
-    std::vector<int64_t> cand;
-    bonds = 0;
-    for (int64_t i = 0; i < n - 1; i++) {
+    void candidates(int64_t i, std::vector<int64_t>& cand) const {
         int64_t c[3];
         cell_of(i, c);
         cand.clear();
@@ -754,6 +776,19 @@ static void scan_bonds(int64_t n, const std::vector<double>& hx, double r, doubl
                         if (order[(size_t)q] > i) cand.push_back(order[(size_t)q]);
                 }
         std::sort(cand.begin(), cand.end());
+    }
+};
+
+static void scan_bonds(int64_t n, const std::vector<double>& hx, double r, double crit, lg_unit_vector_fn gen, void* user,
+                       std::vector<HostBond>& recs, int64_t& bonds) {
+    auto X = [&](int64_t i) { return mk3(hx[3 * (size_t)i], hx[3 * (size_t)i + 1], hx[3 * (size_t)i + 2]); };
+    // candidate partners j > i within 2r + crit, visited in lexicographic order so that the generator is consumed
+    // exactly like the i < j double loop of sinter_bridge.h:148-149
+    const HostGrid grid(n, hx, 2.0 * r + crit);
+    std::vector<int64_t> cand;
+    bonds = 0;
+    for (int64_t i = 0; i < n - 1; i++) {
+        grid.candidates(i, cand);
         const d3 part_i = X(i);
         for (int64_t j : cand) {
             const d3 part_j = X(j);
@@ -780,6 +815,43 @@ static void scan_bonds(int64_t n, const std::vector<double>& hx, double r, doubl
                 store3(bjr.conn + 3 * k, cj[k]);
                 bi.len[k] = bjr.len[k] = (k < 4) ? 2.0 * r : 0.0;
             }
+            recs.push_back(bi);
+            recs.push_back(bjr);
+            bonds++;
+        }
+    }
+}
+
+// alt_sinter_functor's constructor (alt_sinter_bridge.h:56-89): bond when |dist - 2 r| < critical_separation (strict),
+// i < j in lexicographic order; a bond that would close a cycle of bonds is skipped (:70-73 -- its subset relabelling,
+// :83-87, is a "same connected component?" test, done here with a union-find).  Records carry no connectors.
+static void scan_alt_bonds(int64_t n, const std::vector<double>& hx, double r, double crit, std::vector<HostBond>& recs,
+                           int64_t& bonds) {
+    auto X = [&](int64_t i) { return mk3(hx[3 * (size_t)i], hx[3 * (size_t)i + 1], hx[3 * (size_t)i + 2]); };
+    const HostGrid grid(n, hx, 2.0 * r + crit);
+    std::vector<int64_t> parent((size_t)n), cand;
+    for (int64_t i = 0; i < n; i++) parent[(size_t)i] = i;
+    auto find = [&](int64_t q) {
+        int64_t root = q;
+        while (parent[(size_t)root] != root) root = parent[(size_t)root];
+        while (parent[(size_t)q] != root) {
+            const int64_t nx = parent[(size_t)q];
+            parent[(size_t)q] = root;
+            q = nx;
+        }
+        return root;
+    };
+    bonds = 0;
+    for (int64_t i = 0; i < n - 1; i++) {
+        grid.candidates(i, cand);
+        const d3 part_i = X(i);
+        for (int64_t j : cand) {
+            if (!(std::fabs(norm(part_i - X(j)) - 2.0 * r) < crit)) continue;  // :67
+            const int64_t ri = find(i), rj = find(j);
+            if (ri == rj) continue;  // "preventing neck insertion to avoid a cycle"
+            parent[(size_t)rj] = ri;
+            HostBond bi{}, bjr{};
+            bi.i = i; bi.j = j; bjr.i = j; bjr.j = i;
             recs.push_back(bi);
             recs.push_back(bjr);
             bonds++;
@@ -923,6 +995,7 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     // (rotational_binary_system_neighbors_omp.h:66), step count 0 (lg_run's rebuild period restarts).  Bond tables stay.
     s->steps = 0;
     if (s->slots_ready) LG_CUDA(cudaMemsetAsync(s->sgid.p, 0xff, (size_t)s->n * s->S * sizeof(int32_t), s->stream));
+    if (s->mp.alt_bonds && s->n_bonds > 0) LG_CUDA(cudaMemsetAsync(s->bspr.p, 0, (size_t)s->n_bonds * 9 * sizeof(double), s->stream));
     for (size_t f = 0; f < s->facets.size(); f++) {
         LG_CUDA(cudaMemsetAsync(s->wspr[f]->p, 0, (size_t)s->n * 9 * sizeof(double), s->stream));
         LG_CUDA(cudaMemsetAsync(s->wact[f]->p, 0, (size_t)s->n, s->stream));
@@ -970,6 +1043,101 @@ int lg_set_hamaker(lg_system* s, double A, double h0) {
     s->mp.hamaker_A = A;
     s->mp.hamaker_h0 = h0;
     s->mask |= MODEL_HAMAKER;
+    return LG_OK;
+}
+
+/* ---- SURVEY.md section 8f variants: all of them run the reference's schedule literally (kernel variant 0) -------------- */
+static int lock_simple(lg_system* s) {
+    LG_TRY(flush(s));
+    s->variant = 0;
+    s->math_mode = 0;
+    s->simple_only = true;
+    return LG_OK;
+}
+
+int lg_set_hamaker_variant(lg_system* s, int kind, double r_cutoff) {
+    LG_ENTER(s);
+    if (kind < HAMAKER_STANDARD || kind > HAMAKER_SIMPLIFIED) return fail(LG_EINVAL, "unknown Hamaker variant");
+    if (kind == HAMAKER_LIMITED_RANGE && !(r_cutoff > 0.0)) return fail(LG_EINVAL, "limited-range Hamaker needs r_cutoff > 0");
+    LG_TRY(flush(s));
+    s->mp.hamaker_kind = kind;
+    s->mp.hamaker_cutoff = r_cutoff;
+    return LG_OK;
+}
+
+int lg_set_integrator(lg_system* s, int integrator) {
+    LG_ENTER(s);
+    if (integrator != LG_INTEGRATOR_VERLET_HALF && integrator != LG_INTEGRATOR_FORWARD_EULER) return fail(LG_EINVAL, "unknown integrator");
+    if (s->steps > 0 && integrator != s->integrator) return fail(LG_EINVAL, "the integrator is a constructor choice: set it before the first step");
+    s->integrator = integrator;
+    return integrator == LG_INTEGRATOR_FORWARD_EULER ? lock_simple(s) : LG_OK;
+}
+
+int lg_set_fixed_particle(lg_system* s, int64_t index) {
+    LG_ENTER(s);
+    if (index < -1 || index >= s->n) return fail(LG_EINVAL, "fixed particle index out of range");
+    s->fixed_particle = (int)index;
+    return index >= 0 ? lock_simple(s) : LG_OK;
+}
+
+int lg_set_central_attraction(lg_system* s, double k_a, const double x0[3]) {
+    LG_ENTER(s);
+    if (!x0) return fail(LG_EINVAL, "null centre");
+    if (!s->facets.empty()) return fail(LG_EINVAL, "central attraction together with facets is not supported");
+    LG_TRY(lock_simple(s));
+    s->central_on = true;
+    s->central_k = k_a;
+    for (int k = 0; k < 3; k++) s->central_x0[k] = x0[k];
+    return LG_OK;
+}
+
+int lg_alt_bond_table_create(int64_t n, const double* x, double r_part, double crit, lg_bond_table** out) {
+    if (!out) return fail(LG_EINVAL, "out is null");
+    *out = nullptr;
+    if (n <= 0 || !x || !(r_part > 0.0)) return fail(LG_EINVAL, "bad arguments to lg_alt_bond_table_create");
+    std::unique_ptr<lg_bond_table> t(new (std::nothrow) lg_bond_table());
+    if (!t) return fail(LG_ENOMEM, "host allocation failed");
+    t->n = n;
+    t->alt = true;
+    std::vector<double> hx(x, x + 3 * (size_t)n);
+    scan_alt_bonds(n, hx, r_part, crit, t->recs, t->bonds);
+    *out = t.release();
+    return LG_OK;
+}
+
+int lg_set_alt_bond_table(lg_system* s, const lg_contact_params* contact, const double bond_params[9], const lg_bond_table* t) {
+    LG_ENTER(s);
+    if (!contact || !bond_params || !t) return fail(LG_EINVAL, "null contact params, bond params or bond table");
+    if (!t->alt) return fail(LG_EINVAL, "the table was built for sinter_functor (lg_bond_table_create)");
+    if (t->n != s->n) return fail(LG_ESIZE, "bond table was built for a different particle count");
+    if (s->mask & (MODEL_CONTACT | MODEL_SINTER)) return fail(LG_EINVAL, "a contact or sinter model is already installed; alt_sinter embeds contact");
+    LG_TRY(lock_simple(s));
+    std::vector<HostBond> recs = t->recs;
+    to_cp(contact, s->mp.cp);
+    for (int k = 0; k < 8; k++) s->mp.alt[k] = bond_params[k];
+    s->mp.alt_dt = bond_params[8];
+    s->mp.alt_bonds = 1;
+    s->mp.k_d = 0.0;
+    s->mp.gamma_d = 0.0;
+    s->mask |= MODEL_SINTER;  // same row tags, same bond CSR; the bonded law is chosen by mp.alt_bonds
+    LG_CUDA(s->bspr.reserve(recs.size() * 9 + 16));
+    LG_CUDA(cudaMemsetAsync(s->bspr.p, 0, (recs.size() * 9 + 16) * sizeof(double), s->stream));
+    return install_bonds(s, recs);
+}
+
+int lg_get_alt_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double springs[9]) {
+    LG_ENTER(s);
+    if (!bonded || !springs || i < 0 || j < 0 || i >= s->n || j >= s->n) return fail(LG_EINVAL, "bad arguments");
+    *bonded = 0;
+    if (s->n_bonds == 0 || !s->mp.alt_bonds) return LG_OK;
+    LG_TRY(flush(s));
+    for (uint32_t b = s->h_bptr[(size_t)i]; b < s->h_bptr[(size_t)i + 1]; b++)
+        if (s->h_bj[b] == (int32_t)j) {
+            LG_CUDA(cudaMemcpyAsync(springs, s->bspr.p + (size_t)b * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+            LG_CUDA(cudaStreamSynchronize(s->stream));
+            *bonded = 1;
+            break;
+        }
     return LG_OK;
 }
 
@@ -1668,6 +1836,8 @@ int lg_last_step_kernel(lg_system* s, char* out, int cap) {
 int lg_set_kernel_variant(lg_system* s, int variant) {
     LG_ENTER(s);
     if (variant < 0 || variant > 2) return fail(LG_EINVAL, "variant must be 0 (validation), 1 (production) or 2 (row kernel forced)");
+    if (s->simple_only && variant != 0)
+        return fail(LG_EINVAL, "alt_sinter / forward Euler / fixed-particle / central-attraction systems run kernel variant 0 only");
     LG_TRY(flush(s));
     if (variant == 0 && s->math_mode != 0) return fail(LG_EINVAL, "the validation variant is bit-exact only; reset the math mode first");
     s->variant = variant;

@@ -105,7 +105,15 @@ __global__ void __launch_bounds__(128) force_simple_kernel(const __grid_constant
             const int t = A.tag[p];
             if (kSinter && t >= kTagBond && t != kTagNone) {
                 const d3 vj = load3(A.v + 3 * (size_t)j), wj = load3(A.w + 3 * (size_t)j);
-                c = bonded_accel(A, A.bptr[i] + (uint32_t)(t - kTagBond), xi, xj, vi, vj, wi, wj);
+                const uint32_t b = A.bptr[i] + (uint32_t)(t - kTagBond);
+                if (A.mp.alt_bonds) {  // alt_sinter_functor: the record's own three springs, no connectors
+                    double* sp = A.bspr + (size_t)b * 9;
+                    Springs s = load_springs(sp);
+                    c = alt_bonded_force(A.mp.alt, A.mp.alt_dt, A.mp.r, A.mp.mass, A.mp.inertia, g, vi, vj, wi, wj, s);
+                    store_springs(sp, s);
+                } else {
+                    c = bonded_accel(A, b, xi, xj, vi, vj, wi, wj);
+                }
             } else {
                 const double overlap = contact_overlap(g, 2.0 * A.mp.r);
                 if (overlap <= 0) {
@@ -140,7 +148,7 @@ __global__ void __launch_bounds__(128) force_simple_kernel(const __grid_constant
             }
         }
         if constexpr (kHamaker) {
-            const d3 h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
+            const d3 h = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g, A.mp.hamaker_kind, A.mp.hamaker_cutoff);
             if constexpr (kContact)
                 c.a = c.a + h;  // (contact|sinter)(i,j) + hamaker(i,j): two-term fold, torque + 0
             else
@@ -153,6 +161,10 @@ __global__ void __launch_bounds__(128) force_simple_kernel(const __grid_constant
         const Accel u = unary_accel(A, i, xi, vi, wi);
         acc_a += u.a;
         acc_al += u.alpha;
+    }
+    if (A.central_on) {  // central_attraction_functor (Custom-unary-force-model.md:99-100): a = k_a / mass * (x_i - x0), alpha = 0
+        acc_a += (A.central_k / A.mp.mass) * (xi - A.central_x0);
+        acc_al += zero3();
     }
     store3(A.a + 3 * (size_t)i, acc_a);
     store3(A.al + 3 * (size_t)i, acc_al);

@@ -234,7 +234,7 @@ __global__ void __launch_bounds__(TB, FAST ? LG_MINB : LG_MINB_EXACT) step_tiled
             } else {
                 const PairGeom g = pair_geometry(xi, xjv[k]);
                 ov[k] = contact_overlap(g, 2.0 * A.mp.r);
-                if constexpr (kHamaker) hv[k] = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g);
+                if constexpr (kHamaker) hv[k] = hamaker_accel(A.mp.hamaker_A, A.mp.hamaker_h0, A.mp.r, A.mp.mass, g, A.mp.hamaker_kind, A.mp.hamaker_cutoff);
             }
         }
 #pragma unroll

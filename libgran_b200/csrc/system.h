@@ -49,6 +49,7 @@ struct ModelParams {
     double hamaker_cutoff;
     int alt_bonds;          // the bond table belongs to alt_sinter_functor: no connectors, three springs per ordered bond
     double alt[8];          // its k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o
+    double alt_dt;          // its own spring-update time step (alt_sinter_bridge.h:30)
 };
 
 struct ForceArgs {

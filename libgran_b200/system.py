@@ -32,6 +32,9 @@ ABI_SYMBOLS = (
     "lg_bond_table_create", "lg_bond_table_count", "lg_bond_table_records", "lg_bond_table_destroy", "lg_set_bond_table",
     "lg_facet_set_vertices", "lg_set_math_mode", "lg_last_step_kernel",
     "lg_gen_fractal_aggregate", "lg_gen_random_packing",
+    # SURVEY.md section 8f variants
+    "lg_set_hamaker_variant", "lg_set_integrator", "lg_set_fixed_particle", "lg_set_central_attraction",
+    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond",
     # slab decomposition support
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
@@ -123,6 +126,13 @@ def load_library(path: Optional[str] = None):
     lib.lg_last_step_kernel.argtypes = [vp, C.c_char_p, C.c_int]
     lib.lg_gen_fractal_aggregate.argtypes = [C.c_int64, C.c_uint64, C.c_double, dp]
     lib.lg_gen_random_packing.argtypes = [C.c_int64, C.c_double, C.c_double, C.c_double, C.c_uint64, C.c_double, dp, dp]
+    lib.lg_set_hamaker_variant.argtypes = [vp, C.c_int, C.c_double]
+    lib.lg_set_integrator.argtypes = [vp, C.c_int]
+    lib.lg_set_fixed_particle.argtypes = [vp, C.c_int64]
+    lib.lg_set_central_attraction.argtypes = [vp, C.c_double, dp]
+    lib.lg_alt_bond_table_create.argtypes = [C.c_int64, vp, C.c_double, C.c_double, C.POINTER(vp)]
+    lib.lg_set_alt_bond_table.argtypes = [vp, cpp, dp, vp]
+    lib.lg_get_alt_bond.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int), dp]
     # slab decomposition support: device pointers travel as plain integers
     lib.lg_flush.argtypes = [vp]
     lib.lg_first_half_kick.argtypes = [vp, C.c_double]
@@ -219,6 +229,43 @@ class GranularSystem:
     def set_hamaker(self, A: float, h0: float):
         self._check(self.lib.lg_set_hamaker(self.h, float(A), float(h0)))
 
+    def set_hamaker_variant(self, kind: int, r_cutoff: float = 0.0):
+        """1 = limited_range_hamaker_functor (zero beyond r_cutoff), 2 = simplified_hamaker_functor."""
+        self._check(self.lib.lg_set_hamaker_variant(self.h, int(kind), float(r_cutoff)))
+
+    def set_integrator(self, integrator: int):
+        """0 = rotational_velocity_verlet_half, 1 = rotational_forward_euler."""
+        self._check(self.lib.lg_set_integrator(self.h, int(integrator)))
+
+    def set_fixed_particle(self, index: int):
+        self._check(self.lib.lg_set_fixed_particle(self.h, int(index)))
+
+    def set_central_attraction(self, k_a: float, x0):
+        c = np.ascontiguousarray(np.asarray(x0, dtype=np.float64).reshape(3))
+        self._check(self.lib.lg_set_central_attraction(self.h, float(k_a), _dp(c)))
+
+    def build_alt_sinter_bonds(self, contact: Sequence[float], bond_params: Sequence[float], critical_separation: float,
+                               x0, r_part: float) -> int:
+        """alt_sinter_functor's constructor: bond scan over x0 (cycle-free), embedded contact model, and the bond's own
+        {k, gamma_n, k_t, gamma_t, k_r, gamma_r, k_o, gamma_o, dt}."""
+        p = ContactParamsStruct.from_seq(contact)
+        bp = np.ascontiguousarray(np.asarray(bond_params, dtype=np.float64).reshape(9))
+        x = _c3(x0)
+        tbl = C.c_void_p()
+        self._check(self.lib.lg_alt_bond_table_create(len(x), x.ctypes.data, float(r_part), float(critical_separation), C.byref(tbl)))
+        try:
+            nb = C.c_int64(0)
+            self.lib.lg_bond_table_count(tbl, C.byref(nb))
+            self._check(self.lib.lg_set_alt_bond_table(self.h, C.byref(p), _dp(bp), tbl))
+        finally:
+            self.lib.lg_bond_table_destroy(tbl)
+        return int(nb.value)
+
+    def alt_bond(self, i: int, j: int):
+        out, flag = np.zeros(9), C.c_int(0)
+        self._check(self.lib.lg_get_alt_bond(self.h, int(i), int(j), C.byref(flag), _dp(out)))
+        return out if flag.value else None
+
     def set_max_contacts(self, m: int):
         self._check(self.lib.lg_set_max_contacts(self.h, int(m)))
 
@@ -237,8 +284,10 @@ class GranularSystem:
 
             def cb(_user, out):
                 k = state["k"]
-                if k >= len(arr):
-                    raise IndexError("unit vector array exhausted")
+                if k >= len(arr):  # an exception cannot cross the C frame: hand out a valid vector, fail after the call
+                    state["short"] = True
+                    out[0], out[1], out[2] = 1.0, 0.0, 0.0
+                    return
                 out[0], out[1], out[2] = arr[k, 0], arr[k, 1], arr[k, 2]
                 state["k"] = k + 1
         cfn = UNIT_VECTOR_FN(cb)
@@ -246,6 +295,8 @@ class GranularSystem:
         nb = C.c_int64(0)
         self._check(self.lib.lg_build_sinter_bonds(self.h, C.byref(p), float(k_d), float(gamma_d),
                                                    float(critical_separation), cfn, None, C.byref(nb)))
+        if not callable(unit_vectors) and state.get("short"):
+            raise IndexError(f"unit vector array exhausted: {len(arr)} vectors for {int(nb.value)} bonds")
         return int(nb.value)
 
     def set_bonds(self, contact: Sequence[float], k_d: float, gamma_d: float, ij, connectors, rest_lengths):
@@ -381,7 +432,7 @@ class GranularSystem:
 def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1, variant: Optional[int] = None,
                 math_mode: int = 0, bonds=None) -> GranularSystem:
     """Build a GranularSystem from a ``scenarios.DemConfig`` (same meaning as oracle/dem_config.h)."""
-    from .scenarios import MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
+    from .scenarios import MODEL_ALT_SINTER, MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
 
     sysm = GranularSystem(x0, v0, theta0, omega0, cfg.r_part, cfg.mass, cfg.inertia, device=device,
                           r_verlet=cfg.r_verlet if cfg.use_neighbor_list else None)
@@ -398,8 +449,16 @@ def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1
             if unit_vectors is None:
                 raise ValueError("the sinter model needs unit_vectors (callable or array)")
             sysm.build_sinter_bonds(cfg.contact, cfg.k_d, cfg.gamma_d, cfg.critical_separation, unit_vectors)
+    if cfg.model_mask & MODEL_ALT_SINTER:
+        sysm.build_alt_sinter_bonds(cfg.contact, tuple(cfg.alt_bond) + (cfg.contact[14],), cfg.critical_separation, x0, cfg.r_part)
     if cfg.model_mask & MODEL_HAMAKER:
         sysm.set_hamaker(cfg.hamaker_A, cfg.hamaker_h0)
+        if getattr(cfg, "hamaker_kind", 0):
+            sysm.set_hamaker_variant(cfg.hamaker_kind, cfg.hamaker_cutoff)
+    if getattr(cfg, "integrator", 0):
+        sysm.set_integrator(cfg.integrator)
+    if getattr(cfg, "fixed_particle", -1) >= 0:
+        sysm.set_fixed_particle(cfg.fixed_particle)
     if cfg.model_mask & MODEL_FACET:
         sysm.add_facet(cfg.facet_vertices, cfg.facet_v, cfg.surf_contact, (cfg.surf_A, cfg.surf_h0))
     return sysm

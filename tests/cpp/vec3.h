@@ -19,3 +19,4 @@ inline vec3 operator*(vec3 const& a, double s) { return vec3(a[0] * s, a[1] * s,
 inline vec3 operator*(double s, vec3 const& a) { return a * s; }
 inline vec3 operator+(vec3 const& a, vec3 const& b) { return vec3(a[0] + b[0], a[1] + b[1], a[2] + b[2]); }
 inline vec3 operator-(vec3 const& a, vec3 const& b) { return vec3(a[0] - b[0], a[1] - b[1], a[2] - b[2]); }
+inline vec3 operator/(vec3 const& a, double s) { return vec3(a[0] / s, a[1] / s, a[2] / s); }

@@ -23,7 +23,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CPP = os.path.join(HERE, "cpp")
 BUILD = os.path.join(CPP, "_build")
 DRIVER = os.path.join(BUILD, "template_driver")
-DROPIN = ["sintered", "hamaker_neighbor", "hamaker", "contact", "surface"]
+DROPIN = ["sintered", "hamaker_neighbor", "hamaker", "contact", "surface", "alt_sintered"]
 HAVE_REF = os.path.isdir("/root/reference/test")
 
 
@@ -132,11 +132,74 @@ def test_cpp_templates_match_oracle(tmp_path, oracle, name, make, steps, moves):
         assert np.array_equal(got[k], cpu.get(f)), f"{name}: {f} differs from the oracle"
 
 
+def _variant_cases():
+    import variant_cases as V
+
+    alt = V.alt_lattice(True, False)
+    return [
+        ("euler", lambda: V.euler(S.MODEL_CONTACT | S.MODEL_HAMAKER), ["euler"]),
+        ("fixed", lambda: V.fixed(S.MODEL_CONTACT | S.MODEL_HAMAKER), ["fixed", "3"]),
+        ("limited", lambda: V.hamaker_variant(1), ["limited", repr(3.3 * S.R_PART)]),
+        ("simplified", lambda: V.hamaker_variant(2), ["simplified"]),
+        ("alt nl", lambda: V.alt_lattice(True, False), ["alt", *[repr(float(b)) for b in alt.cfg.alt_bond]]),
+        ("alt allpairs", lambda: V.alt_lattice(False, False), ["alt", *[repr(float(b)) for b in alt.cfg.alt_bond]]),
+    ]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,make,args", _variant_cases(), ids=[c[0] for c in _variant_cases()])
+def test_cpp_variant_templates_match_oracle(tmp_path, oracle, name, make, args):
+    """rotational_forward_euler, fixed_particle_step_handler, limited_range / simplified Hamaker and
+    alt_sinter_functor through their header templates (tests/cpp/variants_driver.cpp), bit-identical to the oracle."""
+    build_driver()
+    scn = make()
+    cfg = scn.cfg
+    steps = 300
+    case, out = str(tmp_path / "case.bin"), str(tmp_path / "out.bin")
+    write_case(case, scn, steps, False, None)
+    res = subprocess.run([os.path.join(BUILD, "variants_driver"), case, out, *args], capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stderr
+    got = np.fromfile(out, dtype=np.float64).reshape(6, cfg.n, 3)
+    cpu = oracle.OracleSystem(cfg, *scn.state)
+    advance(cpu, cfg, 0, steps, False)
+    for k, f in enumerate(("x", "v", "theta", "omega", "a", "alpha")):
+        assert np.array_equal(got[k], cpu.get(f)), f"{name}: {f} differs from the oracle"
+
+
+@pytest.mark.gpu
+def test_cpp_central_attraction_template(tmp_path, lib):
+    """Tutorial 3's central_attraction_functor through its header template vs the same model set through the Python binding."""
+    from libgran_b200.system import from_config
+
+    build_driver()
+    scn = S.slab_and_projectile(S.MODEL_CONTACT | S.MODEL_HAMAKER, True)
+    cfg, steps, k_a = scn.cfg, 100, -8.0e-6
+    case, out = str(tmp_path / "case.bin"), str(tmp_path / "out.bin")
+    write_case(case, scn, steps, False, None)
+    res = subprocess.run([os.path.join(BUILD, "variants_driver"), case, out, "central", repr(k_a)], capture_output=True, text=True,
+                         timeout=600)
+    assert res.returncode == 0, res.stderr
+    got = np.fromfile(out, dtype=np.float64).reshape(6, cfg.n, 3)
+    x0 = np.zeros(3)
+    for q in scn.x0:
+        x0 = x0 + q
+    x0 = x0 / float(cfg.n)
+    g = from_config(cfg, *scn.state, device=0)
+    g.set_central_attraction(k_a, x0)
+    advance(g, cfg, 0, steps, False)
+    for k, f in enumerate(("x", "v", "theta", "omega", "a", "alpha")):
+        assert np.array_equal(got[k], g.get(f)), f"central attraction: {f}"
+    plain = from_config(cfg, *scn.state, device=0)
+    advance(plain, cfg, 0, steps, False)
+    assert not np.array_equal(plain.get("x"), g.get("x"))
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("name", DROPIN)
 def test_reference_driver_reaches_its_targets_on_gpu(name):
     """The reference's own known-answer tests (hard-coded targets at +-1 %: test/sintered.cpp:144-145,
-    test/hamaker_neighbor.cpp:129-131, test/hamaker.cpp:127-129, test/contact.cpp:111-112, test/surface.cpp:117),
+    test/hamaker_neighbor.cpp:129-131, test/hamaker.cpp:127-129, test/contact.cpp:111-112, test/surface.cpp:117,
+    test/alt_sintered.cpp:141-148 -- ctest 6/6),
     unmodified sources, running on the CUDA backend.  Built by `make -C tests/cpp dropin` in the build container."""
     exe = os.path.join(BUILD, "dropin", name + "_b200")
     if not os.path.exists(exe):
