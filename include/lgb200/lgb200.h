@@ -79,6 +79,16 @@ int lg_abi_version(void);
 int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v, const double* theta,
                  const double* omega);
 
+/* Spatial renumbering (no reference counterpart).  mode 1: at the first lg_set_state the
+ * particles are renumbered internally along a Morton curve (counting sort by cell on the device), so that the neighbours of
+ * consecutive particles are mostly consecutive -- what the staged position window of the row kernel needs on inputs whose
+ * caller order has no spatial locality (random packings, fractal aggregates).  Invisible at this boundary: lg_set_state,
+ * lg_get_field, bond tables, lg_get_neighbor_rows, lg_get_contact_springs, lg_get_bond ... all speak the caller's order.
+ * The numbering is fixed by the first lg_set_state.  Rows are then accumulated in ascending INTERNAL index, so results are
+ * no longer bit-identical to the reference's ascending-j sums (they stay within rounding of them): meant for LG_MATH_FAST.
+ * Must precede the first lg_set_state; the slab-decomposition entry points below refuse renumbered systems. */
+int lg_set_reorder(lg_system* s, int mode);
+
 /* get_x / get_v / get_a / get_theta / get_omega / get_alpha (rotational_system.h:94-121): copies
  * device -> host, in the caller's particle order.  Implies a stream synchronisation. */
 int lg_get_field(lg_system* s, int field, double* out_3n);
@@ -261,6 +271,28 @@ int lg_gen_fractal_aggregate(int64_t n, uint64_t seed, double r_part, double* x_
  * origin; min_gap_factor in (0.5, 1] scales the excluded diameter (1 = no overlaps).  box_out (nullable) = edges. */
 int lg_gen_random_packing(int64_t n, double volume_fraction, double aspect, double min_gap_factor, uint64_t seed,
                           double r_part, double* x_out_3n, double box_out[3]);
+
+/* ---- dump pipeline ------------------------------------------------------------------------
+ * The reference's writer.cpp (VTK ASCII: write_particles :51-118, write_necks :120-170, write_spring_connectors :13-49; file
+ * numbering from 1 per kind, :9-11) and the tutorial's CSV dump (Writerside/topics/Custom-unary-force-model.md:339-355),
+ * byte for byte.  lg_dump_* does not stall the time loop: it snapshots the needed arrays device-to-device on the system's
+ * stream and returns; a second stream copies the snapshot to pinned host memory and a background thread formats and writes the
+ * file.  Two snapshots may be in flight; a third call blocks until one has been written.  Files are complete after
+ * lg_dumper_wait (or lg_dumper_destroy).  `dir` must exist. */
+typedef struct lg_dumper lg_dumper;
+int lg_dumper_create(lg_system* s, const char* dir, lg_dumper** out);
+int lg_dump_particles(lg_system* s, lg_dumper* d);          /* <dir>/particles_<k>.vtk: x / r_part, orientation triad from theta */
+int lg_dump_necks(lg_system* s, lg_dumper* d);              /* <dir>/necks_<k>.vtk: midpoint and normal of every bond i < j */
+int lg_dump_spring_connectors(lg_system* s, lg_dumper* d);  /* <dir>/spring_connectors_<k>.vtk: 5 connectors per ordered bond */
+int lg_dump_particles_csv(lg_system* s, lg_dumper* d, int64_t count); /* <dir>/particles_<count>.csv */
+int lg_dumper_wait(lg_dumper* d);
+int lg_dumper_destroy(lg_dumper* d);
+/* The same formatter for host arrays -- the argument lists of the reference's functions (writer.h:16-23), with the dense
+ * N x N tables replaced by the bond list: ij_pairs = n_bonds (i, j) pairs (either or both orientations), connectors_15 = the
+ * 5 connectors of every ordered record in (i, j) order.  Pure host code. */
+int lg_write_particles(const char* path, int64_t n, const double* x_3n, const double* theta_3n, double r_part);
+int lg_write_necks(const char* path, int64_t n, const double* x_3n, double r_part, int64_t n_bonds, const int64_t* ij_pairs);
+int lg_write_spring_connectors(const char* path, double r_part, int64_t n_records, const double* connectors_15);
 
 /* ---- slab decomposition (no reference counterpart -- the reference is single-process) ----
  * One lg_system per rank holds that rank's owned particles and its ghosts, ordered by global particle id.  The

@@ -114,6 +114,13 @@ struct lg_system {
     double central_k = 0.0;
     double central_x0[3] = {0.0, 0.0, 0.0};
     DevBuf<double> bspr;      // alt_sinter_functor: three springs (9 doubles) per ordered bond record
+    // Spatial renumbering (lg_set_reorder): internal index k holds the caller's particle perm[k]; inv is the inverse.
+    // Fixed by the first lg_set_state; every entry point that takes or returns particle indices / per-particle arrays maps.
+    int reorder_mode = 0;
+    bool reordered = false;
+    DevBuf<int32_t> d_perm, d_inv;
+    std::vector<int32_t> h_perm, h_inv;
+    DevBuf<double> io_scratch;  // 3n doubles: caller-order staging of lg_get_field / lg_set_state
 
     PingPong x, v, w;         // read by other particles' pair evaluations -> double-buffered
     DevBuf<double> a, th, al;  // private to their particle -> single
@@ -163,6 +170,9 @@ struct lg_system {
     // step_rows2_kernel: per tile of rows2_tile_particles() particles, the bridges to evaluate (build_bridge_work)
     DevBuf<uint16_t> bwork;
     DevBuf<uint32_t> bwork_cnt;
+    int bwork_shape = -1;            // tile shape the lists were built for (-1: none)
+    std::vector<int32_t> h_brev;     // host copies the lists are rebuilt from when the shape changes
+    std::vector<uint8_t> h_pairable; // record and its mirror carry the same rest lengths
 
     // facets
     std::vector<Facet> facets;
@@ -296,6 +306,8 @@ int build_allpairs(lg_system* s) {
     return retag(s);
 }
 
+int build_bridge_work(lg_system* s, int shape);  // below: work lists of step_rows2_kernel's bridge pass
+
 int drain_profile(lg_system* s) {
     LG_CUDA(cudaStreamSynchronize(s->stream));
     for (size_t k = 0; k < s->prof_used; k++) {
@@ -352,7 +364,13 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     {   // short rows (aggregates) -> row kernel; long rows (packings) -> tile kernel.  LGB200_ROWS_KERNEL=0 disables it.
         static const int rows_enabled = [] { const char* e = std::getenv("LGB200_ROWS_KERNEL"); return e ? std::atoi(e) : 2; }();  // 2 = step_rows2_kernel, 1 = step_rows_kernel, 0 = tile kernel
         const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
-        A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= 24.0))) ? (rows_enabled == 1 ? 1 : 2) : 0;  // variant 2: row kernel whatever the row length
+        static const double rows_kmax = [] { const char* e = std::getenv("LGB200_ROWS_KMAX"); return e ? std::atof(e) : 1.0e9; }();  // mean row length above which the tile kernel takes over
+        A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= (rows_enabled == 1 ? 24.0 : rows_kmax)))) ? (rows_enabled == 1 ? 1 : 2) : 0;  // variant 2: row kernel whatever the row length
+        A.rows_shape = rows2_shape_for(k_mean);
+        if (A.use_rows == 2 && s->n_bonds > 0 && s->bwork_shape != A.rows_shape) {
+            LG_TRY(build_bridge_work(s, A.rows_shape));
+            A.bwork = s->bwork.p; A.bwork_cnt = s->bwork_cnt.p;
+        }
     }
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia, s->mp.hamaker_kind, s->mp.hamaker_cutoff);
     const bool fused = fused_dt >= 0.0;
@@ -630,9 +648,10 @@ namespace {
 // record index, bit 15 set when the item also produces its mirror's value.  Records whose mirror lies in another tile, or
 // whose two orientations carry different rest lengths (possible with explicit tables), stay one-sided.  Tiles with more
 // records than the kernel stages get an empty list (the kernel evaluates them from global memory).
-int build_bridge_work(lg_system* s, const std::vector<uint32_t>& bptr, const std::vector<int32_t>& brev,
-                      const std::vector<double>& len) {
-    const int T = rows2_tile_particles(), cap = rows2_tile_records();
+int build_bridge_work(lg_system* s, int shape) {
+    const std::vector<uint32_t>& bptr = s->h_bptr;
+    const std::vector<int32_t>& brev = s->h_brev;
+    const int T = rows2_tile_particles(shape), cap = rows2_tile_records(shape);
     const size_t n = (size_t)s->n, nb = brev.size();
     const size_t n_tiles = (n + (size_t)T - 1) / (size_t)T;
     std::vector<uint16_t> work(nb + 16, 0);
@@ -645,8 +664,7 @@ int build_bridge_work(lg_system* s, const std::vector<uint32_t>& bptr, const std
         for (uint32_t b = b0; b < b1; b++) {
             const uint32_t m = (uint32_t)brev[b];
             const bool in_tile = m >= b0 && m < b1;
-            const bool same_len = in_tile && std::memcmp(&len[5 * (size_t)b], &len[5 * (size_t)m], 5 * sizeof(double)) == 0;
-            if (in_tile && same_len) {
+            if (in_tile && s->h_pairable[b]) {
                 if (b < m) work[b0 + w++] = (uint16_t)((b - b0) | 0x8000u);
             } else {
                 work[b0 + w++] = (uint16_t)(b - b0);
@@ -659,10 +677,28 @@ int build_bridge_work(lg_system* s, const std::vector<uint32_t>& bptr, const std
     LG_CUDA(cudaMemcpyAsync(s->bwork.p, work.data(), (nb + 16) * sizeof(uint16_t), cudaMemcpyHostToDevice, s->stream));
     LG_CUDA(cudaMemcpyAsync(s->bwork_cnt.p, cnt.data(), (n_tiles + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
+    s->bwork_shape = shape;
     return LG_OK;
 }
 
+// host copies the work lists are derived from; the lists themselves are built for the tile shape of the first launch
+void keep_bond_mirrors(lg_system* s, std::vector<int32_t>&& brev, const std::vector<double>& len) {
+    const size_t nb = brev.size();
+    s->h_pairable.assign(nb, 0);
+    for (size_t b = 0; b < nb; b++) {
+        const size_t m = (size_t)brev[b];
+        s->h_pairable[b] = m < nb && std::memcmp(&len[5 * b], &len[5 * m], 5 * sizeof(double)) == 0;
+    }
+    s->h_brev = std::move(brev);
+    s->bwork_shape = -1;
+}
+
 int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
+    if (s->reordered)  // the caller's indices -> internal numbering (connectors are absolute positions: untouched)
+        for (auto& r : recs) {
+            r.i = (int64_t)s->h_inv[(size_t)r.i];
+            r.j = (int64_t)s->h_inv[(size_t)r.j];
+        }
     // CSR by (i, j) ascending
     std::sort(recs.begin(), recs.end(), [](HostBond const& a, HostBond const& b) { return a.i != b.i ? a.i < b.i : a.j < b.j; });
     const size_t nb = recs.size();
@@ -703,7 +739,7 @@ int install_bonds(lg_system* s, std::vector<HostBond>& recs) {
         LG_CUDA(cudaMemcpyAsync(s->blen.p, len.data(), nb * 5 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
     }
     LG_CUDA(cudaStreamSynchronize(s->stream));
-    LG_TRY(build_bridge_work(s, bptr, brev, len));
+    keep_bond_mirrors(s, std::move(brev), len);
     s->n_bonds = (int64_t)nb;
     s->h_bptr = std::move(bptr);
     s->h_bj = std::move(bj);
@@ -970,6 +1006,53 @@ int lg_destroy(lg_system* s) {
     return LG_OK;
 }
 
+// caller index -> internal index (identity unless the system was renumbered)
+static inline int64_t to_internal(const lg_system* s, int64_t i) { return s->reordered ? (int64_t)s->h_inv[(size_t)i] : i; }
+static inline int64_t to_caller(const lg_system* s, int64_t k) { return s->reordered ? (int64_t)s->h_perm[(size_t)k] : k; }
+
+// Computes the Morton renumbering from the caller-order positions d_x (device) and keeps it on both sides.
+static int compute_reorder(lg_system* s, const double* d_x) {
+    const int n = (int)s->n;
+    cudaStream_t st = s->stream;
+    launch_bbox(n, d_x, s->bbox_scratch.p, s->bbox_out.p, st);
+    double bb[6];
+    LG_CUDA(cudaMemcpyAsync(bb, s->bbox_out.p, sizeof(bb), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    double ext = 0.0;
+    for (int k = 0; k < 3; k++) {
+        if (!std::isfinite(bb[k]) || !std::isfinite(bb[3 + k])) return fail(LG_EINVAL, "non-finite particle positions");
+        ext = std::max(ext, bb[3 + k] - bb[k]);
+    }
+    const double cell = std::max(2.0 * s->mp.r, ext / 255.0);
+    const size_t nc1 = morton_cells() + 1;
+    DevBuf<uint32_t> key, count, cursor, scratch;
+    DevBuf<int32_t> tmp;
+    LG_CUDA(key.reserve((size_t)n));
+    LG_CUDA(count.reserve(nc1));
+    LG_CUDA(cursor.reserve(nc1));
+    LG_CUDA(scratch.reserve(scan_scratch_elems(nc1)));
+    LG_CUDA(tmp.reserve((size_t)n));
+    LG_CUDA(s->d_perm.reserve((size_t)n));
+    LG_CUDA(s->d_inv.reserve((size_t)n));
+    launch_morton_order(n, d_x, bb, cell, key.p, count.p, cursor.p, scratch.p, tmp.p, s->d_perm.p, s->d_inv.p, st);
+    LG_CUDA(cudaGetLastError());
+    s->h_perm.resize((size_t)n);
+    s->h_inv.resize((size_t)n);
+    LG_CUDA(cudaMemcpyAsync(s->h_perm.data(), s->d_perm.p, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaMemcpyAsync(s->h_inv.data(), s->d_inv.p, (size_t)n * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    s->reordered = true;
+    return LG_OK;
+}
+
+int lg_set_reorder(lg_system* s, int mode) {
+    LG_ENTER(s);
+    if (mode != 0 && mode != 1) return fail(LG_EINVAL, "reorder mode must be 0 (caller order) or 1 (spatial)");
+    if (s->state_set) return fail(LG_EINVAL, "lg_set_reorder must precede the first lg_set_state");
+    s->reorder_mode = mode;
+    return LG_OK;
+}
+
 int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v, const double* theta, const double* omega) {
     LG_ENTER(s);
     if (n_check != s->n)
@@ -977,10 +1060,24 @@ int lg_set_state(lg_system* s, int64_t n_check, const double* x, const double* v
     if (!x || !v || !theta || !omega) return fail(LG_EINVAL, "null state pointer");
     LG_TRY(sync_pairs(s));
     const size_t bytes = 3 * (size_t)s->n * sizeof(double);
-    LG_CUDA(cudaMemcpyAsync(s->x.p, x, bytes, cudaMemcpyHostToDevice, s->stream));
-    LG_CUDA(cudaMemcpyAsync(s->v.p, v, bytes, cudaMemcpyHostToDevice, s->stream));
-    LG_CUDA(cudaMemcpyAsync(s->th.p, theta, bytes, cudaMemcpyHostToDevice, s->stream));
-    LG_CUDA(cudaMemcpyAsync(s->w.p, omega, bytes, cudaMemcpyHostToDevice, s->stream));
+    if (s->reorder_mode == 0) {
+        LG_CUDA(cudaMemcpyAsync(s->x.p, x, bytes, cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->v.p, v, bytes, cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->th.p, theta, bytes, cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->w.p, omega, bytes, cudaMemcpyHostToDevice, s->stream));
+    } else {
+        // caller order lands in buffers that hold nothing yet (the ping-pong alternates, a), then one gather per field
+        LG_CUDA(cudaMemcpyAsync(s->x.next, x, bytes, cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->v.next, v, bytes, cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->a.p, theta, bytes, cudaMemcpyHostToDevice, s->stream));
+        LG_CUDA(cudaMemcpyAsync(s->w.next, omega, bytes, cudaMemcpyHostToDevice, s->stream));
+        if (!s->reordered) LG_TRY(compute_reorder(s, s->x.next));  // fixed by the first state: bond tables refer to it
+        launch_gather3((int)s->n, s->d_perm.p, s->x.next, s->x.p, s->stream);
+        launch_gather3((int)s->n, s->d_perm.p, s->v.next, s->v.p, s->stream);
+        launch_gather3((int)s->n, s->d_perm.p, s->a.p, s->th.p, s->stream);
+        launch_gather3((int)s->n, s->d_perm.p, s->w.next, s->w.p, s->stream);
+        LG_CUDA(cudaGetLastError());
+    }
     LG_CUDA(cudaMemsetAsync(s->a.p, 0, bytes, s->stream));
     LG_CUDA(cudaMemsetAsync(s->al.p, 0, bytes, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));  // the caller may reuse its buffers
@@ -1016,6 +1113,12 @@ int lg_get_field(lg_system* s, int field, double* out) {
     if (field == LG_A || field == LG_ALPHA) LG_TRY(flush(s));
     double* src = field_ptr(s, field);
     if (!src || !out) return fail(LG_EINVAL, "bad field id or null output");
+    if (s->reordered) {  // back to the caller's particle order
+        LG_CUDA(s->io_scratch.reserve(3 * (size_t)s->n));
+        launch_gather3((int)s->n, s->d_inv.p, src, s->io_scratch.p, s->stream);
+        LG_CUDA(cudaGetLastError());
+        src = s->io_scratch.p;
+    }
     LG_CUDA(cudaMemcpyAsync(out, src, 3 * (size_t)s->n * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     return check_async(s);
 }
@@ -1025,6 +1128,7 @@ int lg_device_field(lg_system* s, int field, double** d_ptr) {
     if (field == LG_A || field == LG_ALPHA) LG_TRY(flush(s));
     double* src = field_ptr(s, field);
     if (!src || !d_ptr) return fail(LG_EINVAL, "bad field id or null output");
+    if (s->reordered) return fail(LG_EINVAL, "device views are in the internal particle order: not available after lg_set_reorder");
     *d_ptr = src;
     return LG_OK;
 }
@@ -1076,7 +1180,7 @@ int lg_set_integrator(lg_system* s, int integrator) {
 int lg_set_fixed_particle(lg_system* s, int64_t index) {
     LG_ENTER(s);
     if (index < -1 || index >= s->n) return fail(LG_EINVAL, "fixed particle index out of range");
-    s->fixed_particle = (int)index;
+    s->fixed_particle = index >= 0 ? (int)to_internal(s, index) : -1;
     return index >= 0 ? lock_simple(s) : LG_OK;
 }
 
@@ -1131,6 +1235,8 @@ int lg_get_alt_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double spri
     *bonded = 0;
     if (s->n_bonds == 0 || !s->mp.alt_bonds) return LG_OK;
     LG_TRY(flush(s));
+    i = to_internal(s, i);
+    j = to_internal(s, j);
     for (uint32_t b = s->h_bptr[(size_t)i]; b < s->h_bptr[(size_t)i + 1]; b++)
         if (s->h_bj[b] == (int32_t)j) {
             LG_CUDA(cudaMemcpyAsync(springs, s->bspr.p + (size_t)b * 9, 9 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
@@ -1178,7 +1284,13 @@ int lg_build_sinter_bonds(lg_system* s, const lg_contact_params* contact, double
     if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
     const int64_t n = s->n;
     std::vector<double> hx(3 * (size_t)n);
-    LG_CUDA(cudaMemcpyAsync(hx.data(), s->x.p, hx.size() * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    const double* d_x = s->x.p;
+    if (s->reordered) {  // the scan consumes `gen` in the CALLER's lexicographic pair order
+        LG_CUDA(s->io_scratch.reserve(3 * (size_t)n));
+        launch_gather3((int)n, s->d_inv.p, s->x.p, s->io_scratch.p, s->stream);
+        d_x = s->io_scratch.p;
+    }
+    LG_CUDA(cudaMemcpyAsync(hx.data(), d_x, hx.size() * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
     std::vector<HostBond> recs;
     int64_t bonds = 0;
@@ -1382,8 +1494,21 @@ int lg_get_neighbor_rows(lg_system* s, int64_t* row_ptr, int64_t* cols) {
     LG_CUDA(cudaMemcpyAsync(hp.data(), s->row_ptr.p, (n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, s->stream));
     if (p) LG_CUDA(cudaMemcpyAsync(hc.data(), s->cols.p, p * sizeof(int32_t), cudaMemcpyDeviceToHost, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
-    for (size_t i = 0; i <= n; i++) row_ptr[i] = (int64_t)hp[i];
-    for (size_t k = 0; k < p; k++) cols[k] = (int64_t)hc[k];
+    if (!s->reordered) {
+        for (size_t i = 0; i <= n; i++) row_ptr[i] = (int64_t)hp[i];
+        for (size_t k = 0; k < p; k++) cols[k] = (int64_t)hc[k];
+        return LG_OK;
+    }
+    // renumbered system: rows in the caller's order, columns in the caller's ids, ascending
+    row_ptr[0] = 0;
+    for (size_t i = 0; i < n; i++) {
+        const size_t k = (size_t)s->h_inv[i];
+        const size_t len = hp[k + 1] - hp[k];
+        int64_t* dst = cols + row_ptr[i];
+        for (size_t q = 0; q < len; q++) dst[q] = (int64_t)s->h_perm[(size_t)hc[hp[k] + q]];
+        std::sort(dst, dst + len);
+        row_ptr[i + 1] = row_ptr[i] + (int64_t)len;
+    }
     return LG_OK;
 }
 
@@ -1393,6 +1518,8 @@ int lg_get_contact_springs(lg_system* s, int64_t i, int64_t j, double out[9]) {
     std::fill(out, out + 9, 0.0);
     if (!s->slots_ready) return LG_OK;
     LG_TRY(flush(s));
+    i = to_internal(s, i);
+    j = to_internal(s, j);
     std::vector<int32_t> ids((size_t)s->S);
     LG_CUDA(cudaMemcpyAsync(ids.data(), s->sgid.p + (size_t)i * s->S, (size_t)s->S * sizeof(int32_t), cudaMemcpyDeviceToHost,
                             s->stream));
@@ -1412,6 +1539,8 @@ int lg_get_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double conn[15]
     if (!bonded || !conn || !len || i < 0 || j < 0 || i >= s->n || j >= s->n) return fail(LG_EINVAL, "bad arguments");
     *bonded = 0;
     if (s->n_bonds == 0) return LG_OK;
+    i = to_internal(s, i);
+    j = to_internal(s, j);
     for (uint32_t b = s->h_bptr[(size_t)i]; b < s->h_bptr[(size_t)i + 1]; b++)
         if (s->h_bj[b] == (int32_t)j) {
             LG_CUDA(cudaMemcpyAsync(conn, s->bconn.p + (size_t)b * 15, 15 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
@@ -1497,6 +1626,7 @@ int lg_first_half_kick(lg_system* s, double dt) {
 int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, const double* d_theta, const double* d_omega,
                            const double* d_a, const double* d_alpha, int kicked) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_import_state_device: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!d_x || !d_v || !d_theta || !d_omega) return fail(LG_EINVAL, "null state pointer");
     LG_TRY(sync_pairs(s));
     const size_t bytes = 3 * (size_t)s->n * sizeof(double);
@@ -1519,6 +1649,7 @@ int lg_import_state_device(lg_system* s, const double* d_x, const double* d_v, c
 
 int lg_set_owned_device(lg_system* s, const uint8_t* d_owned) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_set_owned_device: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!d_owned) {
         s->has_owned = false;
         return LG_OK;
@@ -1532,6 +1663,7 @@ int lg_set_owned_device(lg_system* s, const uint8_t* d_owned) {
 
 int lg_export_slots(lg_system* s, int* S, int32_t** d_sgid, double** d_spr) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_export_slots: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!S || !d_sgid || !d_spr) return fail(LG_EINVAL, "null output");
     LG_TRY(ensure_slots(s));
     LG_TRY(flush(s));
@@ -1544,6 +1676,7 @@ int lg_export_slots(lg_system* s, int* S, int32_t** d_sgid, double** d_spr) {
 
 int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_spr) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_import_slots_device: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!d_sgid || !d_spr) return fail(LG_EINVAL, "null slot tables");
     LG_TRY(ensure_slots(s));
     const size_t cells = (size_t)s->n * (size_t)s->S;
@@ -1557,6 +1690,7 @@ int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_
 
 int lg_export_bonds(lg_system* s, int64_t* n_ordered, uint32_t** d_bptr, int32_t** d_bj, double** d_bconn, double** d_blen) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_export_bonds: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!n_ordered || !d_bptr || !d_bj || !d_bconn || !d_blen) return fail(LG_EINVAL, "null output");
     LG_CUDA(cudaStreamSynchronize(s->stream));
     *n_ordered = s->n_bonds;
@@ -1571,6 +1705,7 @@ int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, doubl
                            const uint32_t* d_bptr, const int32_t* d_bj, const int32_t* d_brev, const double* d_bconn,
                            const double* d_blen) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_import_bonds_device: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!contact || nb < 0 || !d_bptr || (nb > 0 && (!d_bj || !d_brev || !d_bconn || !d_blen)))
         return fail(LG_EINVAL, "bad bond arguments");
     if (s->mask & MODEL_CONTACT) return fail(LG_EINVAL, "contact model already installed; the sinter model embeds it");
@@ -1599,7 +1734,7 @@ int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, doubl
     if (bptr[n] != (uint32_t)nb) return fail(LG_EINVAL, "bptr[n] does not match the number of bond records");
     for (size_t b = 0; b < (size_t)nb; b++)
         if (h_brev[b] < 0 || h_brev[b] >= (int32_t)nb) return fail(LG_EINVAL, "mirror index out of range");
-    LG_TRY(build_bridge_work(s, bptr, h_brev, h_len));
+    keep_bond_mirrors(s, std::move(h_brev), h_len);
     for (size_t i = 0; i < n; i++)
         if (bptr[i + 1] - bptr[i] > (uint32_t)kMaxBondsPerParticle) return fail(LG_ECAPACITY, "more than 120 bonds on one particle");
     to_cp(contact, s->mp.cp);
@@ -1616,6 +1751,7 @@ int lg_import_bonds_device(lg_system* s, const lg_contact_params* contact, doubl
 
 int lg_halo_pack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec, double* d_out) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_halo_pack: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (n_part < 0 || n_rec < 0 || (n_part > 0 && !d_idx) || (n_rec > 0 && !d_rec) || !d_out) return fail(LG_EINVAL, "bad halo arguments");
     launch_halo_pack(n_part, d_idx, n_rec, d_rec, s->x.p, s->v.p, s->w.p, s->bconn.p, d_out, s->stream);
     LG_CUDA(cudaGetLastError());
@@ -1624,6 +1760,7 @@ int lg_halo_pack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, cons
 
 int lg_halo_unpack(lg_system* s, int n_part, const int32_t* d_idx, int n_rec, const int32_t* d_rec, const double* d_in) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_halo_unpack: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (n_part < 0 || n_rec < 0 || (n_part > 0 && !d_idx) || (n_rec > 0 && !d_rec) || !d_in) return fail(LG_EINVAL, "bad halo arguments");
     launch_halo_unpack(n_part, d_idx, n_rec, d_rec, s->x.p, s->v.p, s->w.p, s->bconn.p, d_in, s->stream);
     LG_CUDA(cudaGetLastError());
@@ -1688,6 +1825,7 @@ int halo_exchange(lg_system* s, lg_halo* hl) {
 
 int lg_halo_create(lg_system* s, int n_peers, const int64_t* recv_doubles, lg_halo** out) {
     LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_halo_create: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
     if (!out || n_peers < 0 || n_peers > kMaxHaloPeers || (n_peers > 0 && !recv_doubles)) return fail(LG_EINVAL, "bad halo arguments");
     std::unique_ptr<lg_halo> hl(new (std::nothrow) lg_halo());
     if (!hl) return fail(LG_ENOMEM, "host allocation failed");
@@ -1845,3 +1983,5 @@ int lg_set_kernel_variant(lg_system* s, int variant) {
 }
 
 }  // extern "C"
+
+#include "dump_impl.cuh"

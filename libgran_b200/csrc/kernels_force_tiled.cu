@@ -680,7 +680,7 @@ __global__ void __launch_bounds__(RT, LG_ROWS_MINB) step_rows_kernel(const __gri
         if constexpr (kContact) {
             if (slow != 0ull || pe - pb > 64u) {  // rare: out of line, so that the hot loop keeps its registers
                 double out6[6];
-                rows_slow_pairs<kSinter, kHamaker>(A, sxw, xlo, xcnt, tid + (i0 - xlo), pb, pe, slow, bonds_staged, have_bonds ? sbptr[tid] : 0u, out6);
+                rows_slow_pairs<kSinter, kHamaker>(A, sxw, xlo, xcnt, tid + (i0 - xlo), pb, pe, pb, 1u, slow, bonds_staged, have_bonds ? sbptr[tid] : 0u, out6);
                 acc_a += load3(out6);
                 acc_al += load3(out6 + 3);
             }

@@ -468,4 +468,81 @@ void launch_diag_sums(int n, const double* x, const double* v, const double* w, 
     g_launch_count += 2;
 }
 
+// ---- spatial renumbering (lg_set_reorder) ------------------------------------------------
+// Particles are renumbered along a Morton (Z-order) curve over cubic cells of edge `cell` (>= one particle diameter, at most
+// 256 cells per axis), so that the neighbours of consecutive particles are themselves (mostly) consecutive and the staged
+// position window of the row kernel holds them.  Counting sort by cell; inside a cell ascending caller id, so the numbering
+// is a pure function of the positions (deterministic).
+__device__ __forceinline__ uint32_t spread3(uint32_t v) {  // 8 bits -> every third bit
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+__device__ __forceinline__ uint32_t morton_key(const double* x, int i, double lx, double ly, double lz, double inv_cell) {
+    const int cx = min(255, max(0, (int)floor((x[3 * (size_t)i] - lx) * inv_cell)));
+    const int cy = min(255, max(0, (int)floor((x[3 * (size_t)i + 1] - ly) * inv_cell)));
+    const int cz = min(255, max(0, (int)floor((x[3 * (size_t)i + 2] - lz) * inv_cell)));
+    return spread3((uint32_t)cx) | (spread3((uint32_t)cy) << 1) | (spread3((uint32_t)cz) << 2);
+}
+__global__ void __launch_bounds__(256) morton_count_kernel(int n, const double* x, double lx, double ly, double lz, double inv_cell,
+                                                           uint32_t* key, uint32_t* count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = morton_key(x, i, lx, ly, lz, inv_cell);
+    key[i] = k;
+    atomicAdd(&count[k], 1u);
+}
+__global__ void __launch_bounds__(256) morton_fill_kernel(int n, const uint32_t* key, const uint32_t* start, uint32_t* cursor,
+                                                          int32_t* tmp) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = key[i];
+    tmp[start[k] + atomicAdd(&cursor[k], 1u)] = i;  // arrival order inside a cell: fixed up by morton_rank_kernel
+}
+// position of particle i = start of its cell + number of particles of the cell with a smaller id
+__global__ void __launch_bounds__(256) morton_rank_kernel(int n, const uint32_t* key, const uint32_t* start, const int32_t* tmp,
+                                                          int32_t* perm, int32_t* inv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t k = key[i];
+    const uint32_t b = start[k], e = start[k + 1];
+    uint32_t rank = 0;
+    for (uint32_t q = b; q < e; q++) rank += tmp[q] < i ? 1u : 0u;
+    perm[b + rank] = i;   // new -> caller
+    inv[i] = (int32_t)(b + rank);  // caller -> new
+}
+// dst[k] = src[idx[k]] for 3-vectors
+__global__ void __launch_bounds__(256) gather3_kernel(int n, const int32_t* idx, const double* src, double* dst) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const size_t q = 3 * (size_t)idx[k];
+    dst[3 * (size_t)k] = src[q];
+    dst[3 * (size_t)k + 1] = src[q + 1];
+    dst[3 * (size_t)k + 2] = src[q + 2];
+}
+
+size_t morton_cells() { return (size_t)1 << 24; }
+
+// key: n u32; count / cursor: morton_cells() + 1 u32 each (zeroed here); tmp, perm, inv: n i32
+void launch_morton_order(int n, const double* x, const double lo[3], double cell, uint32_t* key, uint32_t* count, uint32_t* cursor,
+                         uint32_t* scan_scratch, int32_t* tmp, int32_t* perm, int32_t* inv, cudaStream_t st) {
+    const size_t nc1 = morton_cells() + 1;
+    cudaMemsetAsync(count, 0, nc1 * sizeof(uint32_t), st);
+    cudaMemsetAsync(cursor, 0, nc1 * sizeof(uint32_t), st);
+    const int threads = 256, blocks = (n + threads - 1) / threads;
+    morton_count_kernel<<<blocks, threads, 0, st>>>(n, x, lo[0], lo[1], lo[2], 1.0 / cell, key, count);
+    launch_exclusive_scan_u32(count, nc1, scan_scratch, st);
+    morton_fill_kernel<<<blocks, threads, 0, st>>>(n, key, count, cursor, tmp);
+    morton_rank_kernel<<<blocks, threads, 0, st>>>(n, key, count, tmp, perm, inv);
+    g_launch_count += 3;
+}
+
+void launch_gather3(int n, const int32_t* idx, const double* src, double* dst, cudaStream_t st) {
+    if (n <= 0) return;
+    gather3_kernel<<<(n + 255) / 256, 256, 0, st>>>(n, idx, src, dst);
+    g_launch_count++;
+}
+
 }  // namespace lg

@@ -20,6 +20,8 @@
 // LG/granular_system/binary_force_container.h:20-32, LG/contact_force/contact_force.h:57-147,
 // LG/hamaker_force/hamaker_force.h:28-43, LG/sinter_bridge/sinter_bridge.h:24-94,214-259 and
 // LT/rotational_integrator/rotational_velocity_verlet_half.h:63-73.
+#include <cstdlib>
+
 #include "step_common.cuh"
 
 namespace lg {
@@ -27,44 +29,50 @@ namespace lg {
 namespace {
 
 #ifndef LG_R2_RT
-#define LG_R2_RT 128   // particles per tile
+#define LG_R2_RT 128   // default shape: particles per tile
 #endif
 #ifndef LG_R2_LPP
-#define LG_R2_LPP 2    // lanes per particle in pass 2
+#define LG_R2_LPP 2    // default shape: lanes per particle in pass 2
 #endif
 #ifndef LG_R2_MINB
 #define LG_R2_MINB 2   // resident CTAs per SM the launch bound asks for
 #endif
-constexpr int RT2 = LG_R2_RT;
-constexpr int LPP = LG_R2_LPP;
-constexpr int NT2 = RT2 * LPP;        // compute threads
-constexpr int RH2 = 128;              // halo of the staged x window (particles either side)
-constexpr int RPC2 = 12 * RT2;        // staged columns / tags per tile
-constexpr int RBC2 = 2 * RT2 + 32;    // staged bond records per tile
-static_assert(RT2 % 32 == 0 && (LPP == 1 || LPP == 2 || LPP == 4) && RPC2 % 16 == 0 && RBC2 % 16 == 0, "tile shape");
 
-struct alignas(16) Stage2 {
-    double wx[3 * (RT2 + 2 * RH2) + 4];
-    double wv[3 * RT2 + 4];
-    double ww[3 * RT2 + 4];
-    double wth[3 * RT2 + 4];
-    double wconn[15 * RBC2 + 4];
-    double wlen[5 * RBC2 + 4];
-    uint32_t wrow[RT2 + 12];
-    uint32_t wbond[RT2 + 12];
-    int32_t wcols[RPC2 + 8];
-    int32_t wbj[RBC2 + 8];
-    int32_t wrev[RBC2 + 8];
-    uint16_t wwork[RBC2 + 16];
-    uint8_t wtag[RPC2 + 32];
-};
+// Tile shape: RT particles per tile, LPP cooperating lanes per particle in the pair loop (RT * LPP threads per CTA).
+//   <128, 2>  rows of ~10 neighbors (aggregates)          staged x: the tile +- 128 particles, 12 pairs per particle
+//   < 64, 4>  rows of ~20-45 (fractal clusters, loose packings)     +- 192                  48
+//   < 32, 8>  rows of ~50-100 (dense packings)                      +- 256                  96
+template <int RT_, int LPP_>
+struct Shape {
+    static constexpr int RT = RT_, LPP = LPP_;
+    static constexpr int NT = RT * LPP;                                   // compute threads
+    static constexpr int RH = LPP == 2 ? 128 : LPP == 4 ? 192 : 256;      // halo of the staged x window (particles either side)
+    static constexpr int RPC = (LPP == 2 ? 12 : LPP == 4 ? 48 : 96) * RT; // staged columns / tags per tile
+    static constexpr int RBC = 2 * RT + 32;                               // staged bond records per tile
+    static_assert(RT % 32 == 0 && (LPP == 1 || LPP == 2 || LPP == 4 || LPP == 8) && RPC % 16 == 0 && RBC % 16 == 0, "tile shape");
 
-struct alignas(16) Rows2Smem {
-    Stage2 st;
-    double res[6 * RBC2];     // pass 1 results per bond record; pass 3: dx, dtheta of every particle
-    uint8_t brow[RBC2];       // local row of every staged bond record
-    unsigned long long full;
-    uint32_t nwork;           // bridge work items of the staged tile
+    struct alignas(16) Stage {
+        double wx[3 * (RT + 2 * RH) + 4];
+        double wv[3 * RT + 4];
+        double ww[3 * RT + 4];
+        double wth[3 * RT + 4];
+        double wconn[15 * RBC + 4];
+        double wlen[5 * RBC + 4];
+        uint32_t wrow[RT + 12];
+        uint32_t wbond[RT + 12];
+        int32_t wcols[RPC + 8];
+        int32_t wbj[RBC + 8];
+        int32_t wrev[RBC + 8];
+        uint16_t wwork[RBC + 16];
+        uint8_t wtag[RPC + 32];
+    };
+    struct alignas(16) Smem {
+        Stage st;
+        double res[6 * RBC];     // pass 1 results per bond record; pass 3: dx, dtheta of every particle
+        uint8_t brow[RBC];       // local row of every staged bond record
+        unsigned long long full;
+        uint32_t nwork;           // bridge work items of the staged tile
+    };
 };
 
 __device__ __forceinline__ void compute_barrier() { __syncthreads(); }
@@ -93,8 +101,12 @@ __device__ __forceinline__ void l2_prefetch(const void* begin, uint32_t nbytes) 
     asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
 }
 
-template <int MASK, int MODE, bool FACETS>
-__global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
+template <int MASK, int MODE, bool FACETS, int RT2, int LPP>
+__global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
+    using SH = Shape<RT2, LPP>;
+    using Stage2 = typename SH::Stage;
+    using Rows2Smem = typename SH::Smem;
+    constexpr int NT2 = SH::NT, RH2 = SH::RH, RPC2 = SH::RPC, RBC2 = SH::RBC;
     constexpr bool kContact = (MASK & (MODEL_CONTACT | MODEL_SINTER)) != 0;
     constexpr bool kSinter = (MASK & MODEL_SINTER) != 0;
     constexpr bool kHamaker = (MASK & MODEL_HAMAKER) != 0;
@@ -321,6 +333,17 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
                 acc_a += pa;
             }
         }
+        if constexpr (kContact) {
+            // rare: out of line, so that the hot loop keeps its registers.  Every lane evaluates the pairs IT marked (and its
+            // share of the pairs beyond the 64-bit mask), so the contacts of a dense row spread over the LPP lanes.
+            if (live && (slow != 0ull || pe - pb > 64u)) {
+                double out6[6];
+                rows_slow_pairs<kSinter, kHamaker>(A, sxw, xlo, xcnt, r + (i0 - xlo), pb, pe, pb + (uint32_t)lp, (uint32_t)LPP, slow,
+                                                   bonds_staged, have_bonds ? sbptr[r] : 0u, out6);
+                acc_a += load3(out6);
+                acc_al += load3(out6 + 3);
+            }
+        }
         if constexpr (LPP > 1) {  // fixed-shape combination of the lanes' partial sums (all 32 lanes take part)
 #pragma unroll
             for (int off = 1; off < LPP; off <<= 1) {
@@ -330,21 +353,11 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
                 acc_al.x += __shfl_xor_sync(0xffffffffu, acc_al.x, off);
                 acc_al.y += __shfl_xor_sync(0xffffffffu, acc_al.y, off);
                 acc_al.z += __shfl_xor_sync(0xffffffffu, acc_al.z, off);
-                if constexpr (kContact) slow |= __shfl_xor_sync(0xffffffffu, slow, off);
             }
         }
         d3 xn = zero3(), vn = zero3(), wn = zero3(), dth = zero3(), dxv = zero3();
         if (live && lp == 0) {
             const d3 vi = load3(sv + 3 * r), wi = load3(sw + 3 * r);
-            if constexpr (kContact) {
-                if (slow != 0ull || pe - pb > 64u) {  // rare: out of line, so that the hot loop keeps its registers
-                    double out6[6];
-                    rows_slow_pairs<kSinter, kHamaker>(A, sxw, xlo, xcnt, r + (i0 - xlo), pb, pe, slow, bonds_staged,
-                                                       have_bonds ? sbptr[r] : 0u, out6);
-                    acc_a += load3(out6);
-                    acc_al += load3(out6 + 3);
-                }
-            }
             if constexpr (FACETS) {
                 const Accel u = unary_forces(A, i0 + r, xi, vi, wi);
                 acc_a += u.a;
@@ -426,29 +439,36 @@ __global__ void __launch_bounds__(NT2, LG_R2_MINB) step_rows2_kernel(const __gri
     if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
 }
 
-int resident_ctas_rows2(const void* fn) {
-    int dev = 0, sms = 0, occ = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, NT2, sizeof(Rows2Smem));
-    return sms * (occ > 0 ? occ : 1);
+template <int MASK, int MODE, bool FACETS, int RT2, int LPP>
+void launch_rows2_one(const ForceArgs& args, cudaStream_t st) {
+    using SH = Shape<RT2, LPP>;
+    static int grid_cap = 0;  // per instantiation
+    if (grid_cap == 0) {
+        const void* fn = (const void*)step_rows2_kernel<MASK, MODE, FACETS, RT2, LPP>;
+        cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(typename SH::Smem));
+        int dev = 0, sms = 0, occ = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, SH::NT, sizeof(typename SH::Smem));
+        grid_cap = sms * (occ > 0 ? occ : 1);
+    }
+    const int n_tiles = (args.n + RT2 - 1) / RT2;
+    step_rows2_kernel<MASK, MODE, FACETS, RT2, LPP><<<min(n_tiles, grid_cap), SH::NT, sizeof(typename SH::Smem), st>>>(args);
+    g_launch_count++;
 }
 
 template <int MASK, int MODE, bool FACETS>
-void launch_rows2_one(const ForceArgs& args, cudaStream_t st) {
-    static int grid_cap = 0;  // per instantiation
-    if (grid_cap == 0) {
-        cudaFuncSetAttribute(step_rows2_kernel<MASK, MODE, FACETS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(Rows2Smem));
-        grid_cap = resident_ctas_rows2((const void*)step_rows2_kernel<MASK, MODE, FACETS>);
+void launch_rows2_shape(const ForceArgs& args, cudaStream_t st) {
+    switch (args.rows_shape) {
+        case 1: launch_rows2_one<MASK, MODE, FACETS, 64, 4>(args, st); break;
+        case 2: launch_rows2_one<MASK, MODE, FACETS, 32, 8>(args, st); break;
+        default: launch_rows2_one<MASK, MODE, FACETS, LG_R2_RT, LG_R2_LPP>(args, st); break;
     }
-    const int n_tiles = (args.n + RT2 - 1) / RT2;
-    step_rows2_kernel<MASK, MODE, FACETS><<<min(n_tiles, grid_cap), NT2, sizeof(Rows2Smem), st>>>(args);
-    g_launch_count++;
 }
 
 template <int MASK, int MODE>
 void launch_rows2_facets(const ForceArgs& args, cudaStream_t st) {
-    if (args.n_facets > 0) launch_rows2_one<MASK, MODE, true>(args, st); else launch_rows2_one<MASK, MODE, false>(args, st);
+    if (args.n_facets > 0) launch_rows2_shape<MASK, MODE, true>(args, st); else launch_rows2_shape<MASK, MODE, false>(args, st);
 }
 
 template <int MODE>
@@ -465,8 +485,14 @@ void launch_rows2_mode(const ForceArgs& args, int mask, cudaStream_t st) {
 
 }  // namespace
 
-int rows2_tile_particles() { return RT2; }
-int rows2_tile_records() { return RBC2; }
+// tile shape the launch will use for a mean row length (api.cu builds the bridge work lists for its tile size)
+int rows2_shape_for(double k_mean) {
+    static const int forced = [] { const char* e = std::getenv("LGB200_ROWS_SHAPE"); return e ? std::atoi(e) : -1; }();
+    if (forced >= 0 && forced <= 2) return forced;
+    return k_mean <= 16.0 ? 0 : k_mean <= 48.0 ? 1 : 2;
+}
+int rows2_tile_particles(int shape) { return shape == 1 ? 64 : shape == 2 ? 32 : LG_R2_RT; }
+int rows2_tile_records(int shape) { return 2 * rows2_tile_particles(shape) + 32; }
 
 void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {
     if (fused) launch_rows2_mode<MODE_FUSED>(args, mask, st); else launch_rows2_mode<MODE_FORCE>(args, mask, st);

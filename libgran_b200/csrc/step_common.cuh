@@ -174,12 +174,12 @@ __device__ __noinline__ void bridge_from_global(const ForceArgs& A, int i, int j
 // (Luding contact) and pairs inside the rounding band of zero overlap (decided on the reference's exact expression).
 // Returns the sum of their pair values (law + Hamaker) in ascending j.
 template <bool kSinter, bool kHamaker>
-__device__ __noinline__ void rows_slow_pairs(const ForceArgs& A, const double* sx, int i0, int nrows, int r, uint32_t pb, uint32_t pe,  // sx: staged x of particles i0 .. i0 + nrows; r: this particle's index in it
-
+__device__ __noinline__ void rows_slow_pairs(const ForceArgs& A, const double* sx, int i0, int nrows, int r,  // sx: staged x of particles i0 .. i0 + nrows; r: this particle's index in it
+                                             uint32_t pb, uint32_t pe, uint32_t p_first, uint32_t stride,      // this caller's share of the row: p_first, p_first + stride, ... (< pe)
                                              unsigned long long slow, bool bonds_staged, uint32_t bond_base, double* out6) {
     const d3 xi = load3(sx + 3 * r);
     d3 acc_a = zero3(), acc_al = zero3();
-    for (uint32_t p = pb; p < pe; p++) {
+    for (uint32_t p = p_first; p < pe; p += stride) {
         const uint32_t k = p - pb;
         if (k < 64u && !((slow >> k) & 1ull)) continue;
         const int j = A.cols[p];

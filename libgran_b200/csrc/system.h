@@ -86,6 +86,7 @@ struct ForceArgs {
     // tiled / fused kernel only
     int rows_per_block;
     int fast;           // relaxed arithmetic (lg_set_math_mode)
+    int rows_shape;     // step_rows2_kernel: tile shape index (rows2_shape_for)
     int use_rows;       // fast only: short rows -> a row kernel instead of the tile kernel (1 step_rows_kernel, 2 step_rows2_kernel)
     FastConsts fc;      // its host-computed constants
     double dt;          // integration step of the fused update
@@ -127,8 +128,9 @@ void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st)
 // tiled kernel: force only (fused == false) or force + integrate into the next-step buffers (fused == true)
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st);
 void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st);  // kernels_rows.cu
-int rows2_tile_particles();
-int rows2_tile_records();
+int rows2_shape_for(double k_mean);   // tile shape index of step_rows2_kernel for a mean row length
+int rows2_tile_particles(int shape);
+int rows2_tile_records(int shape);
 int tiled_max_rows_per_block();
 int tiled_tile_pairs();
 void launch_integrate(const IntegrateArgs& args, cudaStream_t st);
@@ -140,6 +142,11 @@ void launch_bbox(int n, const double* x, double* d_scratch, double* d_out, cudaS
 size_t scan_scratch_elems(size_t n);
 void launch_exclusive_scan_u32(uint32_t* data, size_t n, uint32_t* scratch, cudaStream_t st);
 
+// spatial renumbering (kernels_neighbor.cu)
+size_t morton_cells();
+void launch_morton_order(int n, const double* x, const double lo[3], double cell, uint32_t* key, uint32_t* count, uint32_t* cursor,
+                         uint32_t* scan_scratch, int32_t* tmp, int32_t* perm, int32_t* inv, cudaStream_t st);
+void launch_gather3(int n, const int32_t* idx, const double* src, double* dst, cudaStream_t st);
 void launch_cell_count(int n, const double* x, NeighborGrid g, int32_t* cell_of, uint32_t* cell_count, cudaStream_t st);
 void launch_cell_fill(int n, const int32_t* cell_of, const uint32_t* cell_start, uint32_t* cell_cursor, int32_t* order,
                       cudaStream_t st);

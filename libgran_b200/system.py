@@ -34,7 +34,7 @@ ABI_SYMBOLS = (
     "lg_gen_fractal_aggregate", "lg_gen_random_packing",
     # SURVEY.md section 8f variants
     "lg_set_hamaker_variant", "lg_set_integrator", "lg_set_fixed_particle", "lg_set_central_attraction",
-    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond",
+    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder",
     # slab decomposition support
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
@@ -133,6 +133,7 @@ def load_library(path: Optional[str] = None):
     lib.lg_alt_bond_table_create.argtypes = [C.c_int64, vp, C.c_double, C.c_double, C.POINTER(vp)]
     lib.lg_set_alt_bond_table.argtypes = [vp, cpp, dp, vp]
     lib.lg_get_alt_bond.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int), dp]
+    lib.lg_set_reorder.argtypes = [vp, C.c_int]
     # slab decomposition support: device pointers travel as plain integers
     lib.lg_flush.argtypes = [vp]
     lib.lg_first_half_kick.argtypes = [vp, C.c_double]
@@ -181,7 +182,7 @@ class GranularSystem:
     """One device-resident granular system (handle of the C ABI)."""
 
     def __init__(self, x0, v0, theta0, omega0, r_part: float, mass: float, inertia: float, device: int = -1,
-                 r_verlet: Optional[float] = None):
+                 r_verlet: Optional[float] = None, reorder: bool = False):
         self.lib = load_library()
         x0, v0, theta0, omega0 = (_c3(a) for a in (x0, v0, theta0, omega0))
         # rotational_system.h:69-70
@@ -192,6 +193,8 @@ class GranularSystem:
         self._facets = 0
         self._cb_keepalive = []
         self._check(self.lib.lg_create(self.n, float(r_part), float(mass), float(inertia), int(device), C.byref(self.h)))
+        if reorder:  # internal spatial renumbering (lg_set_reorder): invisible here, every call speaks the caller's order
+            self._check(self.lib.lg_set_reorder(self.h, 1))
         self._check(self.lib.lg_set_state(self.h, self.n, _dp(x0), _dp(v0), _dp(theta0), _dp(omega0)))
         if r_verlet is not None:
             self.enable_neighbor_list(r_verlet)
@@ -430,12 +433,12 @@ class GranularSystem:
 
 
 def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1, variant: Optional[int] = None,
-                math_mode: int = 0, bonds=None) -> GranularSystem:
+                math_mode: int = 0, bonds=None, reorder: bool = False) -> GranularSystem:
     """Build a GranularSystem from a ``scenarios.DemConfig`` (same meaning as oracle/dem_config.h)."""
     from .scenarios import MODEL_ALT_SINTER, MODEL_CONTACT, MODEL_FACET, MODEL_HAMAKER, MODEL_SINTER
 
     sysm = GranularSystem(x0, v0, theta0, omega0, cfg.r_part, cfg.mass, cfg.inertia, device=device,
-                          r_verlet=cfg.r_verlet if cfg.use_neighbor_list else None)
+                          r_verlet=cfg.r_verlet if cfg.use_neighbor_list else None, reorder=reorder)
     if variant is not None:
         sysm.set_kernel_variant(variant)
     if math_mode:
