@@ -171,6 +171,13 @@ struct lg_system {
     DevBuf<uint16_t> bwork;
     DevBuf<uint32_t> bwork_cnt;
     int bwork_shape = -1;            // tile shape the lists were built for (-1: none)
+    // tile shape of step_rows2_kernel: heuristic (deterministic) or, after lg_set_autotune(1), measured on the first fused launches
+    int autotune = 0;
+    int tuned_shape = -1;
+    double tuned_k = 0.0;
+    int tune_launch = 0;             // 0 .. 3 * kTuneReps - 1 while measuring
+    float tune_ms[3] = {0.f, 0.f, 0.f};
+    cudaEvent_t tune_ev[2] = {nullptr, nullptr};
     std::vector<int32_t> h_brev;     // host copies the lists are rebuilt from when the shape changes
     std::vector<uint8_t> h_pairable; // record and its mirror carry the same rest lengths
 
@@ -337,8 +344,11 @@ int rows_per_block(const lg_system* s) {
 //   fused_dt < 0 : force only, a / alpha <- result (CLEAN afterwards)
 //   fused_dt >= 0: variant 1 only; force at the current state, then integrate with fused_dt into the next-step
 //                  buffers and swap them
+constexpr int kTuneReps = 3;
+
 int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -1.0) {
     ForceArgs A{};
+    bool tuning = false;
     A.n = (int)s->n;
     A.x = s->x.p; A.v = s->v.p; A.w = s->w.p; A.a = s->a.p; A.al = s->al.p;
     A.row_ptr = s->row_ptr.p; A.cols = s->cols.p; A.tag = s->tag.p;
@@ -366,7 +376,16 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
         static const double rows_kmax = [] { const char* e = std::getenv("LGB200_ROWS_KMAX"); return e ? std::atof(e) : 1.0e9; }();  // mean row length above which the tile kernel takes over
         A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= (rows_enabled == 1 ? 24.0 : rows_kmax)))) ? (rows_enabled == 1 ? 1 : 2) : 0;  // variant 2: row kernel whatever the row length
-        A.rows_shape = rows2_shape_for(k_mean);
+        A.rows_shape = rows2_shape_for(k_mean, (int)s->n, s->n_bonds > 0);
+        if (A.use_rows == 2 && s->autotune && std::getenv("LGB200_ROWS_SHAPE") == nullptr) {
+            if (s->tuned_shape >= 0 && std::fabs(k_mean - s->tuned_k) <= 0.25 * s->tuned_k) {
+                A.rows_shape = s->tuned_shape;
+            } else if (fused_dt >= 0.0) {  // measure: kTuneReps fused launches per shape, the first of each discarded
+                if (s->tuned_shape >= 0) { s->tuned_shape = -1; s->tune_launch = 0; }
+                A.rows_shape = s->tune_launch / kTuneReps;
+                tuning = true;
+            }
+        }
         if (A.use_rows == 2 && s->n_bonds > 0 && s->bwork_shape != A.rows_shape) {
             LG_TRY(build_bridge_work(s, A.rows_shape));
             A.bwork = s->bwork.p; A.bwork_cnt = s->bwork_cnt.p;
@@ -375,6 +394,13 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia, s->mp.hamaker_kind, s->mp.hamaker_cutoff);
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;
+    if (tuning) {
+        if (!s->tune_ev[0]) {
+            LG_CUDA(cudaEventCreate(&s->tune_ev[0]));
+            LG_CUDA(cudaEventCreate(&s->tune_ev[1]));
+        }
+        LG_CUDA(cudaEventRecord(s->tune_ev[0], s->stream));
+    }
     A.x_next = s->x.next; A.v_next = s->v.next; A.w_next = s->w.next; A.th = s->th.p; A.bconn_next = s->bconn.next;
     if (s->profiling) {
         if (s->prof_used == s->prof_events.size()) {
@@ -395,6 +421,22 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     s->last_kernel = s->variant == 0 ? "force_simple_kernel" : (A.fast && A.use_rows) ? (A.use_rows == 2 ? "step_rows2_kernel" : "step_rows_kernel") : "step_tiled_kernel";
     if (s->profiling) LG_CUDA(cudaEventRecord(s->prof_events[s->prof_used++].second, s->stream));
     LG_CUDA(cudaGetLastError());
+    if (tuning) {
+        LG_CUDA(cudaEventRecord(s->tune_ev[1], s->stream));
+        LG_CUDA(cudaEventSynchronize(s->tune_ev[1]));
+        float ms = 0.f;
+        LG_CUDA(cudaEventElapsedTime(&ms, s->tune_ev[0], s->tune_ev[1]));
+        const int shape = s->tune_launch / kTuneReps, rep_idx = s->tune_launch % kTuneReps;
+        if (rep_idx == 1 || (rep_idx > 1 && ms < s->tune_ms[shape])) s->tune_ms[shape] = ms;
+        if (++s->tune_launch == 3 * kTuneReps) {
+            int best = 0;
+            for (int k = 1; k < 3; k++)
+                if (s->tune_ms[k] < s->tune_ms[best]) best = k;
+            s->tuned_shape = best;
+            s->tuned_k = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
+            s->tune_launch = 0;
+        }
+    }
     if (fused) {
         s->x.swap();
         s->v.swap();
@@ -1244,6 +1286,21 @@ int lg_get_alt_bond(lg_system* s, int64_t i, int64_t j, int* bonded, double spri
             *bonded = 1;
             break;
         }
+    return LG_OK;
+}
+
+int lg_set_autotune(lg_system* s, int enabled) {
+    LG_ENTER(s);
+    s->autotune = enabled ? 1 : 0;
+    if (!enabled) s->tuned_shape = -1;
+    return LG_OK;
+}
+
+int lg_get_rows_shape(lg_system* s, int* shape) {
+    LG_ENTER(s);
+    if (!shape) return fail(LG_EINVAL, "null output");
+    const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
+    *shape = (s->autotune && s->tuned_shape >= 0) ? s->tuned_shape : rows2_shape_for(k_mean, (int)s->n, s->n_bonds > 0);
     return LG_OK;
 }
 

@@ -128,7 +128,7 @@ void launch_force(const ForceArgs& args, int mask, int variant, cudaStream_t st)
 // tiled kernel: force only (fused == false) or force + integrate into the next-step buffers (fused == true)
 void launch_step_tiled(const ForceArgs& args, int mask, bool fused, cudaStream_t st);
 void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st);  // kernels_rows.cu
-int rows2_shape_for(double k_mean);   // tile shape index of step_rows2_kernel for a mean row length
+int rows2_shape_for(double k_mean, int n, bool bonds);   // tile shape index of step_rows2_kernel for a mean row length
 int rows2_tile_particles(int shape);
 int rows2_tile_records(int shape);
 int tiled_max_rows_per_block();

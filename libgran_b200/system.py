@@ -34,7 +34,9 @@ ABI_SYMBOLS = (
     "lg_gen_fractal_aggregate", "lg_gen_random_packing",
     # SURVEY.md section 8f variants
     "lg_set_hamaker_variant", "lg_set_integrator", "lg_set_fixed_particle", "lg_set_central_attraction",
-    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder",
+    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder", "lg_set_autotune", "lg_get_rows_shape",
+    "lg_dumper_create", "lg_dump_particles", "lg_dump_necks", "lg_dump_spring_connectors", "lg_dump_particles_csv",
+    "lg_dumper_wait", "lg_dumper_destroy", "lg_write_particles", "lg_write_necks", "lg_write_spring_connectors",
     # slab decomposition support
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
@@ -134,6 +136,17 @@ def load_library(path: Optional[str] = None):
     lib.lg_set_alt_bond_table.argtypes = [vp, cpp, dp, vp]
     lib.lg_get_alt_bond.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int), dp]
     lib.lg_set_reorder.argtypes = [vp, C.c_int]
+    lib.lg_set_autotune.argtypes = [vp, C.c_int]
+    lib.lg_get_rows_shape.argtypes = [vp, C.POINTER(C.c_int)]
+    lib.lg_dumper_create.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
+    for name in ("lg_dump_particles", "lg_dump_necks", "lg_dump_spring_connectors"):
+        getattr(lib, name).argtypes = [vp, vp]
+    lib.lg_dump_particles_csv.argtypes = [vp, vp, C.c_int64]
+    lib.lg_dumper_wait.argtypes = [vp]
+    lib.lg_dumper_destroy.argtypes = [vp]
+    lib.lg_write_particles.argtypes = [C.c_char_p, C.c_int64, dp, dp, C.c_double]
+    lib.lg_write_necks.argtypes = [C.c_char_p, C.c_int64, dp, C.c_double, C.c_int64, ip]
+    lib.lg_write_spring_connectors.argtypes = [C.c_char_p, C.c_double, C.c_int64, dp]
     # slab decomposition support: device pointers travel as plain integers
     lib.lg_flush.argtypes = [vp]
     lib.lg_first_half_kick.argtypes = [vp, C.c_double]
@@ -268,6 +281,14 @@ class GranularSystem:
         out, flag = np.zeros(9), C.c_int(0)
         self._check(self.lib.lg_get_alt_bond(self.h, int(i), int(j), C.byref(flag), _dp(out)))
         return out if flag.value else None
+
+    def set_autotune(self, on: bool = True):
+        self._check(self.lib.lg_set_autotune(self.h, int(bool(on))))
+
+    def rows_shape(self) -> int:
+        v = C.c_int(-1)
+        self._check(self.lib.lg_get_rows_shape(self.h, C.byref(v)))
+        return int(v.value)
 
     def set_max_contacts(self, m: int):
         self._check(self.lib.lg_set_max_contacts(self.h, int(m)))
@@ -430,6 +451,43 @@ class GranularSystem:
         self._check(self.lib.lg_diagnostics(self.h, _dp(out)))
         return {"ke": out[0], "ke_trans": out[1], "ke_rot": out[2], "p": out[3], "l": out[4], "com": out[5:8].copy(),
                 "rg": out[8]}
+
+
+class Dumper:
+    """The dump pipeline of a system (lg_dumper_*): VTK files as the reference's writer.cpp writes them, produced off the
+    time loop (device snapshot -> copy stream -> background writer thread)."""
+
+    def __init__(self, system: GranularSystem, directory: str):
+        self.sys = system
+        self.lib = system.lib
+        self.h = C.c_void_p()
+        system._check(self.lib.lg_dumper_create(system.h, os.fsencode(directory), C.byref(self.h)))
+
+    def particles(self):
+        self.sys._check(self.lib.lg_dump_particles(self.sys.h, self.h))
+
+    def necks(self):
+        self.sys._check(self.lib.lg_dump_necks(self.sys.h, self.h))
+
+    def spring_connectors(self):
+        self.sys._check(self.lib.lg_dump_spring_connectors(self.sys.h, self.h))
+
+    def particles_csv(self, count: int):
+        self.sys._check(self.lib.lg_dump_particles_csv(self.sys.h, self.h, int(count)))
+
+    def wait(self):
+        self.sys._check(self.lib.lg_dumper_wait(self.h))
+
+    def close(self):
+        if self.h:
+            self.lib.lg_dumper_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1, variant: Optional[int] = None,
