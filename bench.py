@@ -211,6 +211,8 @@ def run_ours(args):
     bonds = scn.make_bonds(uv) if scn.make_bonds is not None else None
     reorder = (args.reorder == "on") or (args.reorder == "auto" and mode == 1 and args.config in ("2", "3", "5", "5d"))
     sysm = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode, bonds=bonds, reorder=reorder)
+    if mode == 1 and not args.no_autotune:
+        sysm.set_autotune(True)  # tile shape of step_rows2_kernel measured on the first fused launches (inside the warm-up)
     stream = torch.cuda.ExternalStream(sysm.stream_handle(), device=torch.device("cuda", local_rank))
 
     def timed_run(k):
@@ -269,7 +271,7 @@ def run_ours(args):
             print(json.dumps({"config": args.config, "math": args.math, "value": round(value, 1), "ms_per_step": round(ms / args.steps, 5),
                               "particles": n, "pairs": cnt["pairs"], "contacts": cnt["contacts"], "bonds_ordered": cnt["bonds"],
                               "roofline": roofline, "gpu_launches": int(launches), "clocks": clocks,
-                              "reorder": reorder, "lib": os.environ.get("LGB200_LIB", "default"), "tag": os.environ.get("LGB200_TAG")}))
+                              "reorder": reorder, "rows_shape": sysm.rows_shape(), "lib": os.environ.get("LGB200_LIB", "default"), "tag": os.environ.get("LGB200_TAG")}))
         return
 
     # ---- end to end through the host-facing API with host buffers ---------------------------------
@@ -278,6 +280,8 @@ def run_ours(args):
     outs = [torch.empty((n, 3), dtype=torch.float64).pin_memory() for _ in range(4)]
     out_np = [t.numpy() for t in outs]
     e2e_sys = from_config(cfg, *scn.state, unit_vectors=uv, device=local_rank, variant=args.variant, math_mode=mode, bonds=bonds, reorder=reorder)  # model tables built once (as a ctor would)
+    if mode == 1 and not args.no_autotune:
+        e2e_sys.set_autotune(True)
     facet0 = e2e_sys.facet_vertices(0) if moves else None
     e2e_steps = args.steps
     # untimed priming with dt = 0: sizes the neighbor / scratch buffers for exactly this state and leaves positions,
@@ -318,7 +322,7 @@ def run_ours(args):
                    "l2_policy": ("working set larger than L2" if step_bytes > 3 * 126e6 else
                                  f"working set {step_bytes / 1e6:.1f} MB per step is L2-resident by nature of this config (the whole "
                                  "system is smaller than the 126 MB L2); every byte is rewritten each step"),
-                   "kernel_variant": args.variant, "internal_renumbering": reorder, "math_mode": "fast (<=1e-10 rel. forces, bit-exact sets)" if mode else "exact (bit-identical to the reference)"},
+                   "kernel_variant": args.variant, "internal_renumbering": reorder, "rows_tile_shape": sysm.rows_shape(), "math_mode": "fast (<=1e-10 rel. forces, bit-exact sets)" if mode else "exact (bit-identical to the reference)"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
     }
     if rank == 0 and not args.no_cpu_baseline:
@@ -572,6 +576,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--reorder", default="auto", choices=["auto", "on", "off"],
                     help="internal spatial renumbering (lg_set_reorder); auto = on for the configs whose input order has no locality (2, 3, 5, 5d) in fast math")
+    ap.add_argument("--no-autotune", action="store_true", help="keep the deterministic tile-shape rule instead of measuring the shapes")
     ap.add_argument("--kernel-only", action="store_true", help="tuning runs: device-resident throughput + roofline only")
     args = ap.parse_args()
     if args.impl == "reference":

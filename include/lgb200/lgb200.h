@@ -130,6 +130,13 @@ int lg_set_bonds(lg_system* s, const lg_contact_params* contact, double k_d, dou
 typedef struct lg_bond_table lg_bond_table;
 int lg_bond_table_create(int64_t n, const double* x_3n, double r_part, double critical_separation,
                          lg_unit_vector_fn gen, void* user, lg_bond_table** out);
+/* lg_bond_table_create on the GPU (device-side bond detection): candidate partners from the cell
+ * list, the reference's predicate and construction, bond number k in lexicographic (i < j) order takes unit vector k of
+ * `unit_vectors_3m` (the draws of the reference's generator, in order).  Same table as the host scan, bit for bit; a vector
+ * collinear with its bond axis (the reference draws again, sinter_bridge.h:171-175) makes it fall back to the host scan.
+ * device = CUDA ordinal or -1. */
+int lg_bond_table_create_device(int64_t n, const double* x_3n, double r_part, double critical_separation, int64_t n_unit_vectors,
+                                const double* unit_vectors_3m, int device, lg_bond_table** out);
 int lg_bond_table_count(const lg_bond_table* t, int64_t* n_bonds);
 int lg_bond_table_records(const lg_bond_table* t, int64_t* ij_pairs, double* connectors_15, double* rest_lengths_5);
 int lg_bond_table_destroy(lg_bond_table* t);

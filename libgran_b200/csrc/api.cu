@@ -18,6 +18,7 @@
 
 #include "../../include/lgb200/lgb200.h"
 #include "system.h"
+#include "bond_build.cuh"
 
 namespace lg {
 thread_local int64_t g_launch_count = 0;
@@ -870,29 +871,16 @@ static void scan_bonds(int64_t n, const std::vector<double>& hx, double r, doubl
         const d3 part_i = X(i);
         for (int64_t j : cand) {
             const d3 part_j = X(j);
-            const double separation = norm(part_j - part_i) - 2.0 * r;
-            if (std::fabs(separation) > crit) continue;  // sinter_bridge.h:155-157
-            const d3 n_i = normalized(part_j - part_i);
-            const d3 n_j = -n_i;
-            d3 tv, db;
-            do {  // :171-175
+            if (!bridge_candidate(part_i, part_j, r, crit)) continue;  // sinter_bridge.h:155-157
+            HostBond bi{}, bjr{};
+            bi.i = i; bi.j = j; bjr.i = j; bjr.j = i;
+            d3 tv;
+            do {  // :171-175: draw again while the vector is collinear with the bond axis
                 double t[3];
                 gen(user, t);
                 tv = mk3(t[0], t[1], t[2]);
-                db = cross(tv, n_j);
-            } while (norm(db) == 0.0);
-            d3 ds = tv - dot(tv, n_i) * n_i;
-            db = db / sqrt(dot(db, db));
-            ds = ds / sqrt(dot(ds, ds));
-            HostBond bi{}, bjr{};
-            bi.i = i; bi.j = j; bjr.i = j; bjr.j = i;
-            const d3 ci[5] = {part_i + ds * r, part_i - ds * r, part_i + db * r, part_i - db * r, part_i + n_i * r};
-            const d3 cj[5] = {part_j + ds * r, part_j - ds * r, part_j + db * r, part_j - db * r, part_j + n_j * r};
-            for (int k = 0; k < 5; k++) {
-                store3(bi.conn + 3 * k, ci[k]);
-                store3(bjr.conn + 3 * k, cj[k]);
-                bi.len[k] = bjr.len[k] = (k < 4) ? 2.0 * r : 0.0;
-            }
+            } while (!build_bridge(part_i, part_j, tv, r, bi.conn, bjr.conn));
+            for (int k = 0; k < 5; k++) bi.len[k] = bjr.len[k] = (k < 4) ? 2.0 * r : 0.0;
             recs.push_back(bi);
             recs.push_back(bjr);
             bonds++;
@@ -1370,6 +1358,144 @@ int lg_bond_table_create(int64_t n, const double* x, double r_part, double crit,
     t->n = n;
     std::vector<double> hx(x, x + 3 * (size_t)n);
     scan_bonds(n, hx, r_part, crit, gen, user, t->recs, t->bonds);
+    *out = t.release();
+    return LG_OK;
+}
+
+// The same table built on the GPU (kernels_bonds.cu): candidates from the cell list, bond k in lexicographic pair order takes
+// unit vector k.  Falls back to the sequential host scan when a vector is collinear with its bond axis (the reference would
+// redraw and shift every later draw) -- the result is the reference's in either case.
+int lg_bond_table_create_device(int64_t n, const double* x, double r_part, double crit, int64_t n_uv, const double* uv, int device,
+                                lg_bond_table** out) {
+    if (!out) return fail(LG_EINVAL, "out is null");
+    *out = nullptr;
+    if (n <= 0 || n > 2000000000LL || !x || !uv || n_uv < 0 || !(r_part > 0.0)) return fail(LG_EINVAL, "bad arguments to lg_bond_table_create_device");
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count <= 0) return fail(LG_ENODEVICE, "no CUDA device available (use lg_bond_table_create)");
+    if (device < 0) LG_CUDA(cudaGetDevice(&device));
+    if (device >= count) return fail(LG_ENODEVICE, "device ordinal out of range");
+    DeviceGuard guard(device);
+    cudaStream_t st = nullptr;
+    LG_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+    struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } sg{st};
+    const int ni = (int)n;
+    const size_t n3 = 3 * (size_t)n;
+    DevBuf<double> dx, duv, bbs, bbo, dconn, dlen;
+    DevBuf<int32_t> cell_of, order, cols, dbj, dbrev;
+    DevBuf<uint32_t> cell_start, cell_cursor, scratch, row_ptr, deg, up;
+    DevBuf<int> flags;
+    LG_CUDA(dx.reserve(n3));
+    LG_CUDA(duv.reserve(3 * (size_t)std::max<int64_t>(n_uv, 1)));
+    LG_CUDA(bbs.reserve(6 * 1024));
+    LG_CUDA(bbo.reserve(8));
+    LG_CUDA(flags.reserve(1));
+    LG_CUDA(cudaMemcpyAsync(dx.p, x, n3 * sizeof(double), cudaMemcpyHostToDevice, st));
+    if (n_uv) LG_CUDA(cudaMemcpyAsync(duv.p, uv, 3 * (size_t)n_uv * sizeof(double), cudaMemcpyHostToDevice, st));
+    LG_CUDA(cudaMemsetAsync(flags.p, 0, sizeof(int), st));
+    // candidate rows: every pair closer than a hair above 2 r + crit (the exact predicate is applied afterwards)
+    const double range = (2.0 * r_part + crit) * (1.0 + 1e-9);
+    launch_bbox(ni, dx.p, bbs.p, bbo.p, st);
+    double bb[6];
+    LG_CUDA(cudaMemcpyAsync(bb, bbo.p, sizeof(bb), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    NeighborGrid g{};
+    double cell = range * (1.0 + 1e-6);
+    for (;;) {
+        double total = 1.0;
+        for (int k = 0; k < 3; k++) {
+            const double ext = bb[3 + k] - bb[k];
+            if (!(ext >= 0.0) || !std::isfinite(ext)) return fail(LG_EINVAL, "non-finite particle positions");
+            const double d = std::floor(ext / cell) + 1.0;
+            g.dim[k] = d > 2.0e9 ? 2000000000 : (int)d;
+            total *= d;
+        }
+        if (total <= 16.0 * (double)n + 65536.0) break;
+        cell *= 1.26;
+    }
+    g.n_cells = (int64_t)g.dim[0] * g.dim[1] * g.dim[2];
+    g.cell = cell;
+    for (int k = 0; k < 3; k++) g.lo[k] = bb[k];
+    const size_t nc1 = (size_t)g.n_cells + 1;
+    LG_CUDA(cell_of.reserve((size_t)n));
+    LG_CUDA(order.reserve((size_t)n));
+    LG_CUDA(cell_start.reserve(nc1));
+    LG_CUDA(cell_cursor.reserve(nc1));
+    LG_CUDA(scratch.reserve(scan_scratch_elems(std::max(nc1, (size_t)n + 1))));
+    LG_CUDA(row_ptr.reserve((size_t)n + 1));
+    LG_CUDA(deg.reserve((size_t)n + 1));
+    LG_CUDA(up.reserve((size_t)n + 1));
+    LG_CUDA(cudaMemsetAsync(cell_start.p, 0, nc1 * sizeof(uint32_t), st));
+    LG_CUDA(cudaMemsetAsync(cell_cursor.p, 0, nc1 * sizeof(uint32_t), st));
+    launch_cell_count(ni, dx.p, g, cell_of.p, cell_start.p, st);
+    launch_exclusive_scan_u32(cell_start.p, nc1, scratch.p, st);
+    launch_cell_fill(ni, cell_of.p, cell_start.p, cell_cursor.p, order.p, st);
+    launch_row_count(ni, dx.p, g, cell_start.p, order.p, range, row_ptr.p, nullptr, st);
+    LG_CUDA(cudaMemsetAsync(row_ptr.p + n, 0, sizeof(uint32_t), st));
+    launch_exclusive_scan_u32(row_ptr.p, (size_t)n + 1, scratch.p, st);
+    uint32_t n_cand = 0;
+    LG_CUDA(cudaMemcpyAsync(&n_cand, row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    LG_CUDA(cols.reserve((size_t)n_cand + 16));
+    launch_row_fill(ni, dx.p, g, cell_start.p, order.p, range, row_ptr.p, cols.p, nullptr, st);
+    // bonds per particle, lexicographic ranks
+    launch_bond_count(ni, dx.p, row_ptr.p, cols.p, r_part, crit, deg.p, up.p, st);
+    LG_CUDA(cudaMemsetAsync(deg.p + n, 0, sizeof(uint32_t), st));
+    LG_CUDA(cudaMemsetAsync(up.p + n, 0, sizeof(uint32_t), st));
+    launch_exclusive_scan_u32(deg.p, (size_t)n + 1, scratch.p, st);
+    launch_exclusive_scan_u32(up.p, (size_t)n + 1, scratch.p, st);
+    uint32_t totals[2] = {0, 0};
+    LG_CUDA(cudaMemcpyAsync(&totals[0], deg.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaMemcpyAsync(&totals[1], up.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaStreamSynchronize(st));
+    const size_t nb = totals[0];
+    if ((int64_t)totals[1] > n_uv) return fail(LG_EINVAL, "fewer unit vectors than bonds (" + std::to_string(totals[1]) + " bonds)");
+    LG_CUDA(dbj.reserve(nb + 16));
+    LG_CUDA(dbrev.reserve(nb + 16));
+    LG_CUDA(dconn.reserve(nb * 15 + 16));
+    LG_CUDA(dlen.reserve(nb * 5 + 16));
+    launch_bond_fill(ni, dx.p, row_ptr.p, cols.p, r_part, crit, deg.p, up.p, duv.p, n_uv, dbj.p, dbrev.p, dconn.p, dlen.p, flags.p, st);
+    LG_CUDA(cudaGetLastError());
+    int h_flags = 0;
+    std::vector<uint32_t> bptr((size_t)n + 1);
+    std::vector<int32_t> bj(nb);
+    std::vector<double> conn(nb * 15), len(nb * 5);
+    LG_CUDA(cudaMemcpyAsync(&h_flags, flags.p, sizeof(int), cudaMemcpyDeviceToHost, st));
+    LG_CUDA(cudaMemcpyAsync(bptr.data(), deg.p, ((size_t)n + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    if (nb) {
+        LG_CUDA(cudaMemcpyAsync(bj.data(), dbj.p, nb * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaMemcpyAsync(conn.data(), dconn.p, nb * 15 * sizeof(double), cudaMemcpyDeviceToHost, st));
+        LG_CUDA(cudaMemcpyAsync(len.data(), dlen.p, nb * 5 * sizeof(double), cudaMemcpyDeviceToHost, st));
+    }
+    LG_CUDA(cudaStreamSynchronize(st));
+    if (h_flags & 2) {  // a collinear draw: only the sequential scan knows how the reference's generator moves on
+        struct Seq { const double* uv; int64_t n, k; bool short_; } seq{uv, n_uv, 0, false};
+        auto draw = [](void* user, double o[3]) {
+            Seq* q = static_cast<Seq*>(user);
+            if (q->k >= q->n) { q->short_ = true; o[0] = 1.0; o[1] = o[2] = 0.0; return; }
+            for (int c = 0; c < 3; c++) o[c] = q->uv[3 * q->k + c];
+            q->k++;
+        };
+        LG_TRY(lg_bond_table_create(n, x, r_part, crit, draw, &seq, out));
+        if (seq.short_) {
+            lg_bond_table_destroy(*out);
+            *out = nullptr;
+            return fail(LG_EINVAL, "fewer unit vectors than draws (a collinear vector was drawn again)");
+        }
+        return LG_OK;
+    }
+    std::unique_ptr<lg_bond_table> t(new (std::nothrow) lg_bond_table());
+    if (!t) return fail(LG_ENOMEM, "host allocation failed");
+    t->n = n;
+    t->bonds = (int64_t)totals[1];
+    t->recs.resize(nb);
+    for (int64_t i = 0; i < n; i++)
+        for (uint32_t b = bptr[(size_t)i]; b < bptr[(size_t)i + 1]; b++) {
+            HostBond& r = t->recs[b];
+            r.i = i;
+            r.j = bj[b];
+            std::memcpy(r.conn, &conn[(size_t)b * 15], sizeof(r.conn));
+            std::memcpy(r.len, &len[(size_t)b * 5], sizeof(r.len));
+        }
     *out = t.release();
     return LG_OK;
 }

@@ -118,52 +118,61 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const
     const int n_tiles = (A.n + RT2 - 1) / RT2;
     const bool have_bonds = kSinter && A.bptr != nullptr;
 
-    // pair / bond-record ranges and bridge work count of tile t: five independent loads (requested a tile ahead, consumed when
-    // its copies are issued).  Executed by every lane of warp 0 (same addresses: one transaction each).
+    // pair / bond-record ranges of tile t: four independent loads (requested a tile ahead, consumed when its copies are issued)
     auto load_desc = [&](int t, uint32_t d[5]) {
         const int i0 = t * RT2, nr = min(RT2, A.n - i0);
         d[0] = A.row_ptr[i0];
         d[1] = A.row_ptr[i0 + nr];
         d[2] = have_bonds ? A.bptr[i0] : 0u;
         d[3] = have_bonds ? A.bptr[i0 + nr] : 0u;
-        d[4] = have_bonds ? A.bwork_cnt[t] : 0u;
+        d[4] = have_bonds ? A.bwork_cnt[t] : 0u;  // with the others: no dependent load when the copies are issued
     };
-    // Bulk copies of every contiguous range tile t reads, completion counted on sm.full.  Called by all 32 lanes of warp 0:
-    // lane k issues the k-th copy, lane 0 posts the one arrival with the total byte count (the phase cannot complete before
-    // that arrival, so the copies may be issued ahead of it).
-    auto issue_loads = [&](int tile, const uint32_t d[5], int lane) {
+    // bulk copies of every contiguous range tile t reads, completion counted on sm.full (one thread)
+    auto issue_loads = [&](int tile, const uint32_t d[5]) {
         Stage2& S = sm.st;
         const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
         const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
+        const double* gx = A.x + 3 * (size_t)xlo;
+        const double* gv = A.v + 3 * (size_t)i0;
+        const double* gw = A.w + 3 * (size_t)i0;
+        const double* gth = A.th + 3 * (size_t)i0;
+        const uint32_t* grow = A.row_ptr + i0;
+        const uint32_t* gbond = have_bonds ? A.bptr + i0 : nullptr;
         const uint32_t nb3 = 24u * (uint32_t)nrows, nbp = 4u * (uint32_t)(nrows + 1), nbx = 24u * (uint32_t)xcnt;
         const uint32_t np0 = min(d[1] - d[0], (uint32_t)RPC2);
         const uint32_t nbr = (d[3] - d[2] <= (uint32_t)RBC2) ? d[3] - d[2] : 0u;
-        void* dst = nullptr;
-        const void* src = nullptr;
-        uint32_t bytes = 0u;
-        switch (lane) {
-            case 0: dst = S.wx; src = A.x + 3 * (size_t)xlo; bytes = nbx; break;
-            case 1: dst = S.wv; src = A.v + 3 * (size_t)i0; bytes = nb3; break;
-            case 2: dst = S.ww; src = A.w + 3 * (size_t)i0; bytes = nb3; break;
-            case 3: if (MODE == MODE_FUSED) { dst = S.wth; src = A.th + 3 * (size_t)i0; bytes = nb3; } break;
-            case 4: dst = S.wrow; src = A.row_ptr + i0; bytes = nbp; break;
-            case 5: if (have_bonds) { dst = S.wbond; src = A.bptr + i0; bytes = nbp; } break;
-            case 6: dst = S.wcols; src = A.cols + d[0]; bytes = 4u * np0; break;
-            case 7: if (kContact) { dst = S.wtag; src = A.tag + d[0]; bytes = np0; } break;
-            case 8: dst = S.wconn; src = A.bconn + 15 * (size_t)d[2]; bytes = 120u * nbr; break;
-            case 9: dst = S.wlen; src = A.blen + 5 * (size_t)d[2]; bytes = 40u * nbr; break;
-            case 10: dst = S.wbj; src = A.bj + d[2]; bytes = 4u * nbr; break;
-            case 11: dst = S.wrev; src = A.brev + d[2]; bytes = 4u * nbr; break;
-            case 12: dst = S.wwork; src = A.bwork + d[2]; bytes = 2u * nbr; break;
-            default: break;
+        const int32_t* gcols = A.cols + d[0];
+        const uint8_t* gtag = A.tag + d[0];
+        const double* gconn = A.bconn + 15 * (size_t)d[2];
+        const double* glen = A.blen + 5 * (size_t)d[2];
+        const int32_t* gbj = A.bj + d[2];
+        const int32_t* grev = A.brev + d[2];
+        const uint16_t* gwork = A.bwork + d[2];
+        uint32_t total = window_bytes(gx, nbx) + window_bytes(gv, nb3) + window_bytes(gw, nb3) + window_bytes(grow, nbp) +
+                         window_bytes(gcols, 4u * np0);
+        if constexpr (MODE == MODE_FUSED) total += window_bytes(gth, nb3);
+        if (have_bonds) total += window_bytes(gbond, nbp);
+        if constexpr (kContact) total += window_bytes(gtag, np0);
+        if (nbr)
+            total += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(gbj, 4u * nbr) +
+                     window_bytes(grev, 4u * nbr) + window_bytes(gwork, 2u * nbr);
+        sm.nwork = nbr ? d[4] : 0u;  // published to the other threads by the barrier's release / acquire
+        mbar_expect_tx(&sm.full, total);
+        if (nbr) {
+            bulk_load(S.wconn, gconn, 120u * nbr, &sm.full);
+            bulk_load(S.wlen, glen, 40u * nbr, &sm.full);
+            bulk_load(S.wbj, gbj, 4u * nbr, &sm.full);
+            bulk_load(S.wrev, grev, 4u * nbr, &sm.full);
+            bulk_load(S.wwork, gwork, 2u * nbr, &sm.full);
         }
-        const uint32_t mine = bytes ? window_bytes(src, bytes) : 0u;
-        const uint32_t total = __reduce_add_sync(0xffffffffu, mine);
-        if (lane == 0) {
-            sm.nwork = nbr ? d[4] : 0u;  // published to the other threads by the barrier's release / acquire
-            mbar_expect_tx(&sm.full, total);
-        }
-        if (mine) bulk_load(dst, src, bytes, &sm.full);
+        bulk_load(S.wx, gx, nbx, &sm.full);
+        bulk_load(S.wv, gv, nb3, &sm.full);
+        bulk_load(S.ww, gw, nb3, &sm.full);
+        if constexpr (MODE == MODE_FUSED) bulk_load(S.wth, gth, nb3, &sm.full);
+        bulk_load(S.wrow, grow, nbp, &sm.full);
+        if (have_bonds) bulk_load(S.wbond, gbond, nbp, &sm.full);
+        bulk_load(S.wcols, gcols, 4u * np0, &sm.full);
+        if constexpr (kContact) bulk_load(S.wtag, gtag, np0, &sm.full);
     };
     // the big ranges of tile t pulled into L2 (no shared memory needed): by the time the stage is free its copies are L2 hits
     auto prefetch_tile = [&](int t, const uint32_t d[5]) {
@@ -179,19 +188,17 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const
         }
     };
 
-    uint32_t dn[5] = {0u, 0u, 0u, 0u, 0u};  // warp 0: ranges of the NEXT tile of this CTA
+    uint32_t dn[5] = {0u, 0u, 0u, 0u, 0u};  // thread 0: ranges of the NEXT tile of this CTA
     if (tid == 0) {
         mbar_init(&sm.full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    __syncthreads();
-    if (tid < 32) {
         uint32_t d0[5];
         load_desc(blockIdx.x, d0);
-        issue_loads(blockIdx.x, d0, tid);
+        issue_loads(blockIdx.x, d0);
         if ((int)(blockIdx.x + gridDim.x) < n_tiles) load_desc(blockIdx.x + gridDim.x, dn);
     }
+    __syncthreads();
 
     const int r = tid / LPP, lp = tid % LPP;  // particle of the tile and lane within it (pass 2)
     int k = 0;
@@ -409,29 +416,28 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // this thread's shared-memory writes -> async proxy
         compute_barrier();
-        if (tid < 32) {  // warp 0: one bulk store per lane, then the next tile's copies, one per lane
+        if (tid == 0) {
             const uint32_t nb3 = 24u * (uint32_t)nrows;
             const size_t g0 = 3 * (size_t)i0;
             if constexpr (MODE == MODE_FORCE) {
-                if (tid == 0) bulk_store(A.a + g0, sv, nb3);
-                if (tid == 1) bulk_store(A.al + g0, sw, nb3);
+                bulk_store(A.a + g0, sv, nb3);
+                bulk_store(A.al + g0, sw, nb3);
             } else {
-                if (tid == 0) bulk_store(A.x_next + g0, sx, nb3);
-                if (tid == 1) bulk_store(A.v_next + g0, sv, nb3);
-                if (tid == 2) bulk_store(A.w_next + g0, sw, nb3);
-                if (tid == 3) bulk_store(A.th + g0, sth, nb3);
-                if (tid == 4 && kSinter && bonds_staged) bulk_store(A.bconn_next + 15 * (size_t)b0, sconn, 120u * nbond);
+                bulk_store(A.x_next + g0, sx, nb3);
+                bulk_store(A.v_next + g0, sv, nb3);
+                bulk_store(A.w_next + g0, sw, nb3);
+                bulk_store(A.th + g0, sth, nb3);
+                if (kSinter && bonds_staged) bulk_store(A.bconn_next + 15 * (size_t)b0, sconn, 120u * nbond);
             }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // this lane's stores have read the stage
-            __syncwarp();  // ... and so have the other lanes': the stage may be overwritten
+            asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the stage may be overwritten
             if (nxt < n_tiles) {
-                issue_loads(nxt, dn, tid);
+                issue_loads(nxt, dn);
                 if (nxt + (int)gridDim.x < n_tiles) load_desc(nxt + gridDim.x, dn);
             }
         }
     }
-    if (tid < 32) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
 }
 
 template <int MASK, int MODE, bool FACETS, int RT2, int LPP>

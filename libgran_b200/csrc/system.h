@@ -142,6 +142,12 @@ void launch_bbox(int n, const double* x, double* d_scratch, double* d_out, cudaS
 size_t scan_scratch_elems(size_t n);
 void launch_exclusive_scan_u32(uint32_t* data, size_t n, uint32_t* scratch, cudaStream_t st);
 
+// device-side bond detection (kernels_bonds.cu)
+void launch_bond_count(int n, const double* x, const uint32_t* row_ptr, const int32_t* cols, double r, double crit, uint32_t* deg,
+                       uint32_t* up, cudaStream_t st);
+void launch_bond_fill(int n, const double* x, const uint32_t* row_ptr, const int32_t* cols, double r, double crit, const uint32_t* bptr,
+                      const uint32_t* upoff, const double* uv, int64_t n_uv, int32_t* bj, int32_t* brev, double* bconn, double* blen,
+                      int* flags, cudaStream_t st);
 // spatial renumbering (kernels_neighbor.cu)
 size_t morton_cells();
 void launch_morton_order(int n, const double* x, const double lo[3], double cell, uint32_t* key, uint32_t* count, uint32_t* cursor,

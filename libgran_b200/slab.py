@@ -441,7 +441,10 @@ class SlabSystem:
             if cfg.model_mask & MODEL_SINTER:
                 if unit_vectors is None:
                     raise ValueError("the sinter model needs unit_vectors")
-                bonds = _sys.host_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors)
+                if callable(unit_vectors):  # a generator callback can only be consumed by the sequential host scan
+                    bonds = _sys.host_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors)
+                else:  # device-side bond detection on this rank's GPU (kernels_bonds.cu); same table bit for bit
+                    bonds = _sys.device_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors, device=self.device)
         torch.cuda.set_device(self.device)
         t0 = block_tables(self.rank, self.world, x0, v0, theta0, omega0, self.S, *bonds, device=self.device)
         self._install(t0)

@@ -34,7 +34,7 @@ ABI_SYMBOLS = (
     "lg_gen_fractal_aggregate", "lg_gen_random_packing",
     # SURVEY.md section 8f variants
     "lg_set_hamaker_variant", "lg_set_integrator", "lg_set_fixed_particle", "lg_set_central_attraction",
-    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder", "lg_set_autotune", "lg_get_rows_shape",
+    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder", "lg_set_autotune", "lg_get_rows_shape", "lg_bond_table_create_device",
     "lg_dumper_create", "lg_dump_particles", "lg_dump_necks", "lg_dump_spring_connectors", "lg_dump_particles_csv",
     "lg_dumper_wait", "lg_dumper_destroy", "lg_write_particles", "lg_write_necks", "lg_write_spring_connectors",
     # slab decomposition support
@@ -137,6 +137,7 @@ def load_library(path: Optional[str] = None):
     lib.lg_get_alt_bond.argtypes = [vp, C.c_int64, C.c_int64, C.POINTER(C.c_int), dp]
     lib.lg_set_reorder.argtypes = [vp, C.c_int]
     lib.lg_set_autotune.argtypes = [vp, C.c_int]
+    lib.lg_bond_table_create_device.argtypes = [C.c_int64, vp, C.c_double, C.c_double, C.c_int64, vp, C.c_int, C.POINTER(vp)]
     lib.lg_get_rows_shape.argtypes = [vp, C.POINTER(C.c_int)]
     lib.lg_dumper_create.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     for name in ("lg_dump_particles", "lg_dump_necks", "lg_dump_spring_connectors"):
@@ -523,6 +524,35 @@ def from_config(cfg, x0, v0, theta0, omega0, unit_vectors=None, device: int = -1
     if cfg.model_mask & MODEL_FACET:
         sysm.add_facet(cfg.facet_vertices, cfg.facet_v, cfg.surf_contact, (cfg.surf_A, cfg.surf_h0))
     return sysm
+
+
+def _table_records(lib, tbl):
+    nb = C.c_int64(0)
+    lib.lg_bond_table_count(tbl, C.byref(nb))
+    m = 2 * nb.value
+    ij = np.zeros((m, 2), dtype=np.int64)
+    conn = np.zeros((m, 15), dtype=np.float64)
+    ln = np.zeros((m, 5), dtype=np.float64)
+    if m:
+        lib.lg_bond_table_records(tbl, ij.ctypes.data, conn.ctypes.data, ln.ctypes.data)
+    return ij, conn, ln
+
+
+def device_bond_table(x, r_part: float, critical_separation: float, unit_vectors, device: int = -1):
+    """The table of host_bond_table built on the GPU (lg_bond_table_create_device): cell-list candidates, bond k in
+    lexicographic pair order takes unit_vectors[k].  Same records bit for bit."""
+    lib = load_library()
+    x = _c3(x)
+    uv = _c3(unit_vectors)
+    tbl = C.c_void_p()
+    rc = lib.lg_bond_table_create_device(len(x), x.ctypes.data, float(r_part), float(critical_separation), len(uv), uv.ctypes.data,
+                                         int(device), C.byref(tbl))
+    if rc != LG_OK:
+        raise LgError(rc, lib.lg_last_error().decode(errors="replace"))
+    try:
+        return _table_records(lib, tbl)
+    finally:
+        lib.lg_bond_table_destroy(tbl)
 
 
 def host_bond_table(x, r_part: float, critical_separation: float, unit_vectors):

@@ -8,7 +8,7 @@ mkdir -p ../variants
 while [ $# -ge 2 ]; do
   name=$1; flags=$2; shift 2
   d=build/var_$name; mkdir -p $d
-  for f in api kernels_force kernels_force_tiled kernels_rows kernels_integrate kernels_neighbor kernels_halo generators; do
+  for f in api kernels_force kernels_force_tiled kernels_rows kernels_integrate kernels_neighbor kernels_halo kernels_bonds generators; do
     if [ $f = kernels_force_tiled ] || [ $f = kernels_rows ] || [ ! -f build/$f.o ]; then
       /usr/local/cuda/bin/nvcc -gencode arch=compute_100a,code=sm_100a -ccbin /usr/bin/g++ -std=c++17 -O3 -lineinfo --fmad=false \
         -Xcompiler -fPIC,-ffp-contract=off -Xptxas -v $flags -c $f.cu -o $d/$f.o 2> $d/$f.ptxas.log &

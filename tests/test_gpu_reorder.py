@@ -97,3 +97,49 @@ def test_reorder_guards(lib):
     r = from_config(scn.cfg, *scn.state, device=0, reorder=True)
     with pytest.raises(LgError):
         r.device_ptr("x")
+
+
+# ---- device-side bond detection (lg_bond_table_create_device) -----------------------------------------------------------
+BOND_CASES = [
+    ("aggregate 150", lambda: S.aggregate()),
+    ("multi aggregate 40", lambda: S.multi_aggregate_collision(40)),
+    ("fractal 20000", lambda: S.fractal_aggregate(20000, models=S.MODEL_SINTER | S.MODEL_HAMAKER)),
+    ("stress block", lambda: S.stress_block(14, 14, 10, models=S.MODEL_SINTER | S.MODEL_HAMAKER)),
+]
+
+
+@pytest.mark.parametrize("name,make", BOND_CASES, ids=[c[0] for c in BOND_CASES])
+def test_device_bond_table_equals_host_scan(lib, oracle, name, make):
+    """Same bond set, same connectors and rest lengths, bit for bit: the device scan hands unit vector k to the k-th bond in
+    lexicographic (i < j) order, exactly as the reference's constructor consumes its generator."""
+    from libgran_b200 import system as sysm
+
+    scn = make()
+    cfg = scn.cfg
+    uv = unit_vectors_for(cfg, oracle, count=4 * cfg.n + 64)
+    h_ij, h_conn, h_len = sysm.host_bond_table(scn.x0, cfg.r_part, cfg.critical_separation, uv)
+    d_ij, d_conn, d_len = sysm.device_bond_table(scn.x0, cfg.r_part, cfg.critical_separation, uv, device=0)
+    assert len(h_ij) > 0
+    ho = np.lexsort((h_ij[:, 1], h_ij[:, 0]))  # the host table lists (i, j), (j, i) per bond; the device one is in CSR order
+    do = np.lexsort((d_ij[:, 1], d_ij[:, 0]))
+    assert np.array_equal(h_ij[ho], d_ij[do]), f"{name}: bond set"
+    assert np.array_equal(h_conn[ho], d_conn[do]), f"{name}: connectors"
+    assert np.array_equal(h_len[ho], d_len[do]), f"{name}: rest lengths"
+
+
+def test_device_bond_table_collinear_draw_falls_back(lib, oracle):
+    """A unit vector collinear with its bond axis is drawn again by the reference (sinter_bridge.h:171-175), which shifts every
+    later draw: the device scan detects it and hands over to the sequential scan."""
+    from libgran_b200 import system as sysm
+
+    scn = S.sintered_lattice()
+    cfg = scn.cfg
+    uv = unit_vectors_for(cfg, oracle, count=4096).copy()
+    h_ij, _, _ = sysm.host_bond_table(scn.x0, cfg.r_part, cfg.critical_separation, uv)
+    i, j = h_ij[4]  # third bond: make its vector the bond axis itself
+    axis = scn.x0[j] - scn.x0[i]
+    uv[2] = axis / np.linalg.norm(axis)
+    h = sysm.host_bond_table(scn.x0, cfg.r_part, cfg.critical_separation, uv)
+    d = sysm.device_bond_table(scn.x0, cfg.r_part, cfg.critical_separation, uv, device=0)
+    for a, b in zip(h, d):
+        assert np.array_equal(a, b)
