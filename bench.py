@@ -437,7 +437,7 @@ def run_slab(args, scn, desc, moves, world, rank, local_rank):
     nloc = torch.tensor([sysm.n_local, own], dtype=torch.int64, device=dev)
     dist.all_reduce(nloc)
     e2e = {"value": round(n * e2e_steps / float(tt), 1), "unit": METRIC,
-           "h2d_bytes_per_step": round(4 * 24 * n * world / e2e_steps, 1),
+           "h2d_bytes_per_step": round(4 * 24 * int(nloc[0]) / e2e_steps, 1),  # every rank uploads the rows it holds (owned + ghosts)
            "d2h_bytes_per_step": round((4 * 24 * int(nloc[1]) + (e2e_steps // 10) * 12 * 8 * world) / e2e_steps, 1),
            "steps": e2e_steps, "final_ke": ke,
            "what": "per rank: set_state_host (H2D, pinned) + K/10 x [run(10 steps: step + halo exchange, rebuild/20) + KE "

@@ -322,6 +322,15 @@ int lg_set_owned_device(lg_system* s, const uint8_t* d_owned);
 /* The sparse contact-spring table: S slots per particle; sgid[i*S+k] = partner index or -1, spr[(i*S+k)*9..]. */
 int lg_export_slots(lg_system* s, int* S, int32_t** d_sgid, double** d_spr);
 int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_spr);
+/* Wall history of facet `facet_id` (surface_contact_force.h:53): springs [n][9] and active flags [n], device views /
+ * device-to-device import -- wall springs migrate with their particle at a repartition like contact slots do. */
+int lg_export_wall(lg_system* s, int facet_id, double** d_wspr, uint8_t** d_wact);
+int lg_import_wall_device(lg_system* s, int facet_id, const double* d_wspr, const uint8_t* d_wact);
+/* The sums of lg_diagnostics over the particles this system OWNS (ghosts excluded), left on the device for a caller that
+ * reduces them across ranks (queued on the system's stream, no synchronisation).  *d_out = 12 doubles:
+ * pass 0 fills [0..10] = {translational KE, rotational KE, sum v (3), sum (I omega + x cross m v) (3), sum x (3)};
+ * pass 1 (d_com = device pointer to the global centre of mass) fills [11] = sum |x - com|^2. */
+int lg_diagnostics_partial(lg_system* s, int pass, const double* d_com, double** d_out);
 /* The bond CSR (rows ascending in partner index): bptr[n+1], bj[nb], connectors[nb][15], rest lengths[nb][5];
  * brev[b] = record index of the mirror (j, i), or b itself when the mirror is not held locally. */
 int lg_export_bonds(lg_system* s, int64_t* n_ordered, uint32_t** d_bptr, int32_t** d_bj, double** d_bconn,
@@ -352,8 +361,10 @@ int lg_halo_set_lists(lg_halo* h, int peer, int n_send_part, const int32_t* d_se
 int lg_halo_export(lg_halo* h, int peer, unsigned char handle[64], int64_t offs[4]);
 int lg_halo_connect(lg_halo* h, int peer, const unsigned char handle[64], const int64_t offs[4]);
 int lg_halo_exchange(lg_system* s, lg_halo* h);
-/* n_steps x (lg_do_step, lg_halo_exchange) without returning to the caller (no neighbor rebuild inside). */
-int lg_run_slab(lg_system* s, lg_halo* h, double dt, int64_t n_steps);
+/* n_steps x (lg_do_step, [every facet.update_positions(dt)], lg_halo_exchange) without returning to the caller (no neighbor
+ * rebuild inside).  Fused launches of step_rows2_kernel store the halo themselves (the CTA that finishes a tile writes its
+ * halo items into the neighbours' buffers, the last CTA publishes the sequence number): no separate push kernel. */
+int lg_run_slab(lg_system* s, lg_halo* h, double dt, int64_t n_steps, int move_facets);
 int lg_halo_disconnect(lg_halo* h);
 int lg_halo_destroy(lg_halo* h);
 

@@ -172,6 +172,9 @@ struct lg_system {
     DevBuf<uint16_t> bwork;
     DevBuf<uint32_t> bwork_cnt;
     int bwork_shape = -1;            // tile shape the lists were built for (-1: none)
+    // slab runs (lg_run_slab): the halo whose stores the fused step kernel performs itself (kernels_rows.cu, HaloFusedArgs)
+    struct lg_halo* active_halo = nullptr;
+    bool halo_stored_by_step = false;  // the last step launch has stored and published the halo: no push kernel
     // tile shape of step_rows2_kernel: heuristic (deterministic) or, after lg_set_autotune(1), measured on the first fused launches
     int autotune = 0;
     int tuned_shape = -1;
@@ -315,6 +318,7 @@ int build_allpairs(lg_system* s) {
 }
 
 int build_bridge_work(lg_system* s, int shape);  // below: work lists of step_rows2_kernel's bridge pass
+int fill_halo_fused(lg_system* s, ForceArgs& A);  // below: halo stores fused into step_rows2_kernel
 
 int drain_profile(lg_system* s) {
     LG_CUDA(cudaStreamSynchronize(s->stream));
@@ -395,6 +399,8 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia, s->mp.hamaker_kind, s->mp.hamaker_cutoff);
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;
+    s->halo_stored_by_step = false;
+    if (fused && A.fast && A.use_rows == 2 && s->active_halo != nullptr) LG_TRY(fill_halo_fused(s, A));
     if (tuning) {
         if (!s->tune_ev[0]) {
             LG_CUDA(cudaEventCreate(&s->tune_ev[0]));
@@ -1765,7 +1771,7 @@ int lg_diagnostics(lg_system* s, double out[9]) {
     const int n = (int)s->n;
     double* h = s->h_pinned;
     launch_diag_sums(n, s->x.p, s->v.p, s->w.p, s->mp.mass, s->mp.inertia, nullptr, s->diag_partials.p, s->diag_out.p, 0,
-                     s->stream);
+                     nullptr, s->stream);
     LG_CUDA(cudaMemcpyAsync(h, s->diag_out.p, 11 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
     double com[3] = {h[8] / (double)n, h[9] / (double)n, h[10] / (double)n};
@@ -1773,7 +1779,7 @@ int lg_diagnostics(lg_system* s, double out[9]) {
     std::memcpy(sums, h, sizeof(sums));
     LG_CUDA(cudaMemcpyAsync(s->diag_out.p + 12, com, 3 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
     launch_diag_sums(n, s->x.p, s->v.p, s->w.p, s->mp.mass, s->mp.inertia, s->diag_out.p + 12, s->diag_partials.p,
-                     s->diag_out.p, 1, s->stream);
+                     s->diag_out.p, 1, nullptr, s->stream);
     LG_CUDA(cudaMemcpyAsync(h, s->diag_out.p + 11, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     LG_CUDA(cudaStreamSynchronize(s->stream));
     out[0] = sums[0] + sums[1];
@@ -1871,6 +1877,40 @@ int lg_import_slots_device(lg_system* s, const int32_t* d_sgid, const double* d_
     return LG_OK;
 }
 
+int lg_diagnostics_partial(lg_system* s, int pass, const double* d_com, double** d_out) {
+    LG_ENTER(s);
+    if (!d_out || (pass != 0 && pass != 1) || (pass == 1 && !d_com)) return fail(LG_EINVAL, "bad arguments to lg_diagnostics_partial");
+    if (!s->state_set) return fail(LG_EINVAL, "lg_set_state has not been called");
+    const uint8_t* owned = s->has_owned ? s->owned.p : nullptr;
+    if (pass == 1) LG_CUDA(cudaMemcpyAsync(s->diag_out.p + 12, d_com, 3 * sizeof(double), cudaMemcpyDeviceToDevice, s->stream));
+    launch_diag_sums((int)s->n, s->x.p, s->v.p, s->w.p, s->mp.mass, s->mp.inertia, pass == 1 ? s->diag_out.p + 12 : nullptr,
+                     s->diag_partials.p, s->diag_out.p, pass, owned, s->stream);
+    LG_CUDA(cudaGetLastError());
+    *d_out = s->diag_out.p;
+    return LG_OK;
+}
+
+int lg_export_wall(lg_system* s, int facet_id, double** d_wspr, uint8_t** d_wact) {
+    LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_export_wall: not available after lg_set_reorder");
+    if (facet_id < 0 || facet_id >= (int)s->facets.size() || !d_wspr || !d_wact) return fail(LG_EINVAL, "bad facet id or null output");
+    LG_TRY(flush(s));
+    *d_wspr = s->wspr[(size_t)facet_id]->p;
+    *d_wact = s->wact[(size_t)facet_id]->p;
+    return LG_OK;
+}
+
+int lg_import_wall_device(lg_system* s, int facet_id, const double* d_wspr, const uint8_t* d_wact) {
+    LG_ENTER(s);
+    if (s->reorder_mode) return fail(LG_EINVAL, "lg_import_wall_device: not available after lg_set_reorder");
+    if (facet_id < 0 || facet_id >= (int)s->facets.size() || !d_wspr || !d_wact) return fail(LG_EINVAL, "bad facet id or null input");
+    LG_TRY(flush(s));
+    LG_CUDA(cudaMemcpyAsync(s->wspr[(size_t)facet_id]->p, d_wspr, (size_t)s->n * 9 * sizeof(double), cudaMemcpyDeviceToDevice, s->stream));
+    LG_CUDA(cudaMemcpyAsync(s->wact[(size_t)facet_id]->p, d_wact, (size_t)s->n, cudaMemcpyDeviceToDevice, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    return LG_OK;
+}
+
 int lg_export_bonds(lg_system* s, int64_t* n_ordered, uint32_t** d_bptr, int32_t** d_bj, double** d_bconn, double** d_blen) {
     LG_ENTER(s);
     if (s->reorder_mode) return fail(LG_EINVAL, "lg_export_bonds: the slab-decomposition entry points address particles by internal index and are not available after lg_set_reorder");
@@ -1965,9 +2005,83 @@ struct lg_halo {
     double* remote_data[kMaxHaloPeers][2] = {};
     unsigned long long* remote_flag[kMaxHaloPeers][2] = {};
     unsigned long long seq = 0;
+    // halo stores fused into step_rows2_kernel: host mirrors of the send lists, items per tile for one tile shape
+    std::vector<int32_t> h_send_idx[kMaxHaloPeers], h_send_rec[kMaxHaloPeers];
+    int items_shape = -1;
+    DevBuf<uint32_t> d_tile_ptr;
+    DevBuf<uint2> d_items;
+    DevBuf<unsigned int> d_done;
 };
 
 namespace {
+extern "C++" {
+// Items of the fused halo store for tile shape `shape`: every particle / bond record of the send lists, keyed by the tile
+// that computes it (tile of its particle), with its slot in the peer's message (position in the send list).
+int build_halo_items(lg_system* s, lg_halo* hl, int shape) {
+    const int T = rows2_tile_particles(shape);
+    const size_t n = (size_t)s->n, n_tiles = (n + (size_t)T - 1) / (size_t)T;
+    std::vector<std::vector<uint2>> per_tile(n_tiles);
+    for (int k = 0; k < hl->n_peers; k++) {
+        for (size_t q = 0; q < hl->h_send_idx[k].size(); q++) {
+            const uint32_t i = (uint32_t)hl->h_send_idx[k][q];
+            if (i >= n) return fail(LG_EINVAL, "halo send index out of range");
+            per_tile[i / (uint32_t)T].push_back(make_uint2(((uint32_t)k << 24) | (i % (uint32_t)T), (uint32_t)q));
+        }
+        for (size_t q = 0; q < hl->h_send_rec[k].size(); q++) {
+            const uint32_t b = (uint32_t)hl->h_send_rec[k][q];
+            if (s->h_bptr.size() != n + 1 || b >= s->h_bptr[n]) return fail(LG_EINVAL, "halo send record out of range");
+            const size_t i = (size_t)(std::upper_bound(s->h_bptr.begin(), s->h_bptr.end(), b) - s->h_bptr.begin()) - 1;  // owner of record b
+            const size_t t = i / (size_t)T;
+            const uint32_t rel = b - s->h_bptr[t * (size_t)T];
+            if (rel >= 0x800000u) return fail(LG_ECAPACITY, "too many bond records in one tile");
+            per_tile[t].push_back(make_uint2(((uint32_t)k << 24) | 0x800000u | rel, (uint32_t)q));
+        }
+    }
+    std::vector<uint32_t> tp(n_tiles + 1, 0);
+    std::vector<uint2> items;
+    for (size_t t = 0; t < n_tiles; t++) {
+        tp[t] = (uint32_t)items.size();
+        items.insert(items.end(), per_tile[t].begin(), per_tile[t].end());
+    }
+    tp[n_tiles] = (uint32_t)items.size();
+    LG_CUDA(hl->d_tile_ptr.reserve(n_tiles + 1));
+    LG_CUDA(hl->d_items.reserve(items.size() + 1));
+    if (!hl->d_done.p) {
+        LG_CUDA(hl->d_done.reserve(1));
+        LG_CUDA(cudaMemsetAsync(hl->d_done.p, 0, sizeof(unsigned int), s->stream));
+    }
+    LG_CUDA(cudaMemcpyAsync(hl->d_tile_ptr.p, tp.data(), (n_tiles + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
+    if (!items.empty()) LG_CUDA(cudaMemcpyAsync(hl->d_items.p, items.data(), items.size() * sizeof(uint2), cudaMemcpyHostToDevice, s->stream));
+    LG_CUDA(cudaStreamSynchronize(s->stream));
+    hl->items_shape = shape;
+    return LG_OK;
+}
+
+int fill_halo_fused(lg_system* s, ForceArgs& A) {
+    static const int enabled = [] { const char* e = std::getenv("LGB200_HALO_FUSED"); return e ? std::atoi(e) : 1; }();
+    lg_halo* hl = s->active_halo;
+    if (!enabled || hl == nullptr || hl->n_peers == 0) return LG_OK;
+    if (hl->items_shape != A.rows_shape) LG_TRY(build_halo_items(s, hl, A.rows_shape));
+    const unsigned long long seq = hl->seq + 1;  // the exchange halo_exchange is about to run
+    const int par = (int)(seq & 1ull);
+    HaloFusedArgs& H = A.hf;
+    H.n_peers = hl->n_peers;
+    for (int k = 0; k < hl->n_peers; k++) {
+        const long ts = 9L * hl->send[k].n_part + 15L * hl->send[k].n_rec;
+        if (hl->remote_flag[k][par] == nullptr || (ts > 0 && hl->remote_data[k][par] == nullptr)) return fail(LG_EINVAL, "halo peer not connected");
+        H.remote[k] = hl->remote_data[k][par];
+        H.rec_off[k] = 9LL * hl->send[k].n_part;
+        H.remote_flag[k] = hl->remote_flag[k][par];
+    }
+    H.tile_ptr = hl->d_tile_ptr.p;
+    H.items = hl->d_items.p;
+    H.done = hl->d_done.p;
+    H.seq = seq;
+    s->halo_stored_by_step = true;
+    return LG_OK;
+}
+}  // extern "C++"
+
 int halo_exchange(lg_system* s, lg_halo* hl) {
     if (hl->n_peers == 0) return LG_OK;
     hl->seq++;
@@ -1999,7 +2113,8 @@ int halo_exchange(lg_system* s, lg_halo* hl) {
     P.seq = Q.seq = hl->seq;
     Q.timeout_ns = 20ull * 1000000000ull;
     Q.err = s->err.p;
-    launch_halo_push(P, s->stream);
+    if (!s->halo_stored_by_step) launch_halo_push(P, s->stream);  // else: the step kernel has stored and published this exchange
+    s->halo_stored_by_step = false;
     launch_halo_pull(Q, s->stream);
     LG_CUDA(cudaGetLastError());
     return LG_OK;
@@ -2037,6 +2152,14 @@ int lg_halo_set_lists(lg_halo* hl, int k, int n_send_part, const int32_t* d_send
     if (!hl || k < 0 || k >= hl->n_peers) return fail(LG_EINVAL, "bad halo peer");
     if (n_send_part < 0 || n_send_rec < 0 || n_recv_part < 0 || n_recv_rec < 0) return fail(LG_EINVAL, "negative halo list size");
     if (9LL * n_recv_part + 15LL * n_recv_rec > hl->recv_doubles[k]) return fail(LG_ESIZE, "halo receive list exceeds the buffer");
+    {   // host mirrors of the send lists: the fused halo store of step_rows2_kernel is organised by tile on the host
+        DeviceGuard guard_(hl->device);
+        hl->h_send_idx[k].resize((size_t)n_send_part);
+        hl->h_send_rec[k].resize((size_t)n_send_rec);
+        if (n_send_part) LG_CUDA(cudaMemcpy(hl->h_send_idx[k].data(), d_send_idx, (size_t)n_send_part * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        if (n_send_rec) LG_CUDA(cudaMemcpy(hl->h_send_rec[k].data(), d_send_rec, (size_t)n_send_rec * sizeof(int32_t), cudaMemcpyDeviceToHost));
+        hl->items_shape = -1;
+    }
     hl->send[k].n_part = n_send_part; hl->send[k].idx = d_send_idx;
     hl->send[k].n_rec = n_send_rec;   hl->send[k].rec = d_send_rec;
     hl->recv[k].n_part = n_recv_part; hl->recv[k].idx = d_recv_idx;
@@ -2102,15 +2225,22 @@ int lg_halo_exchange(lg_system* s, lg_halo* hl) {
     return halo_exchange(s, hl);
 }
 
-int lg_run_slab(lg_system* s, lg_halo* hl, double dt, int64_t n_steps) {
+int lg_run_slab(lg_system* s, lg_halo* hl, double dt, int64_t n_steps, int move_facets) {
     LG_ENTER(s);
     if (!hl) return fail(LG_EINVAL, "null halo");
     LG_TRY(prepare(s));
-    for (int64_t k = 0; k < n_steps; k++) {
-        LG_TRY(step(s, dt));
-        LG_TRY(halo_exchange(s, hl));
+    s->active_halo = hl;  // fused launches of step_rows2_kernel store the halo themselves
+    int rc = LG_OK;
+    for (int64_t k = 0; k < n_steps && rc == LG_OK; k++) {
+        rc = step(s, dt);
+        if (rc == LG_OK && move_facets)  // facet.update_positions(dt) after every step, as test/surface.cpp's loop does
+            for (auto& f : s->facets)
+                for (int q = 0; q < 3; q++) f.vtx[q] = f.vtx[q] + f.v * dt;
+        if (rc == LG_OK) rc = halo_exchange(s, hl);
     }
-    return LG_OK;
+    s->active_halo = nullptr;
+    s->halo_stored_by_step = false;
+    return rc;
 }
 
 int lg_get_stream(lg_system* s, void** stream) {

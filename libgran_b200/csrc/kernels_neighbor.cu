@@ -413,11 +413,12 @@ constexpr int kDiagSlots = 12;
 
 __global__ void __launch_bounds__(kDiagThreads)
     diag_partial_kernel(int n, const double* x, const double* v, const double* w, double mass, double inertia,
-                        const double* com, double* partial, int pass) {
+                        const double* com, double* partial, int pass, const uint8_t* owned) {
     double s[kDiagSlots];
 #pragma unroll
     for (int k = 0; k < kDiagSlots; k++) s[k] = 0.0;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        if (owned != nullptr && !owned[i]) continue;  // slab decomposition: ghosts belong to another rank's sums
         const d3 xi = load3(x + 3 * (size_t)i);
         if (pass == 0) {
             const d3 vi = load3(v + 3 * (size_t)i), wi = load3(w + 3 * (size_t)i);
@@ -459,11 +460,11 @@ __global__ void diag_final_kernel(int n_partial, const double* partial, double* 
 
 // d_partials: kDiagSlots * kDiagMaxBlocks doubles; d_out: 16 doubles
 void launch_diag_sums(int n, const double* x, const double* v, const double* w, double mass, double inertia,
-                      const double* com, double* d_partials, double* d_out, int pass, cudaStream_t st) {
+                      const double* com, double* d_partials, double* d_out, int pass, const uint8_t* owned, cudaStream_t st) {
     int blocks = (n + kDiagThreads - 1) / kDiagThreads;
     if (blocks > kDiagMaxBlocks) blocks = kDiagMaxBlocks;
     if (blocks < 1) blocks = 1;
-    diag_partial_kernel<<<blocks, kDiagThreads, 0, st>>>(n, x, v, w, mass, inertia, com, d_partials, pass);
+    diag_partial_kernel<<<blocks, kDiagThreads, 0, st>>>(n, x, v, w, mass, inertia, com, d_partials, pass, owned);
     diag_final_kernel<<<1, 32, 0, st>>>(blocks, d_partials, d_out, pass);
     g_launch_count += 2;
 }

@@ -414,6 +414,32 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const
                 }
             }
         }
+        if constexpr (MODE == MODE_FUSED) {
+            if (A.hf.tile_ptr != nullptr) {  // slab runs: this tile's halo items go straight into the neighbours' receive buffers
+                const uint32_t h0 = A.hf.tile_ptr[tile], h1 = A.hf.tile_ptr[tile + 1];
+                if (h1 > h0) {  // uniform over the CTA
+                    compute_barrier();  // the staged results of every thread (and connectors written to global) are visible
+                    for (uint32_t q = h0 + (uint32_t)tid; q < h1; q += NT2) {
+                        const uint2 it = A.hf.items[q];
+                        const int peer = (int)(it.x >> 24), idx = (int)(it.x & 0x7fffffu);
+                        if (it.x & 0x800000u) {  // bond record: 5 connectors
+                            double* dst = A.hf.remote[peer] + A.hf.rec_off[peer] + 15 * (size_t)it.y;
+                            const double* src = bonds_staged ? sconn + 15 * idx : A.bconn_next + 15 * ((size_t)b0 + (size_t)idx);
+#pragma unroll
+                            for (int c = 0; c < 15; c++) dst[c] = src[c];
+                        } else {  // particle: x, v, omega
+                            double* dst = A.hf.remote[peer] + 9 * (size_t)it.y;
+#pragma unroll
+                            for (int c = 0; c < 3; c++) {
+                                dst[c] = sx[3 * idx + c];
+                                dst[3 + c] = sv[3 * idx + c];
+                                dst[6 + c] = sw[3 * idx + c];
+                            }
+                        }
+                    }
+                }
+            }
+        }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // this thread's shared-memory writes -> async proxy
         compute_barrier();
         if (tid == 0) {
@@ -438,6 +464,21 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const
         }
     }
     if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
+    if constexpr (MODE == MODE_FUSED) {
+        if (A.hf.tile_ptr != nullptr) {  // the launch's last CTA publishes the exchange (as halo_push_kernel's last block does)
+            __threadfence_system();
+            __syncthreads();
+            if (tid == 0) {
+                const unsigned int prev = atomicAdd(A.hf.done, 1u);
+                if (prev == gridDim.x - 1u) {
+                    *A.hf.done = 0u;  // next exchange (stream-ordered after this kernel)
+                    __threadfence_system();
+                    for (int p = 0; p < A.hf.n_peers; p++)
+                        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(A.hf.remote_flag[p]), "l"(A.hf.seq) : "memory");
+                }
+            }
+        }
+    }
 }
 
 template <int MASK, int MODE, bool FACETS, int RT2, int LPP>

@@ -52,6 +52,23 @@ struct ModelParams {
     double alt_dt;          // its own spring-update time step (alt_sinter_bridge.h:30)
 };
 
+// Halo stores fused into step_rows2_kernel (multi-GPU slab runs): the CTA that finishes a tile copies the tile's halo items
+// -- new x, v, omega of particles a neighbouring rank holds as ghosts, new connector blocks of the bond records it mirrors --
+// from the staged results straight into that rank's receive buffer over NVLink; the last CTA of the launch publishes the
+// exchange's sequence number (release, system scope).  Replaces the separate halo_push_kernel launch.
+constexpr int kMaxHaloPeers = 8;
+struct HaloFusedArgs {
+    const uint32_t* tile_ptr;   // [n_tiles + 1] first item of every tile; nullptr = off
+    const uint2* items;         // x: peer << 24 | kind << 23 | index inside the tile (kind 0: particle row, 1: bond record
+                                //    relative to the tile's first record), y: slot in the peer's message
+    int n_peers;
+    double* remote[kMaxHaloPeers];              // peer memory of this exchange's parity: particle slot k at 9 k
+    long long rec_off[kMaxHaloPeers];           // doubles: connector block k at rec_off + 15 k
+    unsigned long long* remote_flag[kMaxHaloPeers];
+    unsigned int* done;         // CTAs of this launch that have stored their items
+    unsigned long long seq;
+};
+
 struct ForceArgs {
     int n;
     const double* x;
@@ -87,6 +104,7 @@ struct ForceArgs {
     int rows_per_block;
     int fast;           // relaxed arithmetic (lg_set_math_mode)
     int rows_shape;     // step_rows2_kernel: tile shape index (rows2_shape_for)
+    HaloFusedArgs hf;   // step_rows2_kernel, fused launches of slab runs
     int use_rows;       // fast only: short rows -> a row kernel instead of the tile kernel (1 step_rows_kernel, 2 step_rows2_kernel)
     FastConsts fc;      // its host-computed constants
     double dt;          // integration step of the fused update
@@ -169,7 +187,7 @@ void launch_retag(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* 
 void launch_count_slots(int n, const int32_t* sgid, int S, unsigned long long* d_out, cudaStream_t st);
 // out[16]: sums for lg_diagnostics (pass 0) ; pass 1 adds sum |x - com|^2
 void launch_diag_sums(int n, const double* x, const double* v, const double* w, double mass, double inertia,
-                      const double* com, double* d_partials, double* d_out, int pass, cudaStream_t st);
+                      const double* com, double* d_partials, double* d_out, int pass, const uint8_t* owned, cudaStream_t st);
 
 // slab decomposition: ghost staging (kernels_halo.cu)
 void launch_halo_pack(int n_part, const int32_t* idx, int n_rec, const int32_t* rec, const double* x, const double* v,
@@ -182,7 +200,6 @@ void launch_halo_unpack(int n_part, const int32_t* idx, int n_rec, const int32_t
 // x, v, omega (9 doubles per particle) and the connector blocks of cross-slab bond records (15 doubles each) and
 // stores them straight into the receiving rank's buffer (a cudaIpc mapping of peer memory), then publishes a
 // sequence number there; the RECEIVE side polls its own flag and scatters the buffer into the ghost slots.
-constexpr int kMaxHaloPeers = 8;
 struct HaloSendPeer {
     int n_part, n_rec;
     const int32_t* idx;

@@ -141,7 +141,7 @@ class LocalTables:
     gid: torch.Tensor      # int64 [n]
     owned: torch.Tensor    # bool  [n]
     src: torch.Tensor      # int64 [n]  rank the record came from (the owner, for ghosts)
-    state: torch.Tensor    # float64 [n, 18]  x v theta omega a alpha
+    state: torch.Tensor    # float64 [n, 18 + 10 F]  x v theta omega a alpha, then per facet: 9 wall-spring components + active flag
     S: int
     sgid: torch.Tensor     # int32 [n, S]  local partner index or -1
     spr: torch.Tensor      # float64 [n, S, 9]
@@ -345,7 +345,7 @@ def build_halo_plan(t: LocalTables, rank: int, world: int, group=None) -> HaloPl
 
 
 def block_tables(rank: int, world: int, x, v, theta, omega, S: int, bond_ij=None, bond_conn=None, bond_len=None,
-                 device="cpu") -> LocalTables:
+                 device="cpu", extra_cols: int = 0) -> LocalTables:
     """Initial, arbitrary distribution before the first repartition: rank r 'owns' the contiguous block of global
     ids [r n / W, (r + 1) n / W) of the caller's arrays, without ghosts.  Bond records (global ids, both
     orientations) are taken for the block's particles; partners outside the block are dropped here and come back
@@ -353,7 +353,7 @@ def block_tables(rank: int, world: int, x, v, theta, omega, S: int, bond_ij=None
     n = len(x)
     lo, hi = (rank * n) // world, ((rank + 1) * n) // world
     st = np.concatenate([np.asarray(a, dtype=np.float64)[lo:hi] for a in (x, v, theta, omega)] +
-                        [np.zeros((hi - lo, 6))], axis=1)
+                        [np.zeros((hi - lo, 6 + extra_cols))], axis=1)  # a, alpha, then per-facet wall history (zero)
     gid = torch.arange(lo, hi, dtype=torch.int64, device=device)
     m = hi - lo
     state = torch.from_numpy(st).to(device)
@@ -413,8 +413,10 @@ class SlabSystem:
 
         if not cfg.use_neighbor_list:
             raise ValueError("slab decomposition needs the neighbor-list system (granular_system_neighbor_list)")
-        if cfg.model_mask & MODEL_FACET:
-            raise ValueError("facets are not supported in slab-decomposed runs yet")
+        # one triangular facet (surface contact + surface Hamaker) as in DemConfig; its geometry is global, its per-particle
+        # wall springs migrate with their particle inside the state rows
+        self.n_facets = 1 if cfg.model_mask & MODEL_FACET else 0
+        self.facet_vertices = np.ascontiguousarray(np.asarray(cfg.facet_vertices, dtype=np.float64).reshape(3, 3)).copy()
         self._sys = _sys
         self.lib = _sys.load_library()
         self.cfg = cfg
@@ -444,9 +446,13 @@ class SlabSystem:
                 if callable(unit_vectors):  # a generator callback can only be consumed by the sequential host scan
                     bonds = _sys.host_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors)
                 else:  # device-side bond detection on this rank's GPU (kernels_bonds.cu); same table bit for bit
-                    bonds = _sys.device_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors, device=self.device)
+                    bonds = _sys.device_bond_table(x0, cfg.r_part, cfg.critical_separation, unit_vectors, device=self.dev_index)
         torch.cuda.set_device(self.device)
-        t0 = block_tables(self.rank, self.world, x0, v0, theta0, omega0, self.S, *bonds, device=self.device)
+        self._skin_slots = [(torch.zeros(1, dtype=torch.float64).pin_memory(), torch.cuda.Event()) for _ in range(2)]
+        self._skin_prev, self._skin_turn = None, 0
+        self._stage = None
+        t0 = block_tables(self.rank, self.world, x0, v0, theta0, omega0, self.S, *bonds, device=self.device,
+                          extra_cols=10 * self.n_facets)
         self._install(t0)
 
     # -- plumbing ------------------------------------------------------------------------------------
@@ -504,6 +510,18 @@ class SlabSystem:
         if hamaker:
             self._check(lib.lg_set_hamaker(self.h, cfg.hamaker_A, cfg.hamaker_h0))
         self._check(lib.lg_import_slots_device(self.h, t.sgid.contiguous().data_ptr(), t.spr.contiguous().data_ptr()))
+        for f in range(self.n_facets):
+            verts = np.ascontiguousarray(self.facet_vertices.reshape(9))
+            vf = np.ascontiguousarray(np.asarray(cfg.facet_v, dtype=np.float64).reshape(3))
+            sc = self._sys.ContactParamsStruct.from_seq(cfg.surf_contact)
+            fid = C.c_int(-1)
+            dp = C.POINTER(C.c_double)
+            self._check(lib.lg_add_facet(self.h, verts.ctypes.data_as(dp), vf.ctypes.data_as(dp), C.byref(sc), 1, cfg.surf_A, cfg.surf_h0,
+                                         C.byref(fid)))
+            wall = st[:, 18 + 10 * f:18 + 10 * f + 10]
+            wspr = wall[:, :9].contiguous()
+            wact = (wall[:, 9] != 0.0).to(torch.uint8).contiguous()
+            self._check(lib.lg_import_wall_device(self.h, fid.value, wspr.data_ptr(), wact.data_ptr()))
         self._check(lib.lg_enable_neighbor_list(self.h, cfg.r_verlet))
         sp = C.c_void_p()
         self._check(lib.lg_get_stream(self.h, C.byref(sp)))
@@ -513,6 +531,8 @@ class SlabSystem:
         self.gid, self.owned, self.src = t.gid, t.owned, t.src
         self.own_idx = torch.nonzero(t.owned, as_tuple=True)[0]
         self.x_ref = cols[0][self.own_idx].clone()
+        self._skin_prev = None  # measurements of an older partition are void
+        self.gid_host = None
         self.n_bonds_local = t.n_bonds
         self.plan = build_halo_plan(t, self.rank, self.world, self.group)
         self.send_buf = {r: torch.empty(max(self.plan.send_doubles(r), 1), dtype=torch.float64, device=self.device) for r in self.plan.peers}
@@ -578,7 +598,16 @@ class SlabSystem:
         self._check(lib.lg_export_bonds(self.h, C.byref(nb), C.byref(p_bptr), C.byref(p_bj), C.byref(p_bconn), C.byref(p_blen)))
         self._check(lib.lg_synchronize(self.h))
         n, dev = self.n_local, self.device
-        state = torch.cat([self._field_view(f) for f in ("x", "v", "theta", "omega", "a", "alpha")], dim=1)
+        cols = [self._field_view(f) for f in ("x", "v", "theta", "omega", "a", "alpha")]
+        for f in range(self.n_facets):  # wall history and the facet's current vertices (moved by update_positions)
+            p_ws, p_wa = C.c_void_p(), C.c_void_p()
+            self._check(lib.lg_export_wall(self.h, f, C.byref(p_ws), C.byref(p_wa)))
+            cols.append(_view(p_ws.value, (n, 9), torch.float64, dev))
+            cols.append(_view(p_wa.value, (n,), torch.uint8, dev).to(torch.float64)[:, None])
+            verts = np.zeros(9)
+            self._check(lib.lg_facet_get_vertices(self.h, f, verts.ctypes.data_as(C.POINTER(C.c_double))))
+            self.facet_vertices = verts.reshape(3, 3)
+        state = torch.cat(cols, dim=1)
         nbv = int(nb.value)
         return LocalTables(
             gid=self.gid, owned=self.owned, src=self.src, state=state, S=S.value,
@@ -625,14 +654,29 @@ class SlabSystem:
         self.steps += 1
 
     def needs_repartition(self) -> bool:
-        """True on every rank when some owned particle has moved more than skin / 2 since the last partition."""
+        """True on every rank when some owned particle has moved too far since the last partition.
+
+        The measurement (max displacement, all-reduced) is queued on the system's stream and copied to pinned memory
+        without waiting; what is consumed here is the measurement of the PREVIOUS rebuild, which has long arrived -- no host
+        synchronisation on the every-20-steps path.  Being one period late is paid for with a halved threshold (skin / 4
+        instead of skin / 2): the ghost margin is violated only if the displacement more than doubles within one period.
+        The first check after a (re)partition has nothing to consume and waits."""
         with torch.cuda.stream(self.stream):
             x = self._field_view("x")[self.own_idx]
             d2 = ((x - self.x_ref) ** 2).sum(dim=1).max().reshape(1)
             if self.world > 1:
                 dist.all_reduce(d2, op=dist.ReduceOp.MAX, group=self.group)
-            moved2 = float(d2)  # read back on the system's stream (it is non-blocking: the default stream does not order with it)
-        return moved2 > (0.5 * self.skin) ** 2
+            slot = self._skin_slots[self._skin_turn & 1]
+            slot[0].copy_(d2, non_blocking=True)
+            slot[1].record(self.stream)
+        prev = self._skin_prev
+        self._skin_prev = slot
+        self._skin_turn += 1
+        if prev is None:  # nothing measured yet for this partition
+            slot[1].synchronize()
+            return float(slot[0]) > (0.5 * self.skin) ** 2
+        prev[1].synchronize()  # recorded a whole period ago
+        return float(prev[0]) > (0.25 * self.skin) ** 2
 
     def repartition(self):
         with torch.cuda.stream(self.stream):
@@ -645,7 +689,10 @@ class SlabSystem:
             self.repartition()
         self._check(self.lib.lg_update_neighbor_list(self.h))
 
-    def run(self, dt: float, n_steps: int, rebuild_every: int = 0):
+    def facet_update_positions(self, dt: float, facet_id: int = 0):
+        self._check(self.lib.lg_facet_update_positions(self.h, int(facet_id), float(dt)))
+
+    def run(self, dt: float, n_steps: int, rebuild_every: int = 0, move_facets: bool = False):
         k = 0
         while k < n_steps:
             if rebuild_every > 0 and self.steps % rebuild_every == 0:
@@ -653,11 +700,14 @@ class SlabSystem:
             if self.transport == "p2p" and self.kicked:
                 # the whole stretch up to the next rebuild is queued by ONE library call (step kernel, push, pull per step)
                 chunk = n_steps - k if rebuild_every <= 0 else min(n_steps - k, rebuild_every - self.steps % rebuild_every)
-                self._check(self.lib.lg_run_slab(self.h, self.halo, float(dt), chunk))
+                self._check(self.lib.lg_run_slab(self.h, self.halo, float(dt), chunk, int(move_facets)))
                 self.steps += chunk
                 k += chunk
             else:
                 self.do_step(dt)
+                if move_facets:
+                    for f in range(self.n_facets):
+                        self.facet_update_positions(dt, f)
                 k += 1
 
     def synchronize(self):
@@ -681,16 +731,23 @@ class SlabSystem:
         return out.cpu().numpy()
 
     def set_state_host(self, x, v, theta, omega):
-        """lg_set_state for a decomposed system.  Every rank copies the caller's full arrays host -> device (asynchronous
-        when they are pinned; numpy arrays or tensors) and gathers the rows it holds (owned and ghost) on the device;
-        re-arms the first-step half kick like the reference constructor.  The copies run on torch's current stream, not
+        """lg_set_state for a decomposed system.  Every rank gathers the rows it holds (owned and ghost) from the caller's
+        arrays into a pinned staging block on the host and copies only those host -> device; re-arms the first-step half
+        kick like the reference constructor.  The copies run on torch's current stream, not
         on the library's: pinned host blocks remember the streams that used them, and the library's stream dies with
         the system."""
         cur = torch.cuda.current_stream(self.device)
+        if self.gid_host is None:
+            self.gid_host = self.gid.cpu().numpy()
+        nl = len(self.gid_host)
+        if self._stage is None or self._stage.shape[1] < nl:
+            self._stage = torch.empty((4, int(nl * 1.2) + 16, 3), dtype=torch.float64).pin_memory()
         loc = []
-        for a in (x, v, theta, omega):
-            t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64)))
-            loc.append(t.to(self.device, non_blocking=True).index_select(0, self.gid).contiguous())
+        for k, a in enumerate((x, v, theta, omega)):
+            # only the rows this rank holds (owned + ghosts) cross PCIe: gathered on the host into a pinned staging block
+            src = a.numpy() if isinstance(a, torch.Tensor) else np.asarray(a, dtype=np.float64)
+            np.take(src.reshape(-1, 3), self.gid_host, axis=0, out=self._stage[k, :nl].numpy())
+            loc.append(self._stage[k, :nl].to(self.device, non_blocking=True))
         x_ref = loc[0][self.own_idx].clone()
         cur.synchronize()
         self._check(self.lib.lg_import_state_device(self.h, *[c.data_ptr() for c in loc], None, None, 0))  # synchronises
@@ -726,29 +783,33 @@ class SlabSystem:
                 "ghosts_total": int(tot[3]), "launches": int(out[5]), "repartitions": self.repartitions,
                 "halo_bytes_per_step": self.halo_bytes_per_step, "transport": self.transport}
 
+    def _partial(self, pass_: int, com: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """lg_diagnostics_partial: the device reduction of lg_diagnostics over this rank's OWNED particles, left on the
+        device (call inside the system's stream context)."""
+        p = C.c_void_p()
+        self._check(self.lib.lg_diagnostics_partial(self.h, int(pass_), com.data_ptr() if com is not None else None, C.byref(p)))
+        return _view(p.value, (12,), torch.float64, self.device).clone()
+
     def kinetic_energy(self) -> float:
-        """compute_total_kinetic_energy (test/compute_energy.cpp:7-17) over the owned particles of all ranks."""
-        cfg = self.cfg
+        """compute_total_kinetic_energy (test/compute_energy.cpp:7-17): lg_diagnostics partial sums of the owned particles,
+        all-reduced over the ranks."""
         with torch.cuda.stream(self.stream):
-            v, w = (self._field_view(f)[self.own_idx] for f in ("v", "omega"))
-            s = (cfg.mass * (v * v).sum() / 2.0 + cfg.inertia * (w * w).sum() / 2.0).reshape(1)
+            s = self._partial(0)[:2]
             if self.world > 1:
                 dist.all_reduce(s, group=self.group)
-            return float(s)  # inside the stream context, see needs_repartition
+            return float(s.sum())  # inside the stream context, see needs_repartition
 
     def diagnostics(self) -> dict:
-        """test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26 over the owned particles of all ranks."""
+        """test/compute_energy.cpp:7-58, test/mass_distribution.cpp:7-26: lg_diagnostics partial sums -> all_reduce(SUM)."""
         cfg = self.cfg
         with torch.cuda.stream(self.stream):
-            x, v, w = (self._field_view(f)[self.own_idx] for f in ("x", "v", "omega"))
-            s = torch.cat([(cfg.mass * (v * v).sum(1) / 2.0).sum().reshape(1), (cfg.inertia * (w * w).sum(1) / 2.0).sum().reshape(1),
-                           v.sum(0), (cfg.inertia * w + torch.linalg.cross(x, cfg.mass * v)).sum(0), x.sum(0)])
+            s = self._partial(0)[:11]
             if self.world > 1:
                 dist.all_reduce(s, group=self.group)
-            com = s[8:11] / self.n_global
-            rg2 = ((x - com) ** 2).sum().reshape(1)
+            com = (s[8:11] / self.n_global).contiguous()
+            r = self._partial(1, com)[11:12]
             if self.world > 1:
-                dist.all_reduce(rg2, group=self.group)
-            s, rg2, com = s.cpu().numpy(), float(rg2), com.cpu().numpy()  # inside the stream context, see needs_repartition
+                dist.all_reduce(r, group=self.group)
+            s, rg2, com = s.cpu().numpy(), float(r), com.cpu().numpy()
         return {"ke": s[0] + s[1], "ke_trs": s[0], "ke_rot": s[1], "linear_momentum": cfg.mass * float(np.linalg.norm(s[2:5])),
                 "angular_momentum": float(np.linalg.norm(s[5:8])), "com": com, "rg": float(np.sqrt(rg2 / self.n_global))}

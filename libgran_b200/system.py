@@ -41,7 +41,7 @@ ABI_SYMBOLS = (
     "lg_flush", "lg_first_half_kick", "lg_import_state_device", "lg_set_owned_device", "lg_export_slots",
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
     "lg_halo_create", "lg_halo_set_lists", "lg_halo_export", "lg_halo_connect", "lg_halo_exchange", "lg_run_slab",
-    "lg_halo_disconnect", "lg_halo_destroy",
+    "lg_halo_disconnect", "lg_halo_destroy", "lg_export_wall", "lg_import_wall_device", "lg_diagnostics_partial",
 )
 
 
@@ -164,7 +164,10 @@ def load_library(path: Optional[str] = None):
     lib.lg_halo_export.argtypes = [vp, C.c_int, C.c_char_p, C.POINTER(C.c_int64)]
     lib.lg_halo_connect.argtypes = [vp, C.c_int, C.c_char_p, C.POINTER(C.c_int64)]
     lib.lg_halo_exchange.argtypes = [vp, vp]
-    lib.lg_run_slab.argtypes = [vp, vp, C.c_double, C.c_int64]
+    lib.lg_run_slab.argtypes = [vp, vp, C.c_double, C.c_int64, C.c_int]
+    lib.lg_export_wall.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp)]
+    lib.lg_import_wall_device.argtypes = [vp, C.c_int, vp, vp]
+    lib.lg_diagnostics_partial.argtypes = [vp, C.c_int, vp, C.POINTER(vp)]
     lib.lg_halo_disconnect.argtypes = [vp]
     lib.lg_halo_destroy.argtypes = [vp]
     for name in ABI_SYMBOLS:
