@@ -168,6 +168,30 @@ def build_workload(args, world: int = 1, sample: bool = False):
     raise SystemExit(f"unknown --config {c}")
 
 
+def morton_presort(scn):
+    """The same particles listed along a Morton curve (cells of one diameter).  The slab driver keeps the caller's global-id
+    order on every rank (that is what makes a decomposed run bit-identical to one GPU), so a synthetic input whose ids carry
+    no locality (random packing, fractal cluster) is handed to it spatially ordered; the single-GPU arm leaves the caller's
+    order alone and renumbers internally (lg_set_reorder)."""
+    x = scn.x0
+    c = np.floor((x - x.min(axis=0)) / (2.0 * scn.cfg.r_part)).astype(np.uint64)
+    c = np.minimum(c, 1023)
+
+    def spread(v):
+        v = (v | (v << np.uint64(16))) & np.uint64(0x030000FF)
+        v = (v | (v << np.uint64(8))) & np.uint64(0x0300F00F)
+        v = (v | (v << np.uint64(4))) & np.uint64(0x030C30C3)
+        v = (v | (v << np.uint64(2))) & np.uint64(0x09249249)
+        return v
+
+    key = np.zeros(len(x), dtype=np.uint64)
+    for axis in range(3):  # 10 bits per axis: two 5-bit halves through the 8-bit spreader
+        lo, hi = c[:, axis] & np.uint64(31), c[:, axis] >> np.uint64(5)
+        key |= (spread(lo) << np.uint64(axis)) | (spread(hi) << np.uint64(15 + axis))
+    order = np.argsort(key, kind="stable")
+    return S.Scenario(scn.name + "_morton", scn.cfg, *(np.ascontiguousarray(a[order]) for a in scn.state))
+
+
 def workload_line(desc: str) -> str:
     return f"{desc}, r_verlet=5r, rebuild every {REBUILD_EVERY} steps"
 
@@ -204,6 +228,9 @@ def run_ours(args):
     cfg = scn.cfg
     n = cfg.n
     if world > 1:
+        if args.config in ("2", "3", "5", "5d") and args.reorder != "off":
+            scn = morton_presort(scn)
+            desc += ", input listed along a Morton curve (host pre-sort; the slab driver keeps the caller's id order)"
         return run_slab(args, scn, desc, moves, world, rank, local_rank)
 
     uv = numpy_unit_vectors((4 * n if args.config == "3" else n) + 1024) if cfg.model_mask & S.MODEL_SINTER else None
@@ -434,10 +461,10 @@ def run_slab(args, scn, desc, moves, world, rank, local_rank):
     t1 = time.perf_counter()
     tt = torch.tensor([t1 - t0], dtype=torch.float64, device=dev)
     dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    nloc = torch.tensor([sysm.n_local, own], dtype=torch.int64, device=dev)
+    nloc = torch.tensor([getattr(sysm, "last_upload_rows", n), own], dtype=torch.int64, device=dev)
     dist.all_reduce(nloc)
     e2e = {"value": round(n * e2e_steps / float(tt), 1), "unit": METRIC,
-           "h2d_bytes_per_step": round(4 * 24 * int(nloc[0]) / e2e_steps, 1),  # every rank uploads the rows it holds (owned + ghosts)
+           "h2d_bytes_per_step": round(4 * 24 * int(nloc[0]) / e2e_steps, 1),  # every rank uploads the id range it holds (owned + ghosts)
            "d2h_bytes_per_step": round((4 * 24 * int(nloc[1]) + (e2e_steps // 10) * 12 * 8 * world) / e2e_steps, 1),
            "steps": e2e_steps, "final_ke": ke,
            "what": "per rank: set_state_host (H2D, pinned) + K/10 x [run(10 steps: step + halo exchange, rebuild/20) + KE "

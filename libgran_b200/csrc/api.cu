@@ -177,6 +177,7 @@ struct lg_system {
     bool halo_stored_by_step = false;  // the last step launch has stored and published the halo: no push kernel
     // tile shape of step_rows2_kernel: heuristic (deterministic) or, after lg_set_autotune(1), measured on the first fused launches
     int autotune = 0;
+    int forced_shape = -1;           // lg_set_rows_shape: the caller pins the shape (slab runs: one shape on every rank)
     int tuned_shape = -1;
     double tuned_k = 0.0;
     int tune_launch = 0;             // 0 .. 3 * kTuneReps - 1 while measuring
@@ -381,8 +382,8 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
         static const double rows_kmax = [] { const char* e = std::getenv("LGB200_ROWS_KMAX"); return e ? std::atof(e) : 1.0e9; }();  // mean row length above which the tile kernel takes over
         A.use_rows = (s->math_mode && (s->variant == 2 || (rows_enabled && k_mean <= (rows_enabled == 1 ? 24.0 : rows_kmax)))) ? (rows_enabled == 1 ? 1 : 2) : 0;  // variant 2: row kernel whatever the row length
-        A.rows_shape = rows2_shape_for(k_mean, (int)s->n, s->n_bonds > 0);
-        if (A.use_rows == 2 && s->autotune && std::getenv("LGB200_ROWS_SHAPE") == nullptr) {
+        A.rows_shape = s->forced_shape >= 0 ? s->forced_shape : rows2_shape_for(k_mean, (int)s->n, s->n_bonds > 0);
+        if (A.use_rows == 2 && s->autotune && s->forced_shape < 0 && std::getenv("LGB200_ROWS_SHAPE") == nullptr) {
             if (s->tuned_shape >= 0 && std::fabs(k_mean - s->tuned_k) <= 0.25 * s->tuned_k) {
                 A.rows_shape = s->tuned_shape;
             } else if (fused_dt >= 0.0) {  // measure: kTuneReps fused launches per shape, the first of each discarded
@@ -1290,9 +1291,24 @@ int lg_set_autotune(lg_system* s, int enabled) {
     return LG_OK;
 }
 
+int lg_set_rows_shape(lg_system* s, int shape) {
+    LG_ENTER(s);
+    if (shape < -1 || shape > 2) return fail(LG_EINVAL, "shape must be -1 (rule / autotune), 0, 1 or 2");
+    s->forced_shape = shape;
+    return LG_OK;
+}
+
+int lg_rows_shape_rule(double mean_row_length, int64_t n, int has_bonds) {
+    return rows2_shape_for(mean_row_length, (int)std::min<int64_t>(n, 2000000000LL), has_bonds != 0);
+}
+
 int lg_get_rows_shape(lg_system* s, int* shape) {
     LG_ENTER(s);
     if (!shape) return fail(LG_EINVAL, "null output");
+    if (s->forced_shape >= 0) {
+        *shape = s->forced_shape;
+        return LG_OK;
+    }
     const double k_mean = s->n > 0 ? (double)s->n_pairs / (double)s->n : 0.0;
     *shape = (s->autotune && s->tuned_shape >= 0) ? s->tuned_shape : rows2_shape_for(k_mean, (int)s->n, s->n_bonds > 0);
     return LG_OK;

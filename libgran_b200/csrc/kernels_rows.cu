@@ -29,17 +29,18 @@ namespace lg {
 namespace {
 
 #ifndef LG_R2_RT
-#define LG_R2_RT 128   // default shape: particles per tile
+#define LG_R2_RT 96    // default shape: particles per tile (96 x 2 lanes, 3 CTAs/SM measured best on cfg 4: profiles/README.md r02f, r02j)
 #endif
 #ifndef LG_R2_LPP
 #define LG_R2_LPP 2    // default shape: lanes per particle in pass 2
 #endif
+// resident CTAs per SM the launch bound asks for: 3 for CTAs of up to 192 threads (112 registers), else 2 (128 registers)
 #ifndef LG_R2_MINB
-#define LG_R2_MINB 2   // resident CTAs per SM the launch bound asks for
+#define LG_R2_MINB(threads) ((threads) <= 192 ? 3 : 2)
 #endif
 
 // Tile shape: RT particles per tile, LPP cooperating lanes per particle in the pair loop (RT * LPP threads per CTA).
-//   <128, 2>  rows of ~10 neighbors (aggregates)          staged x: the tile +- 128 particles, 12 pairs per particle
+//   < 96, 2>  rows of ~10 neighbors (aggregates)          staged x: the tile +- 128 particles, 12 pairs per particle
 //   < 64, 4>  rows of ~20-45 (fractal clusters, loose packings)     +- 192                  48
 //   < 32, 8>  rows of ~50-100 (dense packings)                      +- 256                  96
 template <int RT_, int LPP_>
@@ -102,7 +103,7 @@ __device__ __forceinline__ void l2_prefetch(const void* begin, uint32_t nbytes) 
 }
 
 template <int MASK, int MODE, bool FACETS, int RT2, int LPP>
-__global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
+__global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_kernel(const __grid_constant__ ForceArgs A) {
     using SH = Shape<RT2, LPP>;
     using Stage2 = typename SH::Stage;
     using Rows2Smem = typename SH::Smem;
@@ -531,7 +532,7 @@ void launch_rows2_mode(const ForceArgs& args, int mask, cudaStream_t st) {
 int rows2_shape_for(double k_mean, int n, bool bonds) {
     static const int forced = [] { const char* e = std::getenv("LGB200_ROWS_SHAPE"); return e ? std::atoi(e) : -1; }();
     if (forced >= 0 && forced <= 2) return forced;
-    // measured (profiles/README.md r02g): <128,2> for rows of ~10, <64,4> for loose packings (rows of ~35, no bridges),
+    // measured (profiles/README.md r02g): <96,2> for rows of ~10, <64,4> for loose packings (rows of ~35, no bridges),
     // <32,8> for dense rows, for bridged clusters with long rows (fewer tiles overflow the staged records) and for systems
     // too small to fill the SMs with larger tiles
     if (k_mean <= 16.0) return n >= 40000 ? 0 : 2;

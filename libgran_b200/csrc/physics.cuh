@@ -229,7 +229,13 @@ __device__ __forceinline__ d3 cross_fma(d3 a, d3 b) {
 // ITER Newton steps: the seed carries >= 20 good bits, each step doubles them (20 -> 40 -> 80), so two steps reach the
 // last bit or two of a double -- enough wherever 1e-10 is asked (directions, Hamaker); three where the result feeds a
 // cancelling difference (bridge spring lengths, refined once more there).
-template <int ITER = 2>
+#ifndef LG_FAST_NR_ITERS
+#define LG_FAST_NR_ITERS 2
+#endif
+#ifndef LG_BRIDGE_NR_ITERS
+#define LG_BRIDGE_NR_ITERS 3
+#endif
+template <int ITER = LG_FAST_NR_ITERS>
 __device__ __forceinline__ double rcp_nr(double x) {
     double y;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -240,7 +246,7 @@ __device__ __forceinline__ double rcp_nr(double x) {
     }
     return y;
 }
-template <int ITER = 2>
+template <int ITER = LG_FAST_NR_ITERS>
 __device__ __forceinline__ double rsqrt_nr(double x) {
     double y;
     asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(x));
@@ -256,7 +262,7 @@ __device__ __forceinline__ double rsqrt_nr(double x) {
 // (the closing step of the correctly rounded square root; the result is the correctly rounded one except for arguments
 // within ~2^-100 of a rounding tie).  z == 0 -> both 0 (a coincident connector pair contributes no force).
 __device__ __forceinline__ void sqrt_and_rsqrt(double z, double& root, double& inv) {
-    const double y = z > 0.0 ? rsqrt_nr<3>(z) : 0.0;
+    const double y = z > 0.0 ? rsqrt_nr<LG_BRIDGE_NR_ITERS>(z) : 0.0;
     const double g = z * y;
     root = fma(0.5 * y, fma(-g, g, z), g);
     inv = y;

@@ -450,6 +450,7 @@ class SlabSystem:
         torch.cuda.set_device(self.device)
         self._skin_slots = [(torch.zeros(1, dtype=torch.float64).pin_memory(), torch.cuda.Event()) for _ in range(2)]
         self._skin_prev, self._skin_turn = None, 0
+        self.rows_shape = None
         self._stage = None
         t0 = block_tables(self.rank, self.world, x0, v0, theta0, omega0, self.S, *bonds, device=self.device,
                           extra_cols=10 * self.n_facets)
@@ -495,10 +496,13 @@ class SlabSystem:
         self._check(lib.lg_set_max_contacts(self.h, self.S))
         if self.math_mode:
             self._check(lib.lg_set_math_mode(self.h, self.math_mode))
+            if self.rows_shape is not None:
+                self._check(lib.lg_set_rows_shape(self.h, self.rows_shape))
         st = t.state
         cols = [st[:, 3 * k:3 * k + 3].contiguous() for k in range(6)]  # x v theta omega a alpha
-        self._check(lib.lg_import_state_device(self.h, *[c.data_ptr() for c in cols], int(self.kicked)))
         owned_u8 = t.owned.to(torch.uint8).contiguous()
+        torch.cuda.current_stream(self.device).synchronize()  # the library copies on its own stream: the slices must exist
+        self._check(lib.lg_import_state_device(self.h, *[c.data_ptr() for c in cols], int(self.kicked)))
         self._check(lib.lg_set_owned_device(self.h, owned_u8.data_ptr()))
         contact, sinter, hamaker = self._models
         cp = self._sys.ContactParamsStruct.from_seq(cfg.contact)
@@ -511,16 +515,21 @@ class SlabSystem:
             self._check(lib.lg_set_hamaker(self.h, cfg.hamaker_A, cfg.hamaker_h0))
         self._check(lib.lg_import_slots_device(self.h, t.sgid.contiguous().data_ptr(), t.spr.contiguous().data_ptr()))
         for f in range(self.n_facets):
-            verts = np.ascontiguousarray(self.facet_vertices.reshape(9))
+            # unit normal and area are fixed at construction (triangular_facet.h:26-28) and NOT recomputed when the facet moves:
+            # construct from the original vertices, then overwrite the vertices with the current ones
+            verts = np.ascontiguousarray(np.asarray(cfg.facet_vertices, dtype=np.float64).reshape(9))
             vf = np.ascontiguousarray(np.asarray(cfg.facet_v, dtype=np.float64).reshape(3))
             sc = self._sys.ContactParamsStruct.from_seq(cfg.surf_contact)
             fid = C.c_int(-1)
             dp = C.POINTER(C.c_double)
             self._check(lib.lg_add_facet(self.h, verts.ctypes.data_as(dp), vf.ctypes.data_as(dp), C.byref(sc), 1, cfg.surf_A, cfg.surf_h0,
                                          C.byref(fid)))
+            cur = np.ascontiguousarray(self.facet_vertices.reshape(9))
+            self._check(lib.lg_facet_set_vertices(self.h, fid.value, cur.ctypes.data_as(dp)))
             wall = st[:, 18 + 10 * f:18 + 10 * f + 10]
             wspr = wall[:, :9].contiguous()
             wact = (wall[:, 9] != 0.0).to(torch.uint8).contiguous()
+            torch.cuda.current_stream(self.device).synchronize()  # the library copies on its own stream: the slices must exist
             self._check(lib.lg_import_wall_device(self.h, fid.value, wspr.data_ptr(), wact.data_ptr()))
         self._check(lib.lg_enable_neighbor_list(self.h, cfg.r_verlet))
         sp = C.c_void_p()
@@ -666,9 +675,15 @@ class SlabSystem:
             d2 = ((x - self.x_ref) ** 2).sum(dim=1).max().reshape(1)
             if self.world > 1:
                 dist.all_reduce(d2, op=dist.ReduceOp.MAX, group=self.group)
-            slot = self._skin_slots[self._skin_turn & 1]
-            slot[0].copy_(d2, non_blocking=True)
-            slot[1].record(self.stream)
+            ready = torch.cuda.Event()
+            ready.record(self.stream)
+        # the copy into pinned memory runs on torch's current stream (pinned blocks remember the streams that used them, and
+        # the library's stream dies with the system -- see set_state_host), ordered after the measurement by an event
+        cur = torch.cuda.current_stream(self.device)
+        cur.wait_event(ready)
+        slot = self._skin_slots[self._skin_turn & 1]
+        slot[0].copy_(d2, non_blocking=True)
+        slot[1].record(cur)
         prev = self._skin_prev
         self._skin_prev = slot
         self._skin_turn += 1
@@ -688,6 +703,16 @@ class SlabSystem:
         if self.world > 1 and self.needs_repartition():
             self.repartition()
         self._check(self.lib.lg_update_neighbor_list(self.h))
+        if self.math_mode and self.rows_shape is None:
+            # tile shape of step_rows2_kernel from GLOBAL statistics (mean row length over all ranks, total particle count),
+            # pinned on every rank for the life of the run: every row is then summed in the same order as on one GPU
+            out = (C.c_int64 * 8)()
+            self._check(self.lib.lg_get_counters(self.h, out))
+            pairs = torch.tensor([out[0]], dtype=torch.int64, device=self.device)
+            if self.world > 1:
+                dist.all_reduce(pairs, group=self.group)
+            self.rows_shape = int(self.lib.lg_rows_shape_rule(float(int(pairs)) / max(self.n_global, 1), self.n_global, int(self._models[1])))
+            self._check(self.lib.lg_set_rows_shape(self.h, self.rows_shape))
 
     def facet_update_positions(self, dt: float, facet_id: int = 0):
         self._check(self.lib.lg_facet_update_positions(self.h, int(facet_id), float(dt)))
@@ -731,23 +756,24 @@ class SlabSystem:
         return out.cpu().numpy()
 
     def set_state_host(self, x, v, theta, omega):
-        """lg_set_state for a decomposed system.  Every rank gathers the rows it holds (owned and ghost) from the caller's
-        arrays into a pinned staging block on the host and copies only those host -> device; re-arms the first-step half
-        kick like the reference constructor.  The copies run on torch's current stream, not
+        """lg_set_state for a decomposed system.  Every rank copies the id range it holds (owned and ghost rows) of the
+        caller's arrays host -> device and picks its rows there; re-arms the first-step half kick like the reference
+        constructor.  The copies run on torch's current stream, not
         on the library's: pinned host blocks remember the streams that used them, and the library's stream dies with
         the system."""
         cur = torch.cuda.current_stream(self.device)
-        if self.gid_host is None:
-            self.gid_host = self.gid.cpu().numpy()
-        nl = len(self.gid_host)
-        if self._stage is None or self._stage.shape[1] < nl:
-            self._stage = torch.empty((4, int(nl * 1.2) + 16, 3), dtype=torch.float64).pin_memory()
+        if self.gid_host is None:  # cached per partition: the id range this rank holds
+            self.gid_host = (int(self.gid.min()), int(self.gid.max()))
+        gmin, gmax = self.gid_host
+        rel = self.gid - gmin
         loc = []
-        for k, a in enumerate((x, v, theta, omega)):
-            # only the rows this rank holds (owned + ghosts) cross PCIe: gathered on the host into a pinned staging block
-            src = a.numpy() if isinstance(a, torch.Tensor) else np.asarray(a, dtype=np.float64)
-            np.take(src.reshape(-1, 3), self.gid_host, axis=0, out=self._stage[k, :nl].numpy())
-            loc.append(self._stage[k, :nl].to(self.device, non_blocking=True))
+        for a in (x, v, theta, omega):
+            # only the id range this rank holds (owned + ghosts) crosses PCIe -- one contiguous slice of the caller's array
+            # (asynchronous when it is pinned), its rows picked on the device.  Slabs of an input whose ids run along the slab
+            # axis span about 1 / world of the array; an input without such order degrades to the full copy.
+            t = a if isinstance(a, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=np.float64)))
+            loc.append(t.reshape(-1, 3)[gmin:gmax + 1].to(self.device, non_blocking=True).index_select(0, rel).contiguous())
+        self.last_upload_rows = gmax - gmin + 1
         x_ref = loc[0][self.own_idx].clone()
         cur.synchronize()
         self._check(self.lib.lg_import_state_device(self.h, *[c.data_ptr() for c in loc], None, None, 0))  # synchronises

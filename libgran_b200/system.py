@@ -34,7 +34,8 @@ ABI_SYMBOLS = (
     "lg_gen_fractal_aggregate", "lg_gen_random_packing",
     # SURVEY.md section 8f variants
     "lg_set_hamaker_variant", "lg_set_integrator", "lg_set_fixed_particle", "lg_set_central_attraction",
-    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder", "lg_set_autotune", "lg_get_rows_shape", "lg_bond_table_create_device",
+    "lg_alt_bond_table_create", "lg_set_alt_bond_table", "lg_get_alt_bond", "lg_set_reorder", "lg_set_autotune", "lg_get_rows_shape", "lg_bond_table_create_device", "lg_set_rows_shape",
+    "lg_rows_shape_rule",
     "lg_dumper_create", "lg_dump_particles", "lg_dump_necks", "lg_dump_spring_connectors", "lg_dump_particles_csv",
     "lg_dumper_wait", "lg_dumper_destroy", "lg_write_particles", "lg_write_necks", "lg_write_spring_connectors",
     # slab decomposition support
@@ -139,6 +140,8 @@ def load_library(path: Optional[str] = None):
     lib.lg_set_autotune.argtypes = [vp, C.c_int]
     lib.lg_bond_table_create_device.argtypes = [C.c_int64, vp, C.c_double, C.c_double, C.c_int64, vp, C.c_int, C.POINTER(vp)]
     lib.lg_get_rows_shape.argtypes = [vp, C.POINTER(C.c_int)]
+    lib.lg_set_rows_shape.argtypes = [vp, C.c_int]
+    lib.lg_rows_shape_rule.argtypes = [C.c_double, C.c_int64, C.c_int]
     lib.lg_dumper_create.argtypes = [vp, C.c_char_p, C.POINTER(vp)]
     for name in ("lg_dump_particles", "lg_dump_necks", "lg_dump_spring_connectors"):
         getattr(lib, name).argtypes = [vp, vp]
