@@ -56,7 +56,7 @@ def test_halo_bad_arguments(lib):
     hl = C.c_void_p()
     assert lib.lg_halo_create(None, 1, (C.c_int64 * 1)(8), C.byref(hl)) == -1
     assert lib.lg_halo_exchange(None, None) == -1
-    assert lib.lg_run_slab(None, None, 1e-13, 1) == -1
+    assert lib.lg_run_slab(None, None, 1e-13, 1, 0) == -1
     assert lib.lg_halo_set_lists(None, 0, 0, None, 0, None, 0, None, 0, None) == -1
     assert lib.lg_halo_export(None, 0, C.create_string_buffer(64), (C.c_int64 * 4)()) == -1
     assert lib.lg_halo_connect(None, 0, C.create_string_buffer(64), (C.c_int64 * 4)()) == -1
