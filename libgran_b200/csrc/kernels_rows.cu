@@ -420,22 +420,21 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
                 const uint32_t h0 = A.hf.tile_ptr[tile], h1 = A.hf.tile_ptr[tile + 1];
                 if (h1 > h0) {  // uniform over the CTA
                     compute_barrier();  // the staged results of every thread (and connectors written to global) are visible
-                    for (uint32_t q = h0 + (uint32_t)tid; q < h1; q += NT2) {
-                        const uint2 it = A.hf.items[q];
+                    // 16 consecutive threads per item, one double each: an item's 72 / 120 bytes leave as one or two
+                    // contiguous NVLink writes instead of 9 / 15 scattered ones
+                    const uint32_t n_slots = (h1 - h0) * 16u;
+                    for (uint32_t e = (uint32_t)tid; e < n_slots; e += NT2) {
+                        const uint2 it = A.hf.items[h0 + (e >> 4)];
+                        const int c = (int)(e & 15u);
                         const int peer = (int)(it.x >> 24), idx = (int)(it.x & 0x7fffffu);
                         if (it.x & 0x800000u) {  // bond record: 5 connectors
-                            double* dst = A.hf.remote[peer] + A.hf.rec_off[peer] + 15 * (size_t)it.y;
-                            const double* src = bonds_staged ? sconn + 15 * idx : A.bconn_next + 15 * ((size_t)b0 + (size_t)idx);
-#pragma unroll
-                            for (int c = 0; c < 15; c++) dst[c] = src[c];
-                        } else {  // particle: x, v, omega
-                            double* dst = A.hf.remote[peer] + 9 * (size_t)it.y;
-#pragma unroll
-                            for (int c = 0; c < 3; c++) {
-                                dst[c] = sx[3 * idx + c];
-                                dst[3 + c] = sv[3 * idx + c];
-                                dst[6 + c] = sw[3 * idx + c];
+                            if (c < 15) {
+                                const double* src = bonds_staged ? sconn + 15 * idx : A.bconn_next + 15 * ((size_t)b0 + (size_t)idx);
+                                A.hf.remote[peer][A.hf.rec_off[peer] + 15 * (size_t)it.y + c] = src[c];
                             }
+                        } else if (c < 9) {  // particle: x, v, omega
+                            const double* src = c < 3 ? sx : (c < 6 ? sv : sw);
+                            A.hf.remote[peer][9 * (size_t)it.y + c] = src[3 * idx + (c % 3)];
                         }
                     }
                 }

@@ -140,6 +140,32 @@ __device__ __noinline__ void contact_heavy(const ForceArgs& A, int i, int j, uin
     store3(out6 + 3, c.alpha);
 }
 
+// The same for the relaxed-arithmetic kernels (row kernels, LG_MATH_FAST): contact_force_fast on the caller's relaxed geometry
+// (n, overlap -- the overlap DECISION has been taken by the caller, on the exact expression inside the rounding band).
+__device__ __noinline__ void contact_heavy_fast(const ForceArgs& A, int i, int j, uint32_t p, d3 n, double overlap, double* out6) {
+    const d3 vi = load3(A.v + 3 * (size_t)i), wi = load3(A.w + 3 * (size_t)i);
+    const d3 vj = load3(A.v + 3 * (size_t)j), wj = load3(A.w + 3 * (size_t)j);
+    const int t = A.tag[p];
+    int slot = t;
+    Springs s;
+    if (t == kTagNone) {  // first overlapping evaluation: claim a free slot of particle i
+        slot = -1;
+        for (int k = 0; k < A.S; k++)
+            if (atomicCAS(&A.sgid[(size_t)i * A.S + k], -1, j) == -1) {  // bookkeeping only
+                slot = k;
+                break;
+            }
+        s.xi[0] = s.xi[1] = s.xi[2] = zero3();
+        if (slot >= 0) A.tag[p] = (uint8_t)slot; else atomicOr(A.err, ERR_SLOT_OVERFLOW);
+    } else {
+        s = ld_springs(A.spr + ((size_t)i * A.S + slot) * 9);
+    }
+    const Accel c = contact_force_fast(A.mp.cp, A.fc, A.mp.r, n, overlap, vi, vj, wi, wj, s);
+    if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
+    store3(out6, c.a);
+    store3(out6 + 3, c.alpha);
+}
+
 template <bool DAMPED>
 __device__ __forceinline__ void bridge_fast(const ForceArgs& A, const double* ci, const double* cj, const double* len, d3 xi, d3 xj,
                                             d3 vi, d3 vj, d3 wi, d3 wj, d3& fa, d3& ta) {
@@ -206,7 +232,7 @@ __device__ __noinline__ void rows_slow_pairs(const ForceArgs& A, const double* s
                 acc_a += ha;
                 continue;
             }
-            contact_heavy(A, i0 + r, j, p, v6);
+            contact_heavy_fast(A, i0 + r, j, p, gf.n, overlap, v6);
         }
         acc_a += kHamaker ? load3(v6) + ha : load3(v6);
         acc_al += load3(v6 + 3);

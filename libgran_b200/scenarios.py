@@ -175,13 +175,13 @@ def surface_drop() -> Scenario:
     return Scenario("surface_drop", cfg, x0, v0, _zeros(1), _zeros(1))
 
 
-_GOLDEN = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+_DATA = os.path.join(os.path.dirname(os.path.abspath(__file__)), "data")  # package data: the aggregate of resources/aggregate.h
 
 
 def aggregate_coordinates() -> np.ndarray:
     """The 150-particle soot aggregate of resources/aggregate.h:8-158, in units of r_part (fixture
-    extracted by tests/golden/make_golden.py into tests/golden/aggregate_150.npy)."""
-    return np.load(os.path.join(_GOLDEN, "aggregate_150.npy"))
+    extracted by tests/golden/make_golden.py into libgran_b200/data/aggregate_150.npy)."""
+    return np.load(os.path.join(_DATA, "aggregate_150.npy"))
 
 
 def aggregate(models: int = MODEL_SINTER | MODEL_HAMAKER, neighbor_list: bool = True) -> Scenario:

@@ -3,7 +3,7 @@ needs /root/reference and oracle/_ref/libref_oracle.so, i.e. `make -C oracle ref
 
     python tests/golden/make_golden.py
 
-* aggregate_150.npy      the coordinate table of resources/aggregate.h:8-158 (units of r_part)
+* ../../libgran_b200/data/aggregate_150.npy  the coordinate table of resources/aggregate.h:8-158 (units of r_part)
 * <scenario>.npz         state of the UNMODIFIED reference (parity build, -ffp-contract=off) after
                          a number of lock-step steps: x, v, theta, omega, a, alpha, neighbor rows,
                          and the reference's own diagnostics (test/compute_energy.cpp,
@@ -27,7 +27,7 @@ def make_aggregate():
     vals = [float(t) for t in re.findall(r"[-+]?\d+\.\d+(?:[eE][-+]?\d+)?", body)]
     arr = np.array(vals, dtype=np.float64).reshape(-1, 3)
     assert arr.shape == (150, 3), arr.shape
-    np.save(os.path.join(HERE, "aggregate_150.npy"), arr)
+    np.save(os.path.join(os.path.dirname(os.path.dirname(HERE)), "libgran_b200", "data", "aggregate_150.npy"), arr)  # package data
     return arr
 
 
