@@ -398,7 +398,6 @@ int evaluate(lg_system* s, const std::vector<Facet>& facets, double fused_dt = -
         }
     }
     A.fc = fast_consts(s->mp.hamaker_A, s->mp.hamaker_h0, s->mp.r, s->mp.mass, s->mp.inertia, s->mp.hamaker_kind, s->mp.hamaker_cutoff);
-    fast_consts_contact(A.fc, s->mp.cp);
     const bool fused = fused_dt >= 0.0;
     A.dt = fused ? fused_dt : 0.0;
     s->halo_stored_by_step = false;

@@ -288,18 +288,12 @@ struct FastConsts {
     int kind;            // HAMAKER_*
     double cutoff;       // limited range: zero beyond this centre distance
     double c_simple;     // simplified: 2 A r / mass
-    double inv_kt, inv_kr, inv_ko;  // contact law: reciprocal shear stiffnesses (set by the host: fast_consts_contact)
 };
 inline FastConsts fast_consts(double A, double h0, double r, double mass, double inertia, int kind = HAMAKER_STANDARD,
                               double cutoff = 0.0) {
     const double r3 = r * r * r;
     return FastConsts{A / 6.0 * 64.0 * r3 * r3 / mass, 2.0 * r, 4.0 * r, h0, 2.0 * r, 1e-12 * r, 1.0 / mass, 1.0 / inertia,
                       kind, cutoff, 2.0 * A * r / mass};
-}
-inline void fast_consts_contact(FastConsts& fc, const ContactParams& p) {
-    fc.inv_kt = p.k_t != 0.0 ? 1.0 / p.k_t : 0.0;
-    fc.inv_kr = p.k_r != 0.0 ? 1.0 / p.k_r : 0.0;
-    fc.inv_ko = p.k_o != 0.0 ? 1.0 / p.k_o : 0.0;
 }
 typedef FastConsts HamakerFast;
 #if defined(__CUDACC__)
@@ -340,56 +334,6 @@ __device__ __forceinline__ void bonded_spring_fast(double k_d, double gamma_d, d
     }
     force += dforce;
     torque += cross_fma(arm, dforce);
-}
-
-// The Luding contact law in relaxed arithmetic (LG_MATH_FAST): the statements of contact_force / shear_spring above with
-// fused multiply-adds, one call-free reciprocal square root per normalisation (the rescaling |xi| / |xi_new| of the rotated
-// spring is ONE rsqrt of the product of the two squared norms) and multiplications by 1 / k, 1 / mass, 1 / inertia.
-// Within ~1e-15 relative of the exact law per evaluation; the Coulomb switch is taken on the relaxed |f_0| (the force and
-// the spring are continuous across it).  Overlap decisions are NOT taken here: the caller decides them on the exact expression.
-__device__ __forceinline__ d3 shear_spring_fast(d3& xi, d3 n, double stiffness, double inv_stiffness, double damping,
-                                                double normal_force, double mu_static, double phi_dynamic, d3 rel_v, double dt) {
-    const double zx = dot_fma(xi, xi);
-    d3 xi_new = xi - dot_fma(xi, n) * n;
-    const double z_new = dot_fma(xi_new, xi_new);
-    if (z_new > 0.0) xi_new = xi_new * (zx * rsqrt_nr(zx * z_new));  // * |xi| / |xi_new| = sqrt(zx / z_new)
-    xi = xi_new;
-    const d3 f_0 = (-stiffness) * xi - damping * rel_v;
-    const double static_friction = mu_static * normal_force;
-    const double dynamic_friction = (mu_static * phi_dynamic) * normal_force;
-    const double z0 = dot_fma(f_0, f_0);
-    const double inv0 = z0 > 0.0 ? rsqrt_nr(z0) : 0.0;
-    const double f0_len = z0 * inv0;
-    const d3 t = f_0 * inv0;
-    double f_selected;
-    if (f0_len <= static_friction) {
-        xi = xi + rel_v * dt;
-        f_selected = static_friction;
-    } else {
-        xi = (-inv_stiffness) * (dynamic_friction * t + damping * rel_v);
-        f_selected = dynamic_friction;
-    }
-    const double f_mag = (f0_len < f_selected) ? f0_len : f_selected;
-    return f_mag * t;
-}
-
-__device__ __forceinline__ Accel contact_force_fast(const ContactParams& p, const FastConsts& fc, double r, d3 n, double overlap, d3 vi, d3 vj, d3 wi, d3 wj, Springs& s) {
-    const double r_prime = r - 0.5 * overlap;
-    const d3 dv = vi - vj;
-    const double v_n = -dot_fma(dv, n);
-    const double f_n = fma(p.k, overlap, p.gamma_n * v_n);
-    const d3 ncwi = cross_fma(n, wi), ncwj = cross_fma(n, wj);
-    const d3 v_ij = (dv + r_prime * ncwi) + r_prime * ncwj;
-    const d3 v_t = v_ij - dot_fma(v_ij, n) * n;
-    const d3 v_r = (-r_prime) * (ncwi - ncwj);
-    const d3 v_o = (r * (dot_fma(n, wi) - dot_fma(n, wj))) * n;
-    const d3 f_t = shear_spring_fast(s.xi[0], n, p.k_t, fc.inv_kt, p.gamma_t, f_n, p.mu_s, p.phi_d, v_t, p.dt);
-    const d3 f_r = shear_spring_fast(s.xi[1], n, p.k_r, fc.inv_kr, p.gamma_r, f_n, p.mu_r, p.phi_r, v_r, p.dt);
-    const d3 f_o = shear_spring_fast(s.xi[2], n, p.k_o, fc.inv_ko, p.gamma_o, f_n, p.mu_o, p.phi_o, v_o, p.dt);
-    const d3 tau_t = r_prime * cross_fma(n, f_t);
-    const d3 tau_r = r * cross_fma(n, f_r);
-    const d3 tau_o = r * f_o;
-    return Accel{(f_n * n + f_t) * fc.inv_mass, (((-tau_t) + tau_r) + tau_o) * fc.inv_inertia};
 }
 
 // Both orientations of one bridge in one pass (step_rows2_kernel, both ends in the same tile): the springs of (j, i) are

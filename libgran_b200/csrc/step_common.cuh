@@ -113,7 +113,10 @@ __device__ __forceinline__ Accel unary_forces(const ForceArgs& A, int i, d3 xi, 
 // The Luding contact law with its history springs for ONE overlapping ordered pair (phase B).  Kept out of line
 // on purpose: it needs ~110 registers and runs for a small minority of pairs, so the kernel's register budget
 // (and with it the number of resident warps) is set by the Hamaker / bridge paths instead; everything it needs
-// is re-read from global memory (L1/L2 hits).  Always the reference's exact arithmetic, in both math modes.
+// is re-read from global memory (L1/L2 hits).  Always the reference's exact arithmetic, in both math modes: a relaxed
+// version (measured: cfg 5d 5.5 -> 4.1 ms) cannot stay within any tolerance of the reference, because the torsion spring
+// accumulates ALONG the contact normal (v_o is parallel to n, contact_force.h:84) and is then projected into the tangent plane
+// and rescaled to its old length (:115-122) -- the direction that survives is rounding residue, reproducible only bit for bit.
 __device__ __noinline__ void contact_heavy(const ForceArgs& A, int i, int j, uint32_t p, double* out6) {
     const d3 xi = load3(A.x + 3 * (size_t)i), vi = load3(A.v + 3 * (size_t)i), wi = load3(A.w + 3 * (size_t)i);
     const d3 xj = load3(A.x + 3 * (size_t)j), vj = load3(A.v + 3 * (size_t)j), wj = load3(A.w + 3 * (size_t)j);
@@ -135,32 +138,6 @@ __device__ __noinline__ void contact_heavy(const ForceArgs& A, int i, int j, uin
         s = ld_springs(A.spr + ((size_t)i * A.S + slot) * 9);
     }
     const Accel c = contact_force(A.mp.cp, A.mp.r, A.mp.mass, A.mp.inertia, g, overlap, vi, vj, wi, wj, s);
-    if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
-    store3(out6, c.a);
-    store3(out6 + 3, c.alpha);
-}
-
-// The same for the relaxed-arithmetic kernels (row kernels, LG_MATH_FAST): contact_force_fast on the caller's relaxed geometry
-// (n, overlap -- the overlap DECISION has been taken by the caller, on the exact expression inside the rounding band).
-__device__ __noinline__ void contact_heavy_fast(const ForceArgs& A, int i, int j, uint32_t p, d3 n, double overlap, double* out6) {
-    const d3 vi = load3(A.v + 3 * (size_t)i), wi = load3(A.w + 3 * (size_t)i);
-    const d3 vj = load3(A.v + 3 * (size_t)j), wj = load3(A.w + 3 * (size_t)j);
-    const int t = A.tag[p];
-    int slot = t;
-    Springs s;
-    if (t == kTagNone) {  // first overlapping evaluation: claim a free slot of particle i
-        slot = -1;
-        for (int k = 0; k < A.S; k++)
-            if (atomicCAS(&A.sgid[(size_t)i * A.S + k], -1, j) == -1) {  // bookkeeping only
-                slot = k;
-                break;
-            }
-        s.xi[0] = s.xi[1] = s.xi[2] = zero3();
-        if (slot >= 0) A.tag[p] = (uint8_t)slot; else atomicOr(A.err, ERR_SLOT_OVERFLOW);
-    } else {
-        s = ld_springs(A.spr + ((size_t)i * A.S + slot) * 9);
-    }
-    const Accel c = contact_force_fast(A.mp.cp, A.fc, A.mp.r, n, overlap, vi, vj, wi, wj, s);
     if (slot >= 0) st_springs(A.spr + ((size_t)i * A.S + slot) * 9, s);
     store3(out6, c.a);
     store3(out6 + 3, c.alpha);
@@ -232,7 +209,7 @@ __device__ __noinline__ void rows_slow_pairs(const ForceArgs& A, const double* s
                 acc_a += ha;
                 continue;
             }
-            contact_heavy_fast(A, i0 + r, j, p, gf.n, overlap, v6);
+            contact_heavy(A, i0 + r, j, p, v6);
         }
         acc_a += kHamaker ? load3(v6) + ha : load3(v6);
         acc_al += load3(v6 + 3);
