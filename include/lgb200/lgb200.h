@@ -383,7 +383,8 @@ int lg_get_profile(lg_system* s, double* force_ms_total, int64_t* force_launches
  * rows -- the row kernel, 2 = as 1 but the row kernel whatever the row length (LG_MATH_FAST only; coverage tests).
  * Variants 0 and 1 give bit-identical results in LG_MATH_EXACT. */
 int lg_set_kernel_variant(lg_system* s, int variant);
-/* Tile shape of step_rows2_kernel (0 = 96 particles x 2 lanes, 1 = 64 x 4, 2 = 32 x 8).  By default a deterministic
+/* Tile shape of step_rows2_kernel (0 = 96 particles x 2 lanes, 1 = 64 x 4, 2 = 32 x 8, 3 = 48 x 2: shape 0's summation order on half-size tiles, for
+ * the small per-rank systems of slab runs).  By default a deterministic
  * rule on the mean row length picks it; lg_set_autotune(1) measures the three shapes on the first fused launches (CUDA events,
  * three launches each) and keeps the fastest -- results then depend on the shape chosen (summation order inside a row),
  * within the LG_MATH_FAST tolerance.  lg_get_rows_shape reports the shape in use. */

@@ -1293,7 +1293,7 @@ int lg_set_autotune(lg_system* s, int enabled) {
 
 int lg_set_rows_shape(lg_system* s, int shape) {
     LG_ENTER(s);
-    if (shape < -1 || shape > 2) return fail(LG_EINVAL, "shape must be -1 (rule / autotune), 0, 1 or 2");
+    if (shape < -1 || shape > 3) return fail(LG_EINVAL, "shape must be -1 (rule / autotune), 0, 1, 2 or 3");
     s->forced_shape = shape;
     return LG_OK;
 }
@@ -2024,7 +2024,8 @@ struct lg_halo {
     // halo stores fused into step_rows2_kernel: host mirrors of the send lists, items per tile for one tile shape
     std::vector<int32_t> h_send_idx[kMaxHaloPeers], h_send_rec[kMaxHaloPeers];
     int items_shape = -1;
-    DevBuf<uint32_t> d_tile_ptr;
+    unsigned int items_tiles = 0;   // tiles that hold at least one item
+    DevBuf<uint32_t> d_tile_ptr, d_tile_order;
     DevBuf<uint2> d_items;
     DevBuf<unsigned int> d_done;
 };
@@ -2055,11 +2056,21 @@ int build_halo_items(lg_system* s, lg_halo* hl, int shape) {
     }
     std::vector<uint32_t> tp(n_tiles + 1, 0);
     std::vector<uint2> items;
+    hl->items_tiles = 0;
     for (size_t t = 0; t < n_tiles; t++) {
         tp[t] = (uint32_t)items.size();
         items.insert(items.end(), per_tile[t].begin(), per_tile[t].end());
+        hl->items_tiles += per_tile[t].empty() ? 0u : 1u;
     }
     tp[n_tiles] = (uint32_t)items.size();
+    std::vector<uint32_t> order;  // tiles with items first (their peer stores then overlap the interior tiles), both ascending
+    order.reserve(n_tiles);
+    for (size_t t = 0; t < n_tiles; t++)
+        if (!per_tile[t].empty()) order.push_back((uint32_t)t);
+    for (size_t t = 0; t < n_tiles; t++)
+        if (per_tile[t].empty()) order.push_back((uint32_t)t);
+    LG_CUDA(hl->d_tile_order.reserve(n_tiles + 1));
+    LG_CUDA(cudaMemcpyAsync(hl->d_tile_order.p, order.data(), n_tiles * sizeof(uint32_t), cudaMemcpyHostToDevice, s->stream));
     LG_CUDA(hl->d_tile_ptr.reserve(n_tiles + 1));
     LG_CUDA(hl->d_items.reserve(items.size() + 1));
     if (!hl->d_done.p) {
@@ -2078,6 +2089,7 @@ int fill_halo_fused(lg_system* s, ForceArgs& A) {
     lg_halo* hl = s->active_halo;
     if (!enabled || hl == nullptr || hl->n_peers == 0) return LG_OK;
     if (hl->items_shape != A.rows_shape) LG_TRY(build_halo_items(s, hl, A.rows_shape));
+    if (hl->items_tiles == 0) return LG_OK;  // nothing to send from any tile: the push kernel handles (and publishes) it
     const unsigned long long seq = hl->seq + 1;  // the exchange halo_exchange is about to run
     const int par = (int)(seq & 1ull);
     HaloFusedArgs& H = A.hf;
@@ -2090,8 +2102,10 @@ int fill_halo_fused(lg_system* s, ForceArgs& A) {
         H.remote_flag[k] = hl->remote_flag[k][par];
     }
     H.tile_ptr = hl->d_tile_ptr.p;
+    H.tile_order = hl->d_tile_order.p;
     H.items = hl->d_items.p;
     H.done = hl->d_done.p;
+    H.expected = hl->items_tiles;
     H.seq = seq;
     s->halo_stored_by_step = true;
     return LG_OK;

@@ -34,15 +34,17 @@ namespace {
 #ifndef LG_R2_LPP
 #define LG_R2_LPP 2    // default shape: lanes per particle in pass 2
 #endif
-// resident CTAs per SM the launch bound asks for: 3 for CTAs of up to 192 threads (112 registers), else 2 (128 registers)
+// resident CTAs per SM the launch bound asks for: 5 for CTAs of 96 threads, 3 up to 192 threads, else 2
 #ifndef LG_R2_MINB
-#define LG_R2_MINB(threads) ((threads) <= 192 ? 3 : 2)
+#define LG_R2_MINB(threads) ((threads) <= 96 ? 5 : (threads) <= 192 ? 3 : 2)
 #endif
 
 // Tile shape: RT particles per tile, LPP cooperating lanes per particle in the pair loop (RT * LPP threads per CTA).
 //   < 96, 2>  rows of ~10 neighbors (aggregates)          staged x: the tile +- 128 particles, 12 pairs per particle
 //   < 64, 4>  rows of ~20-45 (fractal clusters, loose packings)     +- 192                  48
 //   < 32, 8>  rows of ~50-100 (dense packings)                      +- 256                  96
+//   < 48, 2>  shape < 96, 2> on half-size tiles (same lanes per particle = same summation order): small per-rank systems
+//             of slab runs, where 96-particle tiles leave the last wave of CTAs a quarter full
 template <int RT_, int LPP_>
 struct Shape {
     static constexpr int RT = RT_, LPP = LPP_;
@@ -50,7 +52,7 @@ struct Shape {
     static constexpr int RH = LPP == 2 ? 128 : LPP == 4 ? 192 : 256;      // halo of the staged x window (particles either side)
     static constexpr int RPC = (LPP == 2 ? 12 : LPP == 4 ? 48 : 96) * RT; // staged columns / tags per tile
     static constexpr int RBC = 2 * RT + 32;                               // staged bond records per tile
-    static_assert(RT % 32 == 0 && (LPP == 1 || LPP == 2 || LPP == 4 || LPP == 8) && RPC % 16 == 0 && RBC % 16 == 0, "tile shape");
+    static_assert(RT % 16 == 0 && (LPP == 1 || LPP == 2 || LPP == 4 || LPP == 8) && RPC % 16 == 0 && RBC % 16 == 0, "tile shape");
 
     struct alignas(16) Stage {
         double wx[3 * (RT + 2 * RH) + 4];
@@ -189,25 +191,37 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
         }
     };
 
+    // Order in which the grid walks the tiles: ascending, or -- fused launches of slab runs -- the tiles that hold halo items
+    // first, so that their peer stores, fences and the publication of the exchange run underneath the interior tiles instead
+    // of at the kernel's end.
+    auto tile_of = [&](int slot) -> int {
+        if constexpr (MODE == MODE_FUSED) {
+            if (A.hf.tile_order != nullptr) return (int)A.hf.tile_order[slot];
+        }
+        return slot;
+    };
     uint32_t dn[5] = {0u, 0u, 0u, 0u, 0u};  // thread 0: ranges of the NEXT tile of this CTA
     if (tid == 0) {
         mbar_init(&sm.full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         uint32_t d0[5];
-        load_desc(blockIdx.x, d0);
-        issue_loads(blockIdx.x, d0);
-        if ((int)(blockIdx.x + gridDim.x) < n_tiles) load_desc(blockIdx.x + gridDim.x, dn);
+        const int t0 = tile_of((int)blockIdx.x);
+        load_desc(t0, d0);
+        issue_loads(t0, d0);
+        if ((int)(blockIdx.x + gridDim.x) < n_tiles) load_desc(tile_of((int)(blockIdx.x + gridDim.x)), dn);
     }
     __syncthreads();
 
     const int r = tid / LPP, lp = tid % LPP;  // particle of the tile and lane within it (pass 2)
     int k = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, k++) {
+    for (int slot = blockIdx.x; slot < n_tiles; slot += gridDim.x, k++) {
         Stage2& S = sm.st;
+        const int tile = tile_of(slot);
         const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
         const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
-        const int nxt = tile + gridDim.x;
+        const int nslot = slot + (int)gridDim.x;
+        const int nxt = nslot < n_tiles ? tile_of(nslot) : n_tiles;  // n_tiles: none
         mbar_wait(&sm.full, (uint32_t)(k & 1));
 
         double* sxw = S.wx + (window_lead(A.x + 3 * (size_t)xlo) >> 3);  // x of particle xlo + q at sxw[3 q]
@@ -415,10 +429,12 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
                 }
             }
         }
+        bool halo_tile = false;  // this tile has stored halo items into peer memory
         if constexpr (MODE == MODE_FUSED) {
             if (A.hf.tile_ptr != nullptr) {  // slab runs: this tile's halo items go straight into the neighbours' receive buffers
                 const uint32_t h0 = A.hf.tile_ptr[tile], h1 = A.hf.tile_ptr[tile + 1];
                 if (h1 > h0) {  // uniform over the CTA
+                    halo_tile = true;
                     compute_barrier();  // the staged results of every thread (and connectors written to global) are visible
                     // 16 consecutive threads per item, one double each: an item's 72 / 120 bytes leave as one or two
                     // contiguous NVLink writes instead of 9 / 15 scattered ones
@@ -437,12 +453,22 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
                             A.hf.remote[peer][9 * (size_t)it.y + c] = src[3 * idx + (c % 3)];
                         }
                     }
+                    __threadfence_system();  // this thread's peer stores are visible system-wide before the tile is counted
                 }
             }
         }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // this thread's shared-memory writes -> async proxy
         compute_barrier();
         if (tid == 0) {
+            if (halo_tile) {  // count the tile; the launch's last tile with items publishes the exchange to every peer
+                const unsigned int prev = atomicAdd(A.hf.done, 1u);
+                if (prev == A.hf.expected - 1u) {
+                    *A.hf.done = 0u;  // next exchange (stream-ordered after this kernel)
+                    __threadfence_system();
+                    for (int p = 0; p < A.hf.n_peers; p++)
+                        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(A.hf.remote_flag[p]), "l"(A.hf.seq) : "memory");
+                }
+            }
             const uint32_t nb3 = 24u * (uint32_t)nrows;
             const size_t g0 = 3 * (size_t)i0;
             if constexpr (MODE == MODE_FORCE) {
@@ -459,26 +485,11 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
             asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // the stage may be overwritten
             if (nxt < n_tiles) {
                 issue_loads(nxt, dn);
-                if (nxt + (int)gridDim.x < n_tiles) load_desc(nxt + gridDim.x, dn);
+                if (nslot + (int)gridDim.x < n_tiles) load_desc(tile_of(nslot + (int)gridDim.x), dn);
             }
         }
     }
     if (tid == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // all stores have landed before the CTA retires
-    if constexpr (MODE == MODE_FUSED) {
-        if (A.hf.tile_ptr != nullptr) {  // the launch's last CTA publishes the exchange (as halo_push_kernel's last block does)
-            __threadfence_system();
-            __syncthreads();
-            if (tid == 0) {
-                const unsigned int prev = atomicAdd(A.hf.done, 1u);
-                if (prev == gridDim.x - 1u) {
-                    *A.hf.done = 0u;  // next exchange (stream-ordered after this kernel)
-                    __threadfence_system();
-                    for (int p = 0; p < A.hf.n_peers; p++)
-                        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(A.hf.remote_flag[p]), "l"(A.hf.seq) : "memory");
-                }
-            }
-        }
-    }
 }
 
 template <int MASK, int MODE, bool FACETS, int RT2, int LPP>
@@ -504,6 +515,7 @@ void launch_rows2_shape(const ForceArgs& args, cudaStream_t st) {
     switch (args.rows_shape) {
         case 1: launch_rows2_one<MASK, MODE, FACETS, 64, 4>(args, st); break;
         case 2: launch_rows2_one<MASK, MODE, FACETS, 32, 8>(args, st); break;
+        case 3: launch_rows2_one<MASK, MODE, FACETS, 48, 2>(args, st); break;  // shape 0's arithmetic on half-size tiles
         default: launch_rows2_one<MASK, MODE, FACETS, LG_R2_RT, LG_R2_LPP>(args, st); break;
     }
 }
@@ -538,7 +550,7 @@ int rows2_shape_for(double k_mean, int n, bool bonds) {
     if (k_mean <= 48.0) return (bonds || n < 40000) ? 2 : 1;
     return 2;
 }
-int rows2_tile_particles(int shape) { return shape == 1 ? 64 : shape == 2 ? 32 : LG_R2_RT; }
+int rows2_tile_particles(int shape) { return shape == 1 ? 64 : shape == 2 ? 32 : shape == 3 ? 48 : LG_R2_RT; }
 int rows2_tile_records(int shape) { return 2 * rows2_tile_particles(shape) + 32; }
 
 void launch_rows2(const ForceArgs& args, int mask, bool fused, cudaStream_t st) {

@@ -54,18 +54,20 @@ struct ModelParams {
 
 // Halo stores fused into step_rows2_kernel (multi-GPU slab runs): the CTA that finishes a tile copies the tile's halo items
 // -- new x, v, omega of particles a neighbouring rank holds as ghosts, new connector blocks of the bond records it mirrors --
-// from the staged results straight into that rank's receive buffer over NVLink; the last CTA of the launch publishes the
-// exchange's sequence number (release, system scope).  Replaces the separate halo_push_kernel launch.
+// from the staged results straight into that rank's receive buffer over NVLink, fences, and counts the tile; the tile that
+// completes the count publishes the exchange's sequence number (release, system scope).  Replaces the separate halo_push_kernel launch.
 constexpr int kMaxHaloPeers = 8;
 struct HaloFusedArgs {
     const uint32_t* tile_ptr;   // [n_tiles + 1] first item of every tile; nullptr = off
+    const uint32_t* tile_order; // [n_tiles] the order in which the grid walks the tiles: tiles with items first
     const uint2* items;         // x: peer << 24 | kind << 23 | index inside the tile (kind 0: particle row, 1: bond record
                                 //    relative to the tile's first record), y: slot in the peer's message
     int n_peers;
     double* remote[kMaxHaloPeers];              // peer memory of this exchange's parity: particle slot k at 9 k
     long long rec_off[kMaxHaloPeers];           // doubles: connector block k at rec_off + 15 k
     unsigned long long* remote_flag[kMaxHaloPeers];
-    unsigned int* done;         // CTAs of this launch that have stored their items
+    unsigned int* done;         // tiles of this launch that have stored their items
+    unsigned int expected;      // tiles that hold items: the one that completes the count publishes
     unsigned long long seq;
 };
 

@@ -712,6 +712,10 @@ class SlabSystem:
             if self.world > 1:
                 dist.all_reduce(pairs, group=self.group)
             self.rows_shape = int(self.lib.lg_rows_shape_rule(float(int(pairs)) / max(self.n_global, 1), self.n_global, int(self._models[1])))
+            if self.rows_shape == 0 and self.n_global // max(self.world, 1) < 300_000:
+                # same lanes per particle (= same summation order as one GPU), half-size tiles: with ~100 k particles per rank
+                # 96-particle tiles give each resident CTA 3.2 tiles, i.e. a last wave that is a quarter full
+                self.rows_shape = 3
             self._check(self.lib.lg_set_rows_shape(self.h, self.rows_shape))
 
     def facet_update_positions(self, dt: float, facet_id: int = 0):
