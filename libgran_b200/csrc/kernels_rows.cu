@@ -75,6 +75,7 @@ struct Shape {
         uint8_t brow[RBC];       // local row of every staged bond record
         unsigned long long full;
         uint32_t nwork;           // bridge work items of the staged tile
+        uint32_t h0, h1;          // halo items of the staged tile (fused launches of slab runs)
     };
 };
 
@@ -122,16 +123,23 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
     const bool have_bonds = kSinter && A.bptr != nullptr;
 
     // pair / bond-record ranges of tile t: four independent loads (requested a tile ahead, consumed when its copies are issued)
-    auto load_desc = [&](int t, uint32_t d[5]) {
+    auto load_desc = [&](int t, uint32_t d[7]) {
         const int i0 = t * RT2, nr = min(RT2, A.n - i0);
         d[0] = A.row_ptr[i0];
         d[1] = A.row_ptr[i0 + nr];
         d[2] = have_bonds ? A.bptr[i0] : 0u;
         d[3] = have_bonds ? A.bptr[i0 + nr] : 0u;
         d[4] = have_bonds ? A.bwork_cnt[t] : 0u;  // with the others: no dependent load when the copies are issued
+        d[5] = d[6] = 0u;
+        if constexpr (MODE == MODE_FUSED) {
+            if (A.hf.tile_ptr != nullptr) {
+                d[5] = A.hf.tile_ptr[t];
+                d[6] = A.hf.tile_ptr[t + 1];
+            }
+        }
     };
     // bulk copies of every contiguous range tile t reads, completion counted on sm.full (one thread)
-    auto issue_loads = [&](int tile, const uint32_t d[5]) {
+    auto issue_loads = [&](int tile, const uint32_t d[7]) {
         Stage2& S = sm.st;
         const int i0 = tile * RT2, nrows = min(RT2, A.n - i0);
         const int xlo = max(i0 - RH2, 0), xcnt = min(A.n, i0 + RT2 + RH2) - xlo;
@@ -159,6 +167,8 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
         if (nbr)
             total += window_bytes(gconn, 120u * nbr) + window_bytes(glen, 40u * nbr) + window_bytes(gbj, 4u * nbr) +
                      window_bytes(grev, 4u * nbr) + window_bytes(gwork, 2u * nbr);
+        sm.h0 = d[5];
+        sm.h1 = d[6];
         sm.nwork = nbr ? d[4] : 0u;  // published to the other threads by the barrier's release / acquire
         mbar_expect_tx(&sm.full, total);
         if (nbr) {
@@ -178,7 +188,7 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
         if constexpr (kContact) bulk_load(S.wtag, gtag, np0, &sm.full);
     };
     // the big ranges of tile t pulled into L2 (no shared memory needed): by the time the stage is free its copies are L2 hits
-    auto prefetch_tile = [&](int t, const uint32_t d[5]) {
+    auto prefetch_tile = [&](int t, const uint32_t d[7]) {
         const int j0 = t * RT2, nr = min(RT2, A.n - j0);
         l2_prefetch(A.v + 3 * (size_t)j0, 24u * (uint32_t)nr);
         l2_prefetch(A.w + 3 * (size_t)j0, 24u * (uint32_t)nr);
@@ -200,12 +210,12 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
         }
         return slot;
     };
-    uint32_t dn[5] = {0u, 0u, 0u, 0u, 0u};  // thread 0: ranges of the NEXT tile of this CTA
+    uint32_t dn[7] = {0u, 0u, 0u, 0u, 0u, 0u, 0u};  // thread 0: ranges of the NEXT tile of this CTA
     if (tid == 0) {
         mbar_init(&sm.full, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        uint32_t d0[5];
+        uint32_t d0[7];
         const int t0 = tile_of((int)blockIdx.x);
         load_desc(t0, d0);
         issue_loads(t0, d0);
@@ -432,7 +442,7 @@ __global__ void __launch_bounds__(RT2 * LPP, LG_R2_MINB(RT2 * LPP)) step_rows2_k
         bool halo_tile = false;  // this tile has stored halo items into peer memory
         if constexpr (MODE == MODE_FUSED) {
             if (A.hf.tile_ptr != nullptr) {  // slab runs: this tile's halo items go straight into the neighbours' receive buffers
-                const uint32_t h0 = A.hf.tile_ptr[tile], h1 = A.hf.tile_ptr[tile + 1];
+                const uint32_t h0 = sm.h0, h1 = sm.h1;  // loaded with the tile's descriptors a tile ahead
                 if (h1 > h0) {  // uniform over the CTA
                     halo_tile = true;
                     compute_barrier();  // the staged results of every thread (and connectors written to global) are visible

@@ -4,7 +4,7 @@ B="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 
 timeout 900 $B > gpurun_out/${T}_bench_cfg4_${N}gpu.json 2> gpurun_out/${T}_bench_cfg4_${N}gpu.err
 LGB200_HALO_FUSED=0 timeout 900 $B > gpurun_out/${T}_bench_cfg4_${N}gpu_push.json 2> gpurun_out/${T}_bench_cfg4_${N}gpu_push.err
 if [ "$3" = "cfg5" ]; then timeout 1500 $B --config 5 > gpurun_out/${T}_bench_cfg5_${N}gpu.json 2> gpurun_out/${T}_bench_cfg5_${N}gpu.err; fi
-if [ "$2" = "tests" ]; then timeout 1200 python -m pytest tests/test_slab_gpu.py -k "not 1-" -q --tb=line 2>&1 | grep -v "^\[W\|NCCL\|^frame" | tail -8 > gpurun_out/${T}_tests_slab_${N}gpu.log; cat gpurun_out/${T}_tests_slab_${N}gpu.log; fi
+if [ "$2" = "tests" ]; then timeout 1200 python -m pytest tests/test_slab_gpu.py -q --tb=line 2>&1 | grep -v "^\[W\|NCCL\|^frame" | tail -8 > gpurun_out/${T}_tests_slab_${N}gpu.log; cat gpurun_out/${T}_tests_slab_${N}gpu.log; fi
 python - <<PY
 import json, glob
 for f in sorted(glob.glob("gpurun_out/r02p_bench_*_${N}gpu*.json")):
