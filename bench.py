@@ -151,7 +151,9 @@ def build_workload(args, world: int = 1, sample: bool = False):
         copies = args.sample if sample else args.copies
         if c == "4":
             scn = S.multi_aggregate_collision(copies)
-            return scn, f"cfg4 multi-aggregate collision, {scn.cfg.n} particles ({copies} x aggregate.h), sinter+contact+Hamaker", False
+            return scn, (f"cfg4 multi-aggregate collision, {scn.cfg.n} particles ({copies} x aggregate.h), sinter+contact+Hamaker "
+                         "(the halves approach at 1 m/s: no aggregate touches another inside the timed window, contacts = 0 -- bridges + "
+                         "Hamaker work; --config 4c is the same system at impact)"), False
         # CPU sample: the separated layout -- the reference's sinter constructor would bond the touching aggregates together
         scn = S.multi_aggregate_collision(copies) if sample else S.multi_aggregate_in_contact(copies)
         return scn, (f"cfg4c multi-aggregate collision at impact (rows of aggregates slid into first contact at the static-equilibrium overlap), "
