@@ -238,6 +238,8 @@ struct lg_system {
         if (h_pinned) cudaFreeHost(h_pinned);
         if (ev_bbox) cudaEventDestroy(ev_bbox);
         if (ev_pairs) cudaEventDestroy(ev_pairs);
+        for (auto& ev : tune_ev)
+            if (ev) cudaEventDestroy(ev);
         for (auto& ev : prof_events) {
             cudaEventDestroy(ev.first);
             cudaEventDestroy(ev.second);

@@ -122,7 +122,7 @@ def _worker(rank, world, port):
         skin = 1.0 * cfg.r_part
         r_ghost = cfg.r_verlet + skin
         gstate = np.concatenate([scn.x0, scn.v0, scn.theta0, scn.omega0, np.zeros((cfg.n, 6))], axis=1)
-        t0 = slab.block_tables(rank, world, scn.x0, scn.v0, scn.theta0, scn.omega0, 16, *bonds)
+        t0 = slab.block_tables(rank, world, scn.x0, scn.v0, scn.theta0, scn.omega0, 16, *bonds, extra_cols=10)  # one facet's wall history
         t1, bounds = slab.repartition_tables(t0, 0, r_ghost, world)
         assert len(bounds) == world - 1
         _check_tables(t1, rank, world, bounds, scn.x0, gstate, bonds, cfg.r_verlet, r_ghost)
@@ -156,7 +156,12 @@ def _worker(rank, world, port):
         bonds2 = (ij, conn2.reshape(-1, 15), ln)
         rec_owner = torch.repeat_interleave(torch.arange(t1.n), (t1.bptr[1:] - t1.bptr[:-1]).long())
         t1.bconn.view(-1, 5, 3)[:, :, 0] += torch.from_numpy(shift[gidn[rec_owner.numpy()]])[:, None]
+        # wall history of a facet (9 spring components + active flag per particle) rides in the state rows
+        assert t1.state.shape[1] == 28 and bool((t1.state[:, 18:] == 0).all())
+        wall = lambda g: g.double()[:, None] * 10.0 + torch.arange(10, dtype=torch.float64)[None, :]
+        t1.state[:, 18:] = wall(t1.gid)
         t2, bounds2 = slab.repartition_tables(t1, 0, r_ghost, world)
+        assert torch.equal(t2.state[:, 18:], wall(t2.gid)), "wall springs did not travel with their particles"
         moved = torch.tensor([int((t2.owned & (slab.owner_of(torch.from_numpy(scn.x0[t2.gid.numpy(), 0].copy()), bounds) != rank)).sum())])
         dist.all_reduce(moved)
         assert int(moved) > 0, "the test did not make any particle migrate"
