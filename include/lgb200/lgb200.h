@@ -331,6 +331,20 @@ int lg_import_wall_device(lg_system* s, int facet_id, const double* d_wspr, cons
  * pass 0 fills [0..10] = {translational KE, rotational KE, sum v (3), sum (I omega + x cross m v) (3), sum x (3)};
  * pass 1 (d_com = device pointer to the global centre of mass) fills [11] = sum |x - com|^2. */
 int lg_diagnostics_partial(lg_system* s, int pass, const double* d_com, double** d_out);
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The sums of lg_diagnostics_partial
+ * over caller-owned DEVICE arrays d_x, d_v, d_w ([n][3] doubles, pass 1 reads only d_x) into the caller's d_out_12
+ * (12 device doubles, same slots as above; pass 0 writes [0..10], pass 1 writes [11] and needs d_com = 3 device
+ * doubles).  Queued on `stream` (a cudaStream_t, NULL = the default stream) of the CURRENT device, no synchronisation.
+ * It allocates nothing -- no cudaMalloc / cudaFree, no lg_system: the per-block partial sums live in a 48 KiB
+ * file-scope __device__ array that every GPU loading the library holds until exit.  Limits and caveats:
+ *   - n <= lg_diag_sums_static_max_particles() (= 67 108 864); larger n returns LG_ESIZE with a message;
+ *   - every call on a device shares that array (it keeps the last call's contents; the part a call reads is cleared
+ *     and rewritten first), so calls that OVERLAP on the GPU -- different streams, or two host threads with their own
+ *     streams -- race on it; calls on one stream are ordered and safe. */
+int lg_diag_sums_static(int64_t n, const double* d_x, const double* d_v, const double* d_w, double mass, double inertia,
+                        int pass, const double* d_com, double* d_out_12, void* stream);
+int lg_diag_sums_static_max_particles(void);
 /* The bond CSR (rows ascending in partner index): bptr[n+1], bj[nb], connectors[nb][15], rest lengths[nb][5];
  * brev[b] = record index of the mirror (j, i), or b itself when the mirror is not held locally. */
 int lg_export_bonds(lg_system* s, int64_t* n_ordered, uint32_t** d_bptr, int32_t** d_bj, double** d_bconn,

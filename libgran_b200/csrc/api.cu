@@ -1908,6 +1908,37 @@ int lg_diagnostics_partial(lg_system* s, int pass, const double* d_com, double**
     return LG_OK;
 }
 
+// The sums of lg_diagnostics_partial for caller-owned device arrays, allocating nothing: the per-block partials go to a
+// file-scope device array in kernels_neighbor.cu (see launch_diag_sums_static).  Runs on the caller's current device.
+int lg_diag_sums_static_max_particles(void) { return diag_static_max_particles(); }
+
+int lg_diag_sums_static(int64_t n, const double* d_x, const double* d_v, const double* d_w, double mass, double inertia,
+                        int pass, const double* d_com, double* d_out_12, void* stream) {
+    if (n < 1) return fail(LG_EINVAL, "lg_diag_sums_static: n must be >= 1");
+    if (n > (int64_t)diag_static_max_particles())
+        return fail(LG_ESIZE, "lg_diag_sums_static: n = " + std::to_string(n) + " exceeds the static-scratch entry point's limit of " +
+                                  std::to_string(diag_static_max_particles()) + " particles (use lg_diagnostics_partial on an lg_system)");
+    if (pass != 0 && pass != 1) return fail(LG_EINVAL, "lg_diag_sums_static: pass must be 0 or 1");
+    if (!d_x || !d_out_12 || (pass == 0 && (!d_v || !d_w)) || (pass == 1 && !d_com))
+        return fail(LG_EINVAL, "lg_diag_sums_static: null device pointer");
+    int dev = -1;
+    LG_CUDA(cudaGetDevice(&dev));
+    const void* checked[2] = {d_x, d_out_12};
+    for (const void* p : checked) {  // a host pointer or another GPU's memory would fault inside the kernel: refuse it here
+        cudaPointerAttributes at{};
+        LG_CUDA(cudaPointerGetAttributes(&at, p));
+        if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged)
+            return fail(LG_EINVAL, "lg_diag_sums_static: d_x and d_out_12 must be device memory");
+        if (at.type == cudaMemoryTypeDevice && at.device != dev)
+            return fail(LG_EINVAL, "lg_diag_sums_static: the arrays live on device " + std::to_string(at.device) +
+                                       " but the current device is " + std::to_string(dev));
+    }
+    const char* what = "";
+    const int e = launch_diag_sums_static((int)n, d_x, d_v, d_w, mass, inertia, d_com, d_out_12, pass, (cudaStream_t)stream, &what);
+    if (e != 0) return fail(LG_ECUDA, std::string(what) + ": " + cudaGetErrorString((cudaError_t)e));
+    return LG_OK;
+}
+
 int lg_export_wall(lg_system* s, int facet_id, double** d_wspr, uint8_t** d_wact) {
     LG_ENTER(s);
     if (s->reorder_mode) return fail(LG_EINVAL, "lg_export_wall: not available after lg_set_reorder");

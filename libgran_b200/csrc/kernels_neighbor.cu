@@ -10,6 +10,8 @@
 // (this file is compiled with --fmad=false), strict '<' -- so the pair set is bit-identical.
 #include "system.h"
 
+#include <mutex>
+
 namespace lg {
 
 // ---- bounding box --------------------------------------------------------------------------------
@@ -467,6 +469,66 @@ void launch_diag_sums(int n, const double* x, const double* v, const double* w, 
     diag_partial_kernel<<<blocks, kDiagThreads, 0, st>>>(n, x, v, w, mass, inertia, com, d_partials, pass, owned);
     diag_final_kernel<<<1, 32, 0, st>>>(blocks, d_partials, d_out, pass);
     g_launch_count += 2;
+}
+
+// ---- the same sums without any allocation (lg_diag_sums_static) ------------------------------------------------------
+// For callers that may not call cudaMalloc (graph capture, serving loops): the per-block partial sums of
+// diag_partial_kernel live in a file-scope device array instead of a buffer owned by an lg_system.  Every GPU that loads
+// the library holds these kDiagSlots * kDiagMaxBlocks doubles (48 KiB) until exit.  All calls on a device share the array:
+// two calls that overlap on the GPU (different streams) race on it.
+static __device__ __align__(256) double g_diag_static_scratch[kDiagSlots * kDiagMaxBlocks];
+constexpr int kDiagStaticMaxN = 1 << 26;  // stated limit of the entry point (67 108 864 particles)
+
+constexpr int kStaticMaxDevices = 64;
+static double* g_diag_static_ptr[kStaticMaxDevices];  // device address of the array, per device; null until first use
+static std::mutex g_diag_static_mutex;
+
+// The array's name is a host-side stand-in in host code: resolve its device address once per device, with that device
+// current (the caller's current device is the one the kernels launch on).
+static cudaError_t diag_static_scratch(double** out, int* device) {
+    cudaError_t e = cudaGetDevice(device);
+    if (e != cudaSuccess) return e;
+    if (*device < 0 || *device >= kStaticMaxDevices) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(g_diag_static_mutex);
+    if (g_diag_static_ptr[*device] == nullptr) {
+        double* p = nullptr;
+        e = cudaGetSymbolAddress((void**)&p, g_diag_static_scratch);
+        if (e != cudaSuccess) return e;
+        g_diag_static_ptr[*device] = p;
+    }
+    *out = g_diag_static_ptr[*device];
+    return cudaSuccess;
+}
+
+int diag_static_max_particles() { return kDiagStaticMaxN; }
+
+// Launches diag_partial_kernel + diag_final_kernel on `st` with the static scratch; no cudaMalloc / cudaFree anywhere.
+// Returns a CUDA error code (cudaSuccess = 0); *what names the call that failed.
+int launch_diag_sums_static(int n, const double* x, const double* v, const double* w, double mass, double inertia,
+                            const double* com, double* d_out, int pass, cudaStream_t st, const char** what) {
+    double* scratch = nullptr;
+    int device = -1;
+    cudaError_t e = diag_static_scratch(&scratch, &device);
+    if (e != cudaSuccess) {
+        *what = "cudaGetSymbolAddress(g_diag_static_scratch)";
+        return (int)e;
+    }
+    int blocks = (n + kDiagThreads - 1) / kDiagThreads;
+    if (blocks > kDiagMaxBlocks) blocks = kDiagMaxBlocks;
+    if (blocks < 1) blocks = 1;
+    // the array keeps the previous call's partials: clear the part this call reads (every slot is also rewritten by
+    // diag_partial_kernel, so this is belt and braces against a launch that fails part-way)
+    e = cudaMemsetAsync(scratch, 0, (size_t)blocks * kDiagSlots * sizeof(double), st);
+    if (e != cudaSuccess) {
+        *what = "cudaMemsetAsync(static scratch)";
+        return (int)e;
+    }
+    diag_partial_kernel<<<blocks, kDiagThreads, 0, st>>>(n, x, v, w, mass, inertia, com, scratch, pass, nullptr);
+    diag_final_kernel<<<1, 32, 0, st>>>(blocks, scratch, d_out, pass);
+    g_launch_count += 2;
+    e = cudaGetLastError();
+    if (e != cudaSuccess) *what = "diag_partial_kernel / diag_final_kernel launch";
+    return (int)e;
 }
 
 // ---- spatial renumbering (lg_set_reorder) ------------------------------------------------

@@ -190,6 +190,11 @@ void launch_count_slots(int n, const int32_t* sgid, int S, unsigned long long* d
 // out[16]: sums for lg_diagnostics (pass 0) ; pass 1 adds sum |x - com|^2
 void launch_diag_sums(int n, const double* x, const double* v, const double* w, double mass, double inertia,
                       const double* com, double* d_partials, double* d_out, int pass, const uint8_t* owned, cudaStream_t st);
+// the same two kernels with the partial sums in a file-scope device array (no allocation; lg_diag_sums_static); returns a
+// cudaError_t as int and names the failing call in *what
+int launch_diag_sums_static(int n, const double* x, const double* v, const double* w, double mass, double inertia,
+                            const double* com, double* d_out, int pass, cudaStream_t st, const char** what);
+int diag_static_max_particles();
 
 // slab decomposition: ghost staging (kernels_halo.cu)
 void launch_halo_pack(int n_part, const int32_t* idx, int n_rec, const int32_t* rec, const double* x, const double* v,

@@ -43,6 +43,8 @@ ABI_SYMBOLS = (
     "lg_import_slots_device", "lg_export_bonds", "lg_import_bonds_device", "lg_halo_pack", "lg_halo_unpack",
     "lg_halo_create", "lg_halo_set_lists", "lg_halo_export", "lg_halo_connect", "lg_halo_exchange", "lg_run_slab",
     "lg_halo_disconnect", "lg_halo_destroy", "lg_export_wall", "lg_import_wall_device", "lg_diagnostics_partial",
+    # no counterpart in the reference: allocation-free diagnostics sums (static device scratch)
+    "lg_diag_sums_static", "lg_diag_sums_static_max_particles",
 )
 
 
@@ -171,6 +173,8 @@ def load_library(path: Optional[str] = None):
     lib.lg_export_wall.argtypes = [vp, C.c_int, C.POINTER(vp), C.POINTER(vp)]
     lib.lg_import_wall_device.argtypes = [vp, C.c_int, vp, vp]
     lib.lg_diagnostics_partial.argtypes = [vp, C.c_int, vp, C.POINTER(vp)]
+    lib.lg_diag_sums_static.argtypes = [C.c_int64, vp, vp, vp, C.c_double, C.c_double, C.c_int, vp, vp, vp]
+    lib.lg_diag_sums_static_max_particles.argtypes = []
     lib.lg_halo_disconnect.argtypes = [vp]
     lib.lg_halo_destroy.argtypes = [vp]
     for name in ABI_SYMBOLS:
