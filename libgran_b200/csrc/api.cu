@@ -194,6 +194,7 @@ struct lg_system {
     // cell-list scratch
     DevBuf<double> bbox_scratch, bbox_out;
     DevBuf<int32_t> cell_of, order;
+    DevBuf<int32_t> row_hits;  // rebuild scratch: pairs found by the count pass, [entry][particle]
     DevBuf<uint32_t> cell_start, cell_cursor, scan_scratch;
     int64_t last_cells = 0;
     // The cell grid of the previous rebuild is reused for kGridReuse rebuilds: cell_coords clamps, so a grid that no
@@ -637,7 +638,9 @@ int rebuild(lg_system* s) {
     launch_cell_fill(n, s->cell_of.p, s->cell_start.p, s->cell_cursor.p, s->order.p, st);
     // 3. rows: count, scan, fill + sort
     const uint8_t* owned = s->has_owned ? s->owned.p : nullptr;
-    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, owned, st);
+    // the pairs the count pass finds travel to the fill pass in a hit list (no second sweep of the cells)
+    LG_CUDA(s->row_hits.reserve((size_t)n * (size_t)neighbor_hit_list_entries()));
+    launch_row_count(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, s->row_hits.p, owned, st);
     LG_CUDA(cudaMemsetAsync(row_ptr.p + n, 0, sizeof(uint32_t), st));
     launch_exclusive_scan_u32(row_ptr.p, (size_t)n + 1, s->scan_scratch.p, st);
     LG_CUDA(cudaGetLastError());
@@ -664,7 +667,7 @@ int rebuild(lg_system* s) {
             LG_CUDA(tag.reserve(cols.cap));
         }
     }
-    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, cols.p, owned, st);
+    launch_row_fill(n, s->x.p, g, s->cell_start.p, s->order.p, s->r_verlet, row_ptr.p, cols.p, s->row_hits.p, owned, st);
     LG_CUDA(cudaGetLastError());
     s->rebuilds++;
     if (defer) {
@@ -1453,14 +1456,14 @@ int lg_bond_table_create_device(int64_t n, const double* x, double r_part, doubl
     launch_cell_count(ni, dx.p, g, cell_of.p, cell_start.p, st);
     launch_exclusive_scan_u32(cell_start.p, nc1, scratch.p, st);
     launch_cell_fill(ni, cell_of.p, cell_start.p, cell_cursor.p, order.p, st);
-    launch_row_count(ni, dx.p, g, cell_start.p, order.p, range, row_ptr.p, nullptr, st);
+    launch_row_count(ni, dx.p, g, cell_start.p, order.p, range, row_ptr.p, nullptr, nullptr, st);
     LG_CUDA(cudaMemsetAsync(row_ptr.p + n, 0, sizeof(uint32_t), st));
     launch_exclusive_scan_u32(row_ptr.p, (size_t)n + 1, scratch.p, st);
     uint32_t n_cand = 0;
     LG_CUDA(cudaMemcpyAsync(&n_cand, row_ptr.p + n, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
     LG_CUDA(cudaStreamSynchronize(st));
     LG_CUDA(cols.reserve((size_t)n_cand + 16));
-    launch_row_fill(ni, dx.p, g, cell_start.p, order.p, range, row_ptr.p, cols.p, nullptr, st);
+    launch_row_fill(ni, dx.p, g, cell_start.p, order.p, range, row_ptr.p, cols.p, nullptr, nullptr, st);
     // bonds per particle, lexicographic ranks
     launch_bond_count(ni, dx.p, row_ptr.p, cols.p, r_part, crit, deg.p, up.p, st);
     LG_CUDA(cudaMemsetAsync(deg.p + n, 0, sizeof(uint32_t), st));

@@ -10,6 +10,7 @@
 // (this file is compiled with --fmad=false), strict '<' -- so the pair set is bit-identical.
 #include "system.h"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace lg {
@@ -232,12 +233,16 @@ __device__ __forceinline__ bool within_verlet(d3 xi, d3 xj, double r_verlet) {
     return sqrt((d.x * d.x + d.y * d.y) + d.z * d.z) < r_verlet;
 }
 
-template <bool FILL>
+constexpr int kSweepRowCap = 64;  // hit-list entries per particle (second version of the rebuild, below)
+
+// ONLY_LONG (fill pass): leave the rows that fit the hit list to row_fill_hits_kernel (below)
+template <bool FILL, bool ONLY_LONG>
 __global__ void __launch_bounds__(128)
     row_sweep_kernel(int n, const double* x, const NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
                      double r_verlet, uint32_t* row_count, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
+    if (FILL && ONLY_LONG && row_ptr[i + 1] - row_ptr[i] <= (uint32_t)kSweepRowCap) return;
     if (owned != nullptr && !owned[i]) {  // ghost particle (slab decomposition): its forces belong to another rank
         if (!FILL) row_count[i] = 0u;
         return;
@@ -284,17 +289,159 @@ __global__ void __launch_bounds__(128)
     }
 }
 
+// ---- rows, second version (round 2) ------------------------------------------------------------------------------------
+// What the first version paid for (ncu launch lists of configs 3, 4, 5: the fill pass cost 1.5-2.4 x the count pass): a second
+// full sweep of the 27 cells, an IEEE square root per candidate, dependent order[] -> x[] gathers one candidate at a time, an
+// insertion sort of the row IN GLOBAL MEMORY and 4-byte column stores scattered over 32 rows per warp instruction.  Now:
+//   count pass  row_count_hits_kernel: the sweep, kSweepBatch candidates in flight, no square root outside a thin band, and the
+//               ids it finds go to a hit list hits[k * n + i] (k < kSweepRowCap; entry k of every particle side by side);
+//   fill pass   row_fill_hits_kernel: NO sweep -- reads the hit list, sorts the row in shared memory and writes the columns of a
+//               warp's 32 consecutive rows as one coalesced span;  rows longer than kSweepRowCap (dense inputs with a wide
+//               skin) are left to the first version's kernel, restricted to those rows.
+// The predicate is still the reference's: sqrt((dx*dx + dy*dy) + dz*dz) < r_verlet decides every pair whose d^2 lies within
+// 1e-9 (relative) of r_verlet^2; outside that band the comparison of d^2 alone gives the same answer (sqrt is monotone and
+// correctly rounded: d2 < r^2 (1 - 1e-9) implies fl(sqrt(d2)) <= r (1 - 5e-10)(1 + 2^-53) < r, and symmetrically above).
+constexpr int kSweepThreads = 128;
+constexpr int kSweepBatch = 4;    // candidates in flight per thread
+
+int neighbor_hit_list_entries() { return kSweepRowCap; }
+
+struct VerletTest {
+    double r, lo2, hi2;
+};
+__device__ __forceinline__ bool within_verlet_banded(const VerletTest& t, d3 xi, d3 xj) {
+    const d3 d = xi - xj;
+    const double d2 = (d.x * d.x + d.y * d.y) + d.z * d.z;
+    if (d2 < t.lo2) return true;
+    if (d2 >= t.hi2) return false;
+    return sqrt(d2) < t.r;
+}
+
+__global__ void __launch_bounds__(kSweepThreads, 7)
+    row_count_hits_kernel(int n, const double* __restrict__ x, const NeighborGrid g, const uint32_t* __restrict__ cell_start,
+                          const int32_t* __restrict__ order, double r_verlet, uint32_t* __restrict__ row_count,
+                          int32_t* __restrict__ hits, const uint8_t* __restrict__ owned) {
+    const int i = blockIdx.x * kSweepThreads + threadIdx.x;
+    if (i >= n) return;
+    if (owned != nullptr && !owned[i]) {  // ghost particle (slab decomposition): its forces belong to another rank
+        row_count[i] = 0u;
+        return;
+    }
+    VerletTest vt;
+    vt.r = r_verlet;
+    vt.lo2 = (r_verlet * r_verlet) * (1.0 - 1e-9);
+    vt.hi2 = (r_verlet * r_verlet) * (1.0 + 1e-9);
+    const d3 xi = load3(x + 3 * (size_t)i);
+    int c[3];
+    cell_coords(g, xi, c);
+    uint32_t cnt = 0;
+    for (int dx = -1; dx <= 1; dx++) {
+        const int cx = c[0] + dx;
+        if (cx < 0 || cx >= g.dim[0]) continue;
+        for (int dy = -1; dy <= 1; dy++) {
+            const int cy = c[1] + dy;
+            if (cy < 0 || cy >= g.dim[1]) continue;
+            // the three z-neighbours are contiguous in the cell order: one range
+            const int z0 = max(c[2] - 1, 0), z1 = min(c[2] + 1, g.dim[2] - 1);
+            const uint32_t s0 = cell_start[cell_linear(g, cx, cy, z0)];
+            const uint32_t s1 = cell_start[cell_linear(g, cx, cy, z1) + 1];
+            for (uint32_t s = s0; s < s1; s += kSweepBatch) {
+                int j[kSweepBatch];
+                d3 xj[kSweepBatch];
+#pragma unroll
+                for (int u = 0; u < kSweepBatch; u++) j[u] = s + u < s1 ? order[s + u] : i;  // i = "skip"
+#pragma unroll
+                for (int u = 0; u < kSweepBatch; u++) xj[u] = load3(x + 3 * (size_t)j[u]);
+#pragma unroll
+                for (int u = 0; u < kSweepBatch; u++) {
+                    if (j[u] == i || !within_verlet_banded(vt, xi, xj[u])) continue;
+                    if (hits != nullptr && cnt < (uint32_t)kSweepRowCap) hits[(size_t)cnt * (size_t)n + (size_t)i] = j[u];
+                    cnt++;
+                }
+            }
+        }
+    }
+    row_count[i] = cnt;
+}
+
+// Staging slot of entry k of thread t's row: column t of a [kSweepRowCap][kSweepThreads] array, rotated by k inside the
+// warp's 32 columns -- a warp's lanes hit 32 different banks both when every lane touches entry k of its OWN row (loading,
+// sorting) and when consecutive lanes read consecutive entries of ONE row (the span write).
+__device__ __forceinline__ int sweep_slot(int k, int t) { return k * kSweepThreads + (t & ~31) + ((t + k) & 31); }
+
+__global__ void __launch_bounds__(kSweepThreads, 6)
+    row_fill_hits_kernel(int n, const uint32_t* __restrict__ row_ptr, const int32_t* __restrict__ hits,
+                         int32_t* __restrict__ cols) {
+    __shared__ int32_t sbuf[kSweepRowCap * kSweepThreads];
+    __shared__ uint32_t sbase[kSweepThreads];
+    __shared__ uint32_t scnt[kSweepThreads];
+    const int tid = threadIdx.x;
+    const int i = blockIdx.x * kSweepThreads + tid;
+    const uint32_t base = row_ptr[i < n ? i : n];
+    uint32_t cnt = i < n ? row_ptr[i + 1] - base : 0u;
+    if (cnt > (uint32_t)kSweepRowCap) cnt = 0u;  // a long row: not in the hit list, written by row_sweep_kernel<true, true>
+    for (int k = 0; k < (int)cnt; k++) sbuf[sweep_slot(k, tid)] = hits[(size_t)k * (size_t)n + (size_t)i];
+    for (int a = 1; a < (int)cnt; a++) {  // insertion sort by particle id
+        const int32_t key = sbuf[sweep_slot(a, tid)];
+        int b = a - 1;
+        while (b >= 0) {
+            const int32_t vb = sbuf[sweep_slot(b, tid)];
+            if (vb <= key) break;
+            sbuf[sweep_slot(b + 1, tid)] = vb;
+            b--;
+        }
+        sbuf[sweep_slot(b + 1, tid)] = key;
+    }
+    // The rows of a warp's 32 consecutive particles are one contiguous span of cols: write it with consecutive lanes on
+    // consecutive columns.  Column q belongs to the last row whose base is <= q (empty rows share their successor's base).
+    sbase[tid] = base;
+    scnt[tid] = cnt;
+    __syncwarp();
+    const int lane = tid & 31, w0 = tid & ~31;
+    const uint32_t span0 = sbase[w0];
+    const uint32_t span1 = __shfl_sync(0xffffffffu, i < n ? row_ptr[i + 1] : base, 31);
+    for (uint32_t q = span0 + (uint32_t)lane; q < span1; q += 32u) {
+        int r = 0;
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1)
+            if (sbase[w0 + r + step] <= q) r += step;
+        const uint32_t k = q - sbase[w0 + r];
+        if (k < scnt[w0 + r]) cols[q] = sbuf[sweep_slot((int)k, w0 + r)];
+    }
+}
+
+static bool rebuild_v1() {  // LGB200_REBUILD_V1=1: the round-1 kernels only, kept for A/B timing (scripts/rebuild_ab.py)
+    static const bool v1 = [] {
+        const char* e = std::getenv("LGB200_REBUILD_V1");
+        return e != nullptr && e[0] == '1';
+    }();
+    return v1;
+}
+
+// hits: n * neighbor_hit_list_entries() ints of scratch shared by the two passes, or nullptr (then the fill pass sweeps again)
 void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                      double r_verlet, uint32_t* row_count, const uint8_t* owned, cudaStream_t st) {
-    row_sweep_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, row_count, nullptr,
-                                                             nullptr, owned);
+                      double r_verlet, uint32_t* row_count, int32_t* hits, const uint8_t* owned, cudaStream_t st) {
+    if (rebuild_v1())
+        row_sweep_kernel<false, false><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, row_count,
+                                                                        nullptr, nullptr, owned);
+    else
+        row_count_hits_kernel<<<(n + kSweepThreads - 1) / kSweepThreads, kSweepThreads, 0, st>>>(
+            n, x, g, cell_start, order, r_verlet, row_count, hits, owned);
     g_launch_count++;
 }
 void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned, cudaStream_t st) {
-    row_sweep_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, nullptr, row_ptr, cols,
-                                                            owned);
-    g_launch_count++;
+                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, const int32_t* hits, const uint8_t* owned,
+                     cudaStream_t st) {
+    if (rebuild_v1() || hits == nullptr) {
+        row_sweep_kernel<true, false><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, nullptr, row_ptr,
+                                                                       cols, owned);
+        g_launch_count++;
+        return;
+    }
+    row_fill_hits_kernel<<<(n + kSweepThreads - 1) / kSweepThreads, kSweepThreads, 0, st>>>(n, row_ptr, hits, cols);
+    row_sweep_kernel<true, true><<<(n + 127) / 128, 128, 0, st>>>(n, x, g, cell_start, order, r_verlet, nullptr, row_ptr, cols,
+                                                                  owned);
+    g_launch_count += 2;
 }
 
 // Capacity check of a rebuild that runs without a host round trip: d_total[0] <- number of pairs, d_total[1] <- 1 and
@@ -337,13 +484,27 @@ void launch_allpairs_fill(int n, uint32_t* row_ptr, int32_t* cols, cudaStream_t 
 // Carries the sparse contact-spring records across a rebuild: a record keyed by partner id survives if the
 // partner is still in the row; otherwise it is dropped (the reference would have reset it on the last
 // visited non-overlapping evaluation before the pair left the list).
+// tag[0 .. row_ptr[n]) <- kTagNone with 16-byte stores (the first version did it row by row inside retag_kernel: one
+// scattered byte store per pair)
+__global__ void __launch_bounds__(256) tag_clear_kernel(const uint32_t* row_ptr, int n, uint8_t* tag) {
+    const uint32_t total = row_ptr[n];
+    const uint32_t fill = 0x01010101u * (uint32_t)(uint8_t)kTagNone;
+    const uint4 v = make_uint4(fill, fill, fill, fill);
+    const uint32_t n16 = total >> 4;
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n16; k += gridDim.x * blockDim.x)
+        reinterpret_cast<uint4*>(tag)[k] = v;
+    if (blockIdx.x == 0 && threadIdx.x < (total & 15u)) tag[(n16 << 4) + threadIdx.x] = (uint8_t)kTagNone;
+}
+
+template <bool CLEAR_ROWS>
 __global__ void __launch_bounds__(128)
     retag_kernel(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
                  const uint32_t* bptr, const int32_t* bj, int* err) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const uint32_t p0 = row_ptr[i], p1 = row_ptr[i + 1];
-    for (uint32_t p = p0; p < p1; p++) tag[p] = (uint8_t)kTagNone;
+    if (CLEAR_ROWS)
+        for (uint32_t p = p0; p < p1; p++) tag[p] = (uint8_t)kTagNone;
     if (sgid != nullptr) {
         for (int q = 0; q < S; q++) {
             const int32_t partner = sgid[(size_t)i * S + q];
@@ -385,8 +546,14 @@ __global__ void __launch_bounds__(128)
 void launch_retag(int n, const uint32_t* row_ptr, const int32_t* cols, uint8_t* tag, int32_t* sgid, double* spr, int S,
                   const uint32_t* bptr, const int32_t* bj, int* err, cudaStream_t st) {
     if (n <= 0) return;
-    retag_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, row_ptr, cols, tag, sgid, spr, S, bptr, bj, err);
-    g_launch_count++;
+    if (rebuild_v1()) {
+        retag_kernel<true><<<(n + 127) / 128, 128, 0, st>>>(n, row_ptr, cols, tag, sgid, spr, S, bptr, bj, err);
+        g_launch_count++;
+        return;
+    }
+    tag_clear_kernel<<<148 * 4, 256, 0, st>>>(row_ptr, n, tag);
+    retag_kernel<false><<<(n + 127) / 128, 128, 0, st>>>(n, row_ptr, cols, tag, sgid, spr, S, bptr, bj, err);
+    g_launch_count += 2;
 }
 
 __global__ void __launch_bounds__(256) count_slots_kernel(size_t total, const int32_t* sgid, unsigned long long* out) {

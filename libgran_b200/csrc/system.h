@@ -176,10 +176,14 @@ void launch_gather3(int n, const int32_t* idx, const double* src, double* dst, c
 void launch_cell_count(int n, const double* x, NeighborGrid g, int32_t* cell_of, uint32_t* cell_count, cudaStream_t st);
 void launch_cell_fill(int n, const int32_t* cell_of, const uint32_t* cell_start, uint32_t* cell_cursor, int32_t* order,
                       cudaStream_t st);
+// hits: n * neighbor_hit_list_entries() ints of scratch that carries the pairs found by the count pass to the fill pass
+// (which then does not sweep the cells again), or nullptr
+int neighbor_hit_list_entries();
 void launch_row_count(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                      double r_verlet, uint32_t* row_count, const uint8_t* owned, cudaStream_t st);
+                      double r_verlet, uint32_t* row_count, int32_t* hits, const uint8_t* owned, cudaStream_t st);
 void launch_row_fill(int n, const double* x, NeighborGrid g, const uint32_t* cell_start, const int32_t* order,
-                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, const uint8_t* owned, cudaStream_t st);
+                     double r_verlet, const uint32_t* row_ptr, int32_t* cols, const int32_t* hits, const uint8_t* owned,
+                     cudaStream_t st);
 void launch_allpairs_fill(int n, uint32_t* row_ptr, int32_t* cols, cudaStream_t st);
 void launch_pair_guard(int n, uint32_t* row_ptr, uint32_t cap, uint32_t* d_total, int* err, cudaStream_t st);
 // recompute tag[] for every row from the slot table and the bond CSR; frees slots whose partner left the row
